@@ -1,0 +1,418 @@
+// b200pipe.cu -- C ABI of libb200pipe.so (declared in include/b200pipe.h).
+//
+// Replaces, behind the reference's stage-operator seam, what node.py does with a
+// part object: construct (node.py:300-305), load_state_dict(strict=False) (:306),
+// eval (:317) and the per-request forward (:52-53, :159-160).
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "cifar_simt.cuh"
+#include "common.cuh"
+#include "gpt_simt.cuh"
+#include "stage.cuh"
+
+using namespace b2p;
+
+namespace {
+
+__global__ void transpose2d_f32(const float* __restrict__ in, float* __restrict__ out, int R, int C) {
+  // out[c][r] = in[r][c]; tiny one-off weight repack, not on the hot path
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < R * C) {
+    int r = i / C, c = i % C;
+    out[(size_t)c * R + r] = in[i];
+  }
+}
+
+template <typename T>
+int dev_alloc(T** p, size_t n_elems) {
+  B2P_CUDA(cudaMalloc((void**)p, std::max<size_t>(n_elems, 1) * sizeof(T)));
+  return 0;
+}
+
+bool is_cifar(int kind) { return kind == B2P_CIFAR_PART0 || kind == B2P_CIFAR_PART1; }
+bool is_gpt(int kind) { return kind == B2P_GPT_FIRST || kind == B2P_GPT_MIDDLE || kind == B2P_GPT_FINAL; }
+
+int declare_weights(b2p_stage* st) {
+  const b2p_stage_desc& d = st->d;
+  switch (d.kind) {
+    case B2P_CIFAR_PART0:                                   // cifar_model_parts.py:32-35
+      st->add("conv1.weight", {32, 3, 3, 3});
+      st->add("conv1.bias", {32});
+      st->add("conv2.weight", {64, 32, 3, 3});
+      st->add("conv2.bias", {64});
+      return 0;
+    case B2P_CIFAR_PART1:                                   // cifar_model_parts.py:48-51
+      st->add("fc1.weight", {512, 4096});
+      st->add("fc1.bias", {512});
+      st->add("fc2.weight", {10, 512});
+      st->add("fc2.bias", {10});
+      return 0;
+    default:
+      break;
+  }
+  const int64_t C = d.n_embd;
+  if (d.kind == B2P_GPT_FIRST) {                            // gpt_model_parts.py:10-11
+    st->wte = st->add("transformer.wte.weight", {d.vocab_size, C});
+    st->wpe = st->add("transformer.wpe.weight", {d.block_size, C});
+  }
+  for (int i = d.start_layer; i <= d.end_layer; ++i) {      // gpt_model_parts.py:12,30,40
+    std::string p = "transformer.h." + std::to_string(i) + ".";
+    b2p_gpt_block b;
+    b.ln1_w = st->add(p + "ln_1.weight", {C});
+    b.ln1_b = st->add(p + "ln_1.bias", {C}, false);
+    b.attn_w = st->add(p + "attn.c_attn.weight", {3 * C, C});
+    b.attn_b = st->add(p + "attn.c_attn.bias", {3 * C}, false);
+    b.proj_w = st->add(p + "attn.c_proj.weight", {C, C});
+    b.proj_b = st->add(p + "attn.c_proj.bias", {C}, false);
+    b.ln2_w = st->add(p + "ln_2.weight", {C});
+    b.ln2_b = st->add(p + "ln_2.bias", {C}, false);
+    b.fc_w = st->add(p + "mlp.c_fc.weight", {4 * C, C});
+    b.fc_b = st->add(p + "mlp.c_fc.bias", {4 * C}, false);
+    b.fc2_w = st->add(p + "mlp.c_proj.weight", {C, 4 * C});
+    b.fc2_b = st->add(p + "mlp.c_proj.bias", {C}, false);
+    st->blocks.push_back(b);
+  }
+  if (d.kind == B2P_GPT_FINAL) {                            // gpt_model_parts.py:41-42
+    st->lnf_w = st->add("transformer.ln_f.weight", {C});
+    st->lnf_b = st->add("transformer.ln_f.bias", {C}, false);
+    st->head = st->add("lm_head.weight", {d.vocab_size, C});
+  }
+  return 0;
+}
+
+int alloc_gpt_workspace(b2p_stage* st) {
+  B2P_CUDA(cudaFuncSetAttribute(attention_causal_f32, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(AttnSmem)));
+  const size_t M = (size_t)st->d.max_tokens, C = (size_t)st->d.n_embd;
+  B2P_TRY(dev_alloc(&st->ws_ln, M * C));
+  B2P_TRY(dev_alloc(&st->ws_qkv, M * 3 * C));
+  B2P_TRY(dev_alloc(&st->ws_att, M * C));
+  B2P_TRY(dev_alloc(&st->ws_h, M * 4 * C));
+  B2P_TRY(dev_alloc(&st->ws_x[0], M * C));
+  B2P_TRY(dev_alloc(&st->ws_x[1], M * C));
+  B2P_TRY(dev_alloc(&st->bad_flag, 1));
+  B2P_CUDA(cudaMemset(st->bad_flag, 0, sizeof(int)));
+  return 0;
+}
+
+// ---- forward implementations -------------------------------------------------------
+
+int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
+  const int dev = st->d.device;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = (int)std::min<int64_t>(batch, sms);
+  B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
+             st->dev(3), out, (int)batch);
+  return 0;
+}
+
+int fc1_splits(int64_t batch) {
+  const int tiles = ceil_div(batch, 64) * (FC1_N / 64);
+  int splits = 1;
+  while (splits < 16 && tiles * splits < 2 * 148) splits *= 2;
+  return splits;
+}
+
+int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
+  const int splits = fc1_splits(batch);
+  const size_t need = (size_t)splits * batch * FC1_N * sizeof(float);
+  if (need > st->fc_ws_bytes) {
+    // grow the split-K scratch; synchronous, happens only when a larger batch shows up
+    if (st->fc_ws) B2P_CUDA(cudaFree(st->fc_ws));
+    st->fc_ws = nullptr;
+    st->fc_ws_bytes = 0;
+    B2P_CUDA(cudaMalloc((void**)&st->fc_ws, need));
+    st->fc_ws_bytes = need;
+  }
+  dim3 grid(FC1_N / 64, ceil_div(batch, 64), splits);
+  B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, in, st->dev(0), st->fc_ws, (int)batch, FC1_K / splits);
+  B2P_LAUNCH(fc_tail_f32, (int)batch, 128, 0, s, st->fc_ws, splits, (int)batch, st->dev(1),
+             st->dev(2), st->dev(3), out);
+  return 0;
+}
+
+int linear(int epi, const float* A, const float* W, const float* bias, const float* res, float* out,
+           int M, int N, int K, cudaStream_t s) {
+  dim3 grid(ceil_div(N, 64), ceil_div(M, 64));
+  if (K % 16) return fail(B2P_EINVAL, "linear: K=%d must be a multiple of 16", K);
+  switch (epi) {
+    case EPI_NONE: B2P_LAUNCH(linear_f32<EPI_NONE>, grid, 256, 0, s, A, W, bias, res, out, M, N, K); break;
+    case EPI_RELU: B2P_LAUNCH(linear_f32<EPI_RELU>, grid, 256, 0, s, A, W, bias, res, out, M, N, K); break;
+    case EPI_GELU: B2P_LAUNCH(linear_f32<EPI_GELU>, grid, 256, 0, s, A, W, bias, res, out, M, N, K); break;
+    default: return fail(B2P_EINVAL, "linear: bad epilogue %d", epi);
+  }
+  return 0;
+}
+
+int layernorm(const float* x, const float* g, const float* b, float* y, int M, int C, cudaStream_t s) {
+  B2P_LAUNCH(layernorm_rows<float>, ceil_div((int64_t)M * 32, 256), 256, 0, s, x, g, b, y, M, C);
+  return 0;
+}
+
+// Runs this stage's blocks.  `x` is the stage input (never written); the result of
+// the last block lands in `final_out` (caller-provided) -- intermediates ping-pong
+// between the two workspace activations.
+int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s) {
+  const int C = st->d.n_embd, H = st->d.n_head, M = B * T;
+  const float* cur = x;
+  const size_t nb = st->blocks.size();
+  for (size_t i = 0; i < nb; ++i) {
+    const b2p_gpt_block& k = st->blocks[i];
+    float* x1 = st->ws_x[0];
+    float* x2 = (i + 1 == nb) ? final_out : st->ws_x[1];
+    B2P_TRY(layernorm(cur, st->dev(k.ln1_w), st->dev(k.ln1_b), st->ws_ln, M, C, s));
+    B2P_TRY(linear(EPI_NONE, st->ws_ln, st->dev(k.attn_w), st->dev(k.attn_b), nullptr, st->ws_qkv, M, 3 * C, C, s));
+    dim3 agrid(ceil_div(T, 64), H, B);
+    B2P_LAUNCH(attention_causal_f32, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv, st->ws_att, T, C);
+    B2P_TRY(linear(EPI_NONE, st->ws_att, st->dev(k.proj_w), st->dev(k.proj_b), cur, x1, M, C, C, s));
+    B2P_TRY(layernorm(x1, st->dev(k.ln2_w), st->dev(k.ln2_b), st->ws_ln, M, C, s));
+    B2P_TRY(linear(EPI_GELU, st->ws_ln, st->dev(k.fc_w), st->dev(k.fc_b), nullptr, st->ws_h, M, 4 * C, C, s));
+    B2P_TRY(linear(EPI_NONE, st->ws_h, st->dev(k.fc2_w), st->dev(k.fc2_b), x1, x2, M, C, 4 * C, s));
+    cur = x2;
+  }
+  if (nb == 0 && final_out != x)
+    B2P_CUDA(cudaMemcpyAsync(final_out, x, (size_t)M * C * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  return 0;
+}
+
+int check_gpt_geometry(b2p_stage* st, int64_t batch, int64_t seq) {
+  if (batch <= 0 || seq <= 0) return fail(B2P_EINVAL, "batch and seq must be positive");
+  if (seq > st->d.block_size)                                 // gpt_model_parts.py:15
+    return fail(B2P_EINVAL, "Cannot forward, model block size is exhausted. (T=%lld > block_size=%d)",
+                (long long)seq, st->d.block_size);
+  if (batch * seq > st->d.max_tokens)
+    return fail(B2P_ELIMIT, "batch*seq=%lld exceeds the stage's max_tokens=%d", (long long)(batch * seq),
+                st->d.max_tokens);
+  return 0;
+}
+
+int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t seq, cudaStream_t s,
+                int64_t* ids_out) {
+  B2P_TRY(check_gpt_geometry(st, batch, seq));
+  const int B = (int)batch, T = (int)seq, M = B * T, C = st->d.n_embd, V = st->d.vocab_size;
+  const float* x = static_cast<const float*>(in);
+  if (st->d.kind == B2P_GPT_FIRST) {
+    // The embedding is block 0's input: it goes to ws_x[1], which block 0 overwrites
+    // (with its own output) only after reading it for the last time.
+    float* emb = st->blocks.empty() ? static_cast<float*>(out) : st->ws_x[1];
+    B2P_LAUNCH(embed_f32, ceil_div((int64_t)M * 32, 256), 256, 0, s, static_cast<const int64_t*>(in),
+               st->dev(st->wte), st->dev(st->wpe), emb, M, T, C, V, st->bad_flag);
+    if (st->blocks.empty()) return 0;
+    return gpt_blocks(st, emb, static_cast<float*>(out), B, T, s);
+  }
+  if (st->d.kind == B2P_GPT_MIDDLE) return gpt_blocks(st, x, static_cast<float*>(out), B, T, s);
+
+  // final: blocks -> ln_f -> lm_head                          gpt_model_parts.py:44-50
+  const float* hx = x;
+  if (!st->blocks.empty()) {
+    B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s));          // ws_att is free after the last block's proj
+    hx = st->ws_att;
+  }
+  B2P_TRY(layernorm(hx, st->dev(st->lnf_w), st->dev(st->lnf_b), st->ws_ln, M, C, s));
+  if (!ids_out)
+    return linear(EPI_NONE, st->ws_ln, st->dev(st->head), nullptr, nullptr, static_cast<float*>(out), M, V, C, s);
+  // greedy ids: logits in row chunks through a bounded scratch buffer, then row arg-max
+  const size_t chunk = std::min<size_t>((size_t)M, 2048);
+  if (st->ws_logits_rows < chunk) {
+    if (st->ws_logits) B2P_CUDA(cudaFree(st->ws_logits));
+    st->ws_logits = nullptr;
+    st->ws_logits_rows = 0;
+    B2P_CUDA(cudaMalloc((void**)&st->ws_logits, chunk * (size_t)V * sizeof(float)));
+    st->ws_logits_rows = chunk;
+  }
+  for (size_t m0 = 0; m0 < (size_t)M; m0 += chunk) {
+    const int rows = (int)std::min(chunk, (size_t)M - m0);
+    B2P_TRY(linear(EPI_NONE, st->ws_ln + m0 * C, st->dev(st->head), nullptr, nullptr, st->ws_logits, rows, V, C, s));
+    B2P_LAUNCH(argmax_rows, rows, 256, 0, s, st->ws_logits, ids_out + m0, V, (int64_t)V);
+  }
+  return 0;
+}
+
+}  // namespace
+
+// =====================================================================================
+extern "C" {
+
+int b2p_abi_version(void) { return B2P_ABI_VERSION; }
+
+const char* b2p_last_error(void) { return err_slot().c_str(); }
+
+int b2p_device_count(int* count) {
+  if (!count) return fail(B2P_EINVAL, "count is null");
+  *count = 0;
+  B2P_CUDA(cudaGetDeviceCount(count));
+  return 0;
+}
+
+int64_t b2p_launch_count(void) { return launch_counter().load(); }
+
+int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
+  if (!out || !desc) return fail(B2P_EINVAL, "null argument");
+  *out = nullptr;
+  if (!is_cifar(desc->kind) && !is_gpt(desc->kind)) return fail(B2P_EINVAL, "unknown stage kind %d", desc->kind);
+  if (desc->math != B2P_MATH_FP32)
+    return fail(B2P_EINVAL, "math mode %d is not available in this build for kind %d", desc->math, desc->kind);
+  if (is_gpt(desc->kind)) {
+    if (desc->n_embd <= 0 || desc->n_embd % 128 || desc->n_embd > 2048)
+      return fail(B2P_EINVAL, "n_embd=%d must be a positive multiple of 128, at most 2048", desc->n_embd);
+    if (desc->n_head <= 0 || desc->n_embd != desc->n_head * 64)
+      return fail(B2P_EINVAL, "head dim must be 64 (n_embd=%d, n_head=%d)", desc->n_embd, desc->n_head);
+    if (desc->start_layer < 0 || desc->end_layer < desc->start_layer - 1)
+      return fail(B2P_EINVAL, "bad layer range [%d,%d]", desc->start_layer, desc->end_layer);
+    if (desc->block_size <= 0 || desc->max_tokens <= 0) return fail(B2P_EINVAL, "block_size and max_tokens must be positive");
+    if (desc->kind != B2P_GPT_MIDDLE && desc->vocab_size <= 0) return fail(B2P_EINVAL, "vocab_size must be positive");
+  }
+  int ndev = 0;
+  B2P_CUDA(cudaGetDeviceCount(&ndev));
+  if (desc->device < 0 || desc->device >= ndev)
+    return fail(B2P_ECUDA, "device %d not present (%d CUDA devices visible); there is no CPU fallback", desc->device, ndev);
+  b2p_stage* st = new (std::nothrow) b2p_stage();
+  if (!st) return fail(B2P_EINVAL, "out of host memory");
+  st->d = *desc;
+  declare_weights(st);
+  DeviceGuard g(desc->device);
+  for (auto& w : st->w) {
+    int rc = dev_alloc(&w.dev, w.elems());
+    if (rc < 0) { b2p_stage_destroy(st); return rc; }
+  }
+  if (is_gpt(desc->kind)) {
+    int rc = alloc_gpt_workspace(st);
+    if (rc < 0) { b2p_stage_destroy(st); return rc; }
+  }
+  if (desc->kind == B2P_CIFAR_PART0) {
+    // per-device function attribute: set with the stage's device current
+    cudaError_t e = cudaFuncSetAttribute(part0_fused_f32, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sizeof(Part0Smem));
+    if (e != cudaSuccess) {
+      b2p_stage_destroy(st);
+      return fail(B2P_ECUDA, "cudaFuncSetAttribute(part0_fused_f32): %s", cudaGetErrorString(e));
+    }
+  }
+  *out = st;
+  return 0;
+}
+
+int b2p_stage_destroy(b2p_stage* st) {
+  if (!st) return 0;
+  DeviceGuard g(st->d.device);
+  for (auto& w : st->w) cudaFree(w.dev);
+  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->fc_ws);
+  cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
+  cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
+  delete st;
+  return 0;
+}
+
+int b2p_stage_load_weight(b2p_stage* st, const char* name, const void* host_data, int32_t dtype,
+                          const int64_t* shape, int32_t ndim) {
+  if (!st || !name || !host_data || (ndim > 0 && !shape)) return fail(B2P_EINVAL, "null argument");
+  std::string n(name);
+  int i = st->find(n);
+  // tied head: a final stage accepts the embedding matrix under its wte name when the
+  // checkpoint carries no separate lm_head.weight (same tensor upstream).
+  if (i < 0 && st->d.kind == B2P_GPT_FINAL && n == "transformer.wte.weight" && !st->w[st->head].loaded) i = st->head;
+  if (i < 0) return 0;                                      // "unexpected key": not ours
+  b2p_weight& w = st->w[i];
+  if (dtype != B2P_DT_F32) return fail(B2P_EINVAL, "%s: only float32 checkpoints are supported (dtype code %d)", name, dtype);
+  bool same = (size_t)ndim == w.shape.size();
+  for (int k = 0; same && k < ndim; ++k) same = shape[k] == w.shape[k];
+  if (!same) {
+    std::string got, want;
+    for (int k = 0; k < ndim; ++k) got += (k ? "," : "") + std::to_string(shape[k]);
+    for (size_t k = 0; k < w.shape.size(); ++k) want += (k ? "," : "") + std::to_string(w.shape[k]);
+    return fail(B2P_EINVAL, "size mismatch for %s: checkpoint has [%s], stage expects [%s]", name, got.c_str(), want.c_str());
+  }
+  DeviceGuard g(st->d.device);
+  B2P_CUDA(cudaMemcpy(w.dev, host_data, w.elems() * sizeof(float), cudaMemcpyHostToDevice));
+  w.loaded = true;
+  st->finalized = false;
+  return 1;
+}
+
+int b2p_stage_missing(b2p_stage* st, char* names_buf, size_t buf_len) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  int n = 0;
+  std::string all;
+  for (auto& w : st->w)
+    if (w.required && !w.loaded) { ++n; all += (all.empty() ? "" : "\n") + w.name; }
+  if (names_buf && buf_len) {
+    strncpy(names_buf, all.c_str(), buf_len - 1);
+    names_buf[buf_len - 1] = 0;
+  }
+  return n;
+}
+
+int b2p_stage_finalize(b2p_stage* st) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  for (auto& w : st->w)
+    if (w.required && !w.loaded) return fail(B2P_EMISSING, "weight %s was never loaded", w.name.c_str());
+  DeviceGuard g(st->d.device);
+  if (st->d.kind == B2P_CIFAR_PART0) {
+    if (!st->w1t) B2P_TRY(dev_alloc(&st->w1t, 27 * 32));
+    if (!st->w2t) B2P_TRY(dev_alloc(&st->w2t, 288 * 64));
+    B2P_LAUNCH(transpose2d_f32, ceil_div(32 * 27, 256), 256, 0, 0, st->dev(0), st->w1t, 32, 27);
+    B2P_LAUNCH(transpose2d_f32, ceil_div(64 * 288, 256), 256, 0, 0, st->dev(2), st->w2t, 64, 288);
+  }
+  B2P_CUDA(cudaDeviceSynchronize());
+  st->finalized = true;
+  return 0;
+}
+
+int b2p_stage_out_elems(b2p_stage* st, int64_t batch, int64_t seq, int64_t* elems) {
+  if (!st || !elems) return fail(B2P_EINVAL, "null argument");
+  switch (st->d.kind) {
+    case B2P_CIFAR_PART0: *elems = batch * 4096; break;
+    case B2P_CIFAR_PART1: *elems = batch * 10; break;
+    case B2P_GPT_FINAL: *elems = batch * seq * st->d.vocab_size; break;
+    default: *elems = batch * seq * st->d.n_embd; break;
+  }
+  return 0;
+}
+
+int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq, void* stream) {
+  if (!st || !in_dev || !out_dev) return fail(B2P_EINVAL, "null argument");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_forward called before stage_finalize");
+  if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  if (batch > (1LL << 30)) return fail(B2P_ELIMIT, "batch too large");
+  DeviceGuard g(st->d.device);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (st->d.kind) {
+    case B2P_CIFAR_PART0:
+      return cifar_part0_forward(st, static_cast<const float*>(in_dev), static_cast<float*>(out_dev), batch, s);
+    case B2P_CIFAR_PART1:
+      return cifar_part1_forward(st, static_cast<const float*>(in_dev), static_cast<float*>(out_dev), batch, s);
+    default:
+      return gpt_forward(st, in_dev, out_dev, batch, seq, s, nullptr);
+  }
+}
+
+int b2p_stage_check(b2p_stage* st, void* stream) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  if (!st->bad_flag) return 0;
+  DeviceGuard g(st->d.device);
+  int flag = 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  B2P_CUDA(cudaMemcpyAsync(&flag, st->bad_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+  B2P_CUDA(cudaStreamSynchronize(s));
+  if (flag) {
+    B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));
+    return fail(B2P_EINVAL, "index out of range in self: a token id was outside [0, vocab_size=%d)", st->d.vocab_size);
+  }
+  return 0;
+}
+
+int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev, int64_t batch, int64_t seq,
+                             void* stream) {
+  if (!st || !in_dev || !ids_dev) return fail(B2P_EINVAL, "null argument");
+  if (st->d.kind != B2P_GPT_FINAL) return fail(B2P_EINVAL, "forward_argmax is only defined for the GPT final stage");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_forward_argmax called before stage_finalize");
+  DeviceGuard g(st->d.device);
+  return gpt_forward(st, in_dev, nullptr, batch, seq, static_cast<cudaStream_t>(stream), ids_dev);
+}
+
+}  // extern "C"
+
+#include "handoff.cuh"

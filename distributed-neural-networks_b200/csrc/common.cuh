@@ -1,0 +1,96 @@
+// common.cuh -- error plumbing, launch accounting and small device helpers shared
+// by every translation unit of libb200pipe.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <atomic>
+#include <string>
+
+#include "../../include/b200pipe.h"
+
+namespace b2p {
+
+// ---- thread-local error string -------------------------------------------------
+inline std::string& err_slot() {
+  static thread_local std::string s;
+  return s;
+}
+
+inline int fail(int code, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  err_slot() = buf;
+  return code;
+}
+
+#define B2P_CUDA(expr)                                                              \
+  do {                                                                              \
+    cudaError_t _e = (expr);                                                        \
+    if (_e != cudaSuccess)                                                          \
+      return ::b2p::fail(B2P_ECUDA, "%s failed: %s (%s:%d)", #expr,                 \
+                         cudaGetErrorString(_e), __FILE__, __LINE__);               \
+  } while (0)
+
+#define B2P_TRY(expr)                                                               \
+  do {                                                                              \
+    int _rc = (expr);                                                               \
+    if (_rc < 0) return _rc;                                                        \
+  } while (0)
+
+// ---- launch accounting (bench.py reports it as gpu_launches) ---------------------
+inline std::atomic<int64_t>& launch_counter() {
+  static std::atomic<int64_t> c{0};
+  return c;
+}
+
+// Launch + count + check.  Usage: B2P_LAUNCH(kernel, grid, block, smem, stream, args...)
+#define B2P_LAUNCH(kernel, grid, block, smem, stream, ...)                          \
+  do {                                                                              \
+    kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                     \
+    ::b2p::launch_counter().fetch_add(1, std::memory_order_relaxed);                \
+    cudaError_t _e = cudaGetLastError();                                            \
+    if (_e != cudaSuccess)                                                          \
+      return ::b2p::fail(B2P_ECUDA, "launch of %s failed: %s (%s:%d)", #kernel,     \
+                         cudaGetErrorString(_e), __FILE__, __LINE__);               \
+  } while (0)
+
+// Scoped "make this device current, restore on exit".
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// ---- device helpers ----------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// exact (erf) GELU, the nn.GELU() default the oracle pins (oracle/gpt_model.py)
+__device__ __forceinline__ float gelu_erf(float x) {
+  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+}
+
+}  // namespace b2p

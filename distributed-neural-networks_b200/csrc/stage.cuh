@@ -1,0 +1,61 @@
+// stage.cuh -- the stage object behind the C ABI: weight table, packed weights,
+// workspaces.  One b2p_stage corresponds to one instance of a reference part class
+// (MODEL_PARTS_CLASSES value, node.py:29-32 / partitions/gpt_model_parts.py).
+#pragma once
+#include <string>
+#include <vector>
+#include "common.cuh"
+
+struct b2p_weight {
+  std::string name;                 // key in the FULL-model state dict
+  std::vector<int64_t> shape;
+  bool required = true;
+  bool loaded = false;
+  float* dev = nullptr;             // fp32 copy in the original layout
+  size_t elems() const {
+    size_t n = 1;
+    for (auto d : shape) n *= (size_t)d;
+    return n;
+  }
+};
+
+struct b2p_gpt_block {
+  int ln1_w, ln1_b, attn_w, attn_b, proj_w, proj_b, ln2_w, ln2_b, fc_w, fc_b, fc2_w, fc2_b;
+};
+
+struct b2p_stage {
+  b2p_stage_desc d{};
+  std::vector<b2p_weight> w;
+  bool finalized = false;
+
+  // ---- CIFAR part 0 ----
+  float* w1t = nullptr;             // [27][32]
+  float* w2t = nullptr;             // [288][64]
+  // ---- CIFAR part 1 ----
+  float* fc_ws = nullptr;           // split-K partials [splits][M][512]
+  size_t fc_ws_bytes = 0;
+
+  // ---- GPT ----
+  std::vector<b2p_gpt_block> blocks;
+  int wte = -1, wpe = -1, lnf_w = -1, lnf_b = -1, head = -1;
+  float *ws_ln = nullptr, *ws_qkv = nullptr, *ws_att = nullptr, *ws_h = nullptr;
+  float *ws_x[2] = {nullptr, nullptr};
+  float* ws_logits = nullptr;       // forward_argmax chunk buffer
+  size_t ws_logits_rows = 0;
+  int* bad_flag = nullptr;          // device flag: out-of-range token id seen
+
+  int find(const std::string& n) const {
+    for (size_t i = 0; i < w.size(); ++i)
+      if (w[i].name == n) return (int)i;
+    return -1;
+  }
+  int add(const std::string& n, std::vector<int64_t> shape, bool required = true) {
+    b2p_weight x;
+    x.name = n;
+    x.shape = std::move(shape);
+    x.required = required;
+    w.push_back(std::move(x));
+    return (int)w.size() - 1;
+  }
+  float* dev(int i) const { return i >= 0 && w[i].loaded ? w[i].dev : nullptr; }
+};

@@ -1,0 +1,169 @@
+/* b200pipe.h -- C ABI of the B200 pipeline-stage engine (libb200pipe.so).
+ *
+ * The reference (123-code/Distributed-neural-networks) is pure Python and has no
+ * FFI of its own; its seams are Python-level.  This ABI
+ * sits *under* seam 1, the stage-operator seam: everything the reference does
+ * with a stage object --
+ *     part = MODEL_PARTS_CLASSES[part_index](full_model).to(DEVICE)   node.py:300-305
+ *     part.load_state_dict(full_state_dict, strict=False)             node.py:306
+ *     part.eval()                                                     node.py:317
+ *     with torch.no_grad(): y = part(x)                               node.py:52-53,159-160
+ * -- maps onto stage_create / stage_load_weight / stage_finalize / stage_forward
+ * below, and the activation hop  output_np.tobytes() -> TensorRequest ->
+ * stub.SendTensor -> np.frombuffer().copy()  (node.py:73-89, 170-181) maps onto
+ * the b2p_ring_* peer-handoff calls.
+ *
+ * Conventions
+ *   - plain C types only; no torch, no C++ types, no exceptions cross the ABI;
+ *   - every call returns 0 on success or a negative B2P_E* code; the message is
+ *     available from b2p_last_error() (thread-local, valid until the thread's
+ *     next failing call);
+ *   - the caller owns all input/output DEVICE buffers; the library owns weights,
+ *     workspaces and handoff rings;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *     calls only enqueue work, they never synchronise unless stated;
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails
+ *     with B2P_ECUDA.
+ */
+#ifndef B200PIPE_H_
+#define B200PIPE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2P_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B2P_API __attribute__((visibility("default")))
+#else
+#define B2P_API
+#endif
+
+/* error codes */
+#define B2P_OK        0
+#define B2P_EINVAL   -1   /* bad argument (shape, kind, null pointer ...)        */
+#define B2P_ECUDA    -2   /* a CUDA runtime/driver call failed                   */
+#define B2P_ESTATE   -3   /* call out of order (e.g. forward before finalize)    */
+#define B2P_EMISSING -4   /* finalize: a required weight was never loaded        */
+#define B2P_ELIMIT   -5   /* size beyond a documented maximum                    */
+
+/* stage kinds: one per reference part class */
+#define B2P_CIFAR_PART0   0   /* ModelPart0_2Node   cifar_model_parts.py:29-42   */
+#define B2P_CIFAR_PART1   1   /* ModelPart1_2Node   cifar_model_parts.py:45-58   */
+#define B2P_GPT_FIRST     2   /* ModelPart0          partitions/gpt_model_parts.py:6-22  */
+#define B2P_GPT_MIDDLE    3   /* ModelPartIntermediate          ...:26-34        */
+#define B2P_GPT_FINAL     4   /* ModelPartFinal_GPT             ...:36-50        */
+
+/* arithmetic modes (what the contractions compute in) */
+#define B2P_MATH_FP32     0   /* CUDA-core fp32 FMA: reference-grade parity mode           */
+#define B2P_MATH_TF32X3   1   /* tcgen05 kind::tf32, 3-term split ~ fp32: tensor parity    */
+#define B2P_MATH_TF32     2   /* tcgen05 kind::tf32, single pass                           */
+#define B2P_MATH_BF16     3   /* tcgen05 kind::f16 (bf16 in, fp32 accumulate): throughput  */
+
+/* element types of host weight tensors handed to stage_load_weight */
+#define B2P_DT_F32        0
+#define B2P_DT_BF16       1
+#define B2P_DT_I64        2
+
+typedef struct b2p_stage b2p_stage;   /* opaque */
+typedef struct b2p_ring  b2p_ring;    /* opaque */
+
+/* Stage geometry.  CIFAR parts ignore every field except `math`.
+ * GPT parts: local blocks are the reference's inclusive [start_layer,end_layer]
+ * (gpt_model_parts.py:7,12) -- n_local = end-start+1 may be 0. */
+typedef struct b2p_stage_desc {
+  int32_t kind;          /* B2P_CIFAR_* / B2P_GPT_*                               */
+  int32_t math;          /* B2P_MATH_*                                            */
+  int32_t device;        /* CUDA device ordinal that will own the weights         */
+  int32_t start_layer;   /* GPT: first global block index of this stage           */
+  int32_t end_layer;     /* GPT: last global block index (inclusive)              */
+  int32_t n_head;        /* GPT                                                   */
+  int32_t n_embd;        /* GPT: C, multiple of 64, head dim must be 64           */
+  int32_t vocab_size;    /* GPT first/final                                       */
+  int32_t block_size;    /* GPT: max T (gpt_model_parts.py:15 assert)             */
+  int32_t max_tokens;    /* GPT: largest B*T one forward() will carry (workspace) */
+  int32_t reserved[6];
+} b2p_stage_desc;
+
+/* ---- library ---------------------------------------------------------------- */
+B2P_API int         b2p_abi_version(void);
+B2P_API const char* b2p_last_error(void);
+B2P_API int         b2p_device_count(int* count);
+/* number of kernels this library has launched in this process (bench's gpu_launches) */
+B2P_API int64_t     b2p_launch_count(void);
+
+/* ---- stage lifecycle (seam 1; node.py:300-317) ------------------------------- */
+B2P_API int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc);
+B2P_API int b2p_stage_destroy(b2p_stage* st);
+
+/* Upload one named tensor of the FULL-model state dict from host memory.
+ * Names are the reference's .pth keys: "conv1.weight", "fc2.bias", ... for CIFAR
+ * (cifar_model_parts.py:10-14); nanoGPT names "transformer.wte.weight",
+ * "transformer.h.<global i>.attn.c_attn.weight", "lm_head.weight" ... for GPT.
+ * Returns 1 if the stage consumed the tensor, 0 if the name is not one of this
+ * stage's weights (the strict=False "unexpected key" case, node.py:306), <0 on
+ * error (e.g. shape mismatch).  Synchronous w.r.t. the host buffer. */
+B2P_API int b2p_stage_load_weight(b2p_stage* st, const char* name, const void* host_data,
+                          int32_t dtype, const int64_t* shape, int32_t ndim);
+
+/* Number of weights still missing, and their names (strict=False "missing keys"). */
+B2P_API int b2p_stage_missing(b2p_stage* st, char* names_buf, size_t buf_len);
+
+/* Pack weights for the selected math mode (bf16 copies, tf32 hi/lo planes,
+ * transposes).  Must be called once after loading, before forward. */
+B2P_API int b2p_stage_finalize(b2p_stage* st);
+
+/* Output element count for a given input geometry (host helper). */
+B2P_API int b2p_stage_out_elems(b2p_stage* st, int64_t batch, int64_t seq, int64_t* elems);
+
+/* ---- the hot path: one stage forward (node.py:52-53) -------------------------
+ *   CIFAR part0 : in  fp32 [batch,3,32,32] NCHW   -> out fp32 [batch,4096]
+ *   CIFAR part1 : in  fp32 [batch,4096]            -> out fp32 [batch,10] (probabilities)
+ *   GPT first   : in  int64 [batch,seq]            -> out fp32 [batch,seq,C]
+ *   GPT middle  : in  fp32 [batch,seq,C]           -> out fp32 [batch,seq,C]
+ *   GPT final   : in  fp32 [batch,seq,C]           -> out fp32 [batch,seq,V] logits
+ * `seq` is ignored by the CIFAR kinds.  in/out are device pointers on the
+ * stage's device; `in` is not modified; in and out must not overlap. */
+B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
+                      int64_t batch, int64_t seq, void* stream);
+
+/* Synchronising health check: waits for `stream`, then reports (and clears) deferred
+ * device-side input errors of earlier forwards -- today: a token id outside
+ * [0,vocab_size) seen by a GPT first stage (an IndexError in the reference's
+ * nn.Embedding, gpt_model_parts.py:17).  Returns 0 when clean. */
+B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
+
+/* GPT final only: greedy token ids (row arg-max of the logits) without
+ * materialising [B,T,V]; out int64 [batch,seq].  (north_star: "greedy token ids") */
+B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
+                             int64_t batch, int64_t seq, void* stream);
+
+/* ---- activation handoff (replaces node.py:73-89 / :170-181) ------------------
+ * A ring is a set of `slots` fixed-size receive buffers living on the CONSUMER's
+ * GPU plus two 64-bit sequence flags per slot (full / free).  The consumer
+ * process creates it, exports an opaque handle (CUDA IPC), and the producer
+ * process opens it; inside one process ring_open_local() skips IPC.  Data moves
+ * with one device-to-device copy over NVLink; signalling is done with stream
+ * memory operations, so neither side ever blocks the host. */
+#define B2P_RING_HANDLE_BYTES 256
+B2P_API int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes);
+B2P_API int b2p_ring_export(b2p_ring* ring, void* handle_out /* B2P_RING_HANDLE_BYTES */);
+B2P_API int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device);
+B2P_API int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_device);
+B2P_API int b2p_ring_destroy(b2p_ring* ring);
+/* producer: wait until slot (seq % slots) is free, copy `bytes` from src_dev into
+ * it and publish sequence number seq (seq counts from 0, strictly increasing). */
+B2P_API int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uint64_t seq, void* stream);
+/* consumer: make `stream` wait until message seq has landed; returns its device address. */
+B2P_API int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream);
+/* consumer: mark message seq consumed (enqueue after the last kernel that reads the slot). */
+B2P_API int b2p_ring_release(b2p_ring* ring, uint64_t seq, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PIPE_H_ */
