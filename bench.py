@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl engine|reference]
+
+Workload (config.workload): configs[1] of BASELINE.json -- the CIFAR-10 CNN split into
+2 stages (conv | FC), synthetic batch 1024 fed as 8 microbatches of 128, seeded
+default-init weights.  A "step" is one batch of 1024 through both stages.
+  N=1  both stages on the one GPU (the configuration fits one GPU);
+  N=2  stage k on GPU k, activations handed over NVLink (one process per GPU);
+  N=4/8  N/2 independent 2-stage pipelines (CIFAR has only two stages).
+`value`  samples/s with inputs resident in HBM; `e2e` the same through the host-facing
+call (pinned host input -> H2D -> stages -> D2H result inside the timed region).
+`--impl reference` times the CPU port of the reference's two-node localhost gRPC
+pipeline (oracle/node_oracle.py; the reference itself is Python and cannot travel to the
+GPU box) on the host cores; one reference step = ONE microbatch request of 128 samples
+(the reference cannot carry more than 255 samples per message: 4 MiB gRPC cap).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+BATCH, MICROBATCH = 1024, 128
+WEIGHT_SEED, INPUT_SEED = 1234, 0
+FLOP_PART0 = 11_206_656            # per sample, SURVEY 8d
+FLOP_PART1 = 4_204_544
+BYTES_PART0 = 28_672               # per sample: 12 288 in + 16 384 out
+WORKLOAD = "cifar10_cnn_2stage_b1024_mb128"
+METRIC, UNIT = "samples/sec end-to-end", "samples/s"
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU while the timed regions run."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown",
+               0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.active = threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            while not self._stop_evt.is_set():
+                if self.active.is_set():
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                    try:
+                        mask = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                    except Exception:
+                        mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for bit, name in self.REASONS.items():
+                        if mask & bit:
+                            self.reasons.add(name)
+                time.sleep(0.01)
+        except Exception as e:                      # never fail the bench on telemetry
+            self.reasons.add(f"sampler_error:{type(e).__name__}")
+
+    def finish(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ============================================================================================
+# reference arm: CPU port of the two-node gRPC pipeline
+# ============================================================================================
+def time_cpu_pipeline(n_requests: int, warmup: int, batch: int = MICROBATCH, budget_s: float = 120.0):
+    import numpy as np
+    import torch
+    from oracle import cifar_oracle as co
+    from oracle.node_oracle import TwoNodePipeline
+    sd = co.init_state_dict(WEIGHT_SEED)
+    xs = [co.make_input(batch, seed=INPUT_SEED + i).numpy() for i in range(4)]
+    lat = []
+    with TwoNodePipeline(sd) as pipe:
+        for i in range(warmup):
+            pipe.request(xs[i % 4], f"warm{i}")
+        t_start = time.perf_counter()
+        for i in range(n_requests):
+            t0 = time.perf_counter()
+            res, status = pipe.request(xs[i % 4], f"req{i}")
+            lat.append(time.perf_counter() - t0)
+            assert res is not None and res.shape == (batch, 10), status
+            if time.perf_counter() - t_start > budget_s:
+                break
+        total = time.perf_counter() - t_start
+    return {"samples_per_s": batch * len(lat) / total, "requests": len(lat), "batch": batch,
+            "p50_ms": 1e3 * statistics.median(lat), "total_s": total,
+            "cores": os.cpu_count(), "torch_threads": torch.get_num_threads()}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    r = time_cpu_pipeline(args.steps, args.warmup)
+    sample = (f"{r['requests']} requests of {r['batch']} samples (one microbatch each) through the CPU port of "
+              f"the 2-node localhost gRPC pipeline, torch threads {r['torch_threads']} per node process")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT,
+        "n_gpus": args.gpus, "steps": r["requests"], "warmup": args.warmup,
+        "ms_per_step": 1e3 * r["total_s"] / r["requests"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH,
+                   "step": "one 128-sample request (bounded sample: 1/8 of a 1024 batch)"},
+        "p50_request_latency_ms": r["p50_ms"],
+        "cpu_baseline": {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": r["samples_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ============================================================================================
+# engine arm
+# ============================================================================================
+def engine_arm(args):
+    import torch
+    import dnn_b200 as engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        from importlib import import_module
+        return import_module("distributed-neural-networks_b200.rank_pipeline").bench_main(args)
+    if args.gpus != 1:
+        raise SystemExit("--gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+
+    assert torch.cuda.is_available(), "bench.py needs a GPU; there is no CPU fallback"
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    peaks, peaks_kind = _peaks()
+
+    # -- model: seeded default-init weights, the reference's loader sequence -------------------
+    torch.manual_seed(WEIGHT_SEED)
+    full = engine.NeuralNetwork()
+    sd = full.state_dict()
+    parts = []
+    for k in (0, 1):
+        p = engine.MODEL_PARTS_CLASSES[k](full, math=args.math).to(dev)
+        p.load_state_dict(sd, strict=False)
+        parts.append(p.eval())
+    from importlib import import_module
+    pipe = import_module("distributed-neural-networks_b200.pipeline").cifar_pipeline(parts, MICROBATCH, BATCH)
+
+    # -- inputs: a pool of distinct batches larger than L2 (126 MB) so every step reads HBM -----
+    n_pool = 16                                             # 16 x 12.6 MB = 201 MB
+    g = torch.Generator().manual_seed(INPUT_SEED)
+    host_pool = [torch.randn(BATCH, 3, 32, 32, generator=g).pin_memory() for _ in range(n_pool)]
+    dev_pool = [h.to(dev) for h in host_pool]
+    torch.cuda.synchronize()
+
+    sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else local)
+    sampler.start()
+    W, K = max(args.warmup, 3), args.steps
+    last = pipe.compute[-1]
+
+    # -- (1) device-resident throughput --------------------------------------------------------------
+    for i in range(W):
+        pipe.run_device(dev_pool[i % n_pool])
+    pipe.synchronize()
+    launches0 = engine.launch_count()
+    sampler.active.set()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t0.record(pipe.compute[0])
+    for i in range(K):
+        pipe.run_device(dev_pool[(W + i) % n_pool])
+    last.wait_stream(pipe.compute[0])
+    t1.record(last)
+    torch.cuda.synchronize()
+    ms_dev = t0.elapsed_time(t1)
+    launches = engine.launch_count() - launches0
+
+    # -- (2) end to end through the host-facing call ----------------------------------------------------
+    for i in range(W):
+        pipe.run_host(host_pool[i % n_pool], sync=False)
+    pipe.synchronize()
+    torch.cuda.synchronize()
+    w0 = time.perf_counter()
+    for i in range(K):
+        pipe.run_host(host_pool[(W + i) % n_pool], sync=False)
+    last.synchronize()
+    torch.cuda.synchronize()
+    ms_e2e = 1e3 * (time.perf_counter() - w0)
+    checksum = float(pipe.out_host.sum())          # a real read of the last step's result
+
+    # -- (3) request latency: B=1 through the same call, synchronous ---------------------------------------
+    one = host_pool[0][:1].clone().pin_memory()
+    lats = []
+    for i in range(20 + 200):
+        q0 = time.perf_counter()
+        pipe.run_host(one, sync=True)
+        if i >= 20:
+            lats.append(1e3 * (time.perf_counter() - q0))
+
+    # -- (4) roofline of the dominant kernel (stage 0), timed alone on its launch stream ------------------
+    s0 = pipe.compute[0]
+    act = pipe.hidden[0]
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_launch = 0
+    torch.cuda.synchronize()
+    r0.record(s0)
+    for i in range(K):
+        x = dev_pool[(W + i) % n_pool]
+        for lo in range(0, BATCH, MICROBATCH):
+            parts[0].forward_ptr(x[lo:].data_ptr(), act[lo:].data_ptr(), MICROBATCH, 0, s0.cuda_stream)
+            n_launch += 1
+    r1.record(s0)
+    torch.cuda.synchronize()
+    us_k0 = 1e3 * r0.elapsed_time(r1) / n_launch
+    sampler.active.clear()
+    clocks = sampler.finish()
+
+    tf = FLOP_PART0 * MICROBATCH / (us_k0 * 1e-6) / 1e12
+    peak_tf = peaks["bf16_tflops_sustained"]
+    roofline = {"kernel": "part0 (conv1+ReLU+pool+conv2+ReLU+pool), one launch per 128-sample microbatch",
+                "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                "traffic": None, "peak_source": f"bf16_tflops_sustained of {peaks_kind}",
+                "us_per_launch": us_k0,
+                "hbm_view": {"achieved_gbs": BYTES_PART0 * MICROBATCH / (us_k0 * 1e-6) / 1e9, "peak_gbs": peaks["hbm_gbs"]}}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        r = time_cpu_pipeline(n_requests=40, warmup=3, budget_s=25.0)
+        cpu = {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+               "p50_request_latency_ms": r["p50_ms"],
+               "sample": f"{r['requests']} requests of {r['batch']} samples through the CPU port of the reference's "
+                         f"2-node localhost gRPC pipeline ({r['total_s']:.1f} s, torch threads {r['torch_threads']})"}
+
+    line = {
+        "metric": METRIC, "value": BATCH * K / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
+        "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"fp32": "f32", "tf32x3": "tf32x3", "tf32": "tf32", "bf16": "bf16"}[args.math],
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH, "stages": 2,
+                   "placement": "both stages on one GPU", "math": args.math,
+                   "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
+        "e2e": {"value": BATCH * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4,
+                "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
+        "p50_request_latency_ms": statistics.median(lats),
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["engine", "reference"], default="engine")
+    ap.add_argument("--math", default="fp32", choices=["fp32", "tf32x3", "tf32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    return reference_arm(args) if args.impl == "reference" else engine_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -109,12 +109,10 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   return 0;
 }
 
-int fc1_splits(int64_t batch) {
-  const int tiles = ceil_div(batch, 64) * (FC1_N / 64);
-  int splits = 1;
-  while (splits < 16 && tiles * splits < 2 * 148) splits *= 2;
-  return splits;
-}
+// Fixed split count: a row's summation order must not depend on the batch it travels
+// in, so that micro-batching (8 x 128 vs 1 x 1024) is bit-exact.
+constexpr int FC1_SPLITS = 8;
+int fc1_splits(int64_t) { return FC1_SPLITS; }
 
 int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
   const int splits = fc1_splits(batch);

@@ -1,0 +1,138 @@
+"""Micro-batched pipeline schedules over the stage operators.
+
+The reference moves ONE whole activation per request from node to node through
+gRPC and overlaps nothing (node.py:52-53 blocks the event loop; node.py:73-89 is a
+nested unary RPC).  Here a request batch is cut along the batch dimension into
+microbatches -- exact, because no op on the path mixes samples -- and every
+microbatch flows stage by stage while the next one is already being copied /
+computed (1F pipelining).
+
+``LocalPipeline``  all stages driven from one process (one or several GPUs); this is
+                   what the NodeService front door and the single-GPU bench use.
+``RankPipeline``   (multi-process, one rank per GPU) lives in rank_pipeline.py.
+"""
+from __future__ import annotations
+
+import torch
+
+from .stages import EngineStage
+
+
+class LocalPipeline:
+    """Stages on one or more GPUs of this process, activations stay in HBM.
+
+    ``run_device``  inputs already resident on the first stage's GPU
+    ``run_host``    the user-facing call: pinned host input -> H2D per microbatch on a
+                    copy stream -> stages -> D2H of the result, all asynchronous; only
+                    the final ``synchronize`` blocks.
+    """
+
+    def __init__(self, stages: list[EngineStage], microbatch: int, in_shape: tuple, in_dtype,
+                 out_shape: tuple, hidden_shapes: list[tuple], max_batch: int):
+        assert stages and all(s._handle is not None for s in stages), "stages must be on CUDA devices"
+        self.stages = stages
+        self.mb = int(microbatch)
+        self.max_batch = int(max_batch)
+        self.devs = [s._device for s in stages]
+        self.in_shape, self.in_dtype, self.out_shape = tuple(in_shape), in_dtype, tuple(out_shape)
+        d0, dl = self.devs[0], self.devs[-1]
+        self.compute = [torch.cuda.Stream(device=d) for d in self.devs]
+        self.copy_in = torch.cuda.Stream(device=d0)
+        # device-resident buffers, allocated once
+        self.x_dev = [torch.empty((self.max_batch, *self.in_shape), dtype=in_dtype, device=d0) for _ in range(2)]
+        self.hidden = [torch.empty((self.max_batch, *shp), dtype=torch.float32, device=self.devs[k + 1])
+                       for k, shp in enumerate(hidden_shapes)]
+        # when consecutive stages sit on different GPUs the producer writes into a staging
+        # buffer on its own GPU and a peer copy moves it (handoff); same GPU: write in place
+        self.stage_out = []
+        for k, shp in enumerate(hidden_shapes):
+            if self.devs[k] == self.devs[k + 1]:
+                self.stage_out.append(self.hidden[k])
+            else:
+                self.stage_out.append(torch.empty((self.max_batch, *shp), dtype=torch.float32, device=self.devs[k]))
+        self.out_dev = torch.empty((self.max_batch, *self.out_shape), dtype=torch.float32, device=dl)
+        self.out_host = torch.empty((self.max_batch, *self.out_shape), dtype=torch.float32).pin_memory()
+        self._flip = 0
+        self._x_free = [None, None]        # event: last reader of x_dev[i] has finished
+        # back-pressure between steps: hidden[k] rows of microbatch i may be overwritten only
+        # after stage k+1 has consumed what the previous step left there
+        self._consumed = [dict() for _ in hidden_shapes]
+        for s in stages:
+            s._finalize()
+
+    # -- device-resident schedule -------------------------------------------------------
+    def run_device(self, x: torch.Tensor, out: torch.Tensor | None = None, seq: int = 0,
+                   ready: list | None = None) -> torch.Tensor:
+        """x: [B, *in_shape] on stage 0's GPU.  Enqueues everything; returns the device
+        output (valid once ``self.compute[-1]`` has drained).  ``ready[i]`` (optional) is
+        an event after which microbatch i of x may be read."""
+        b = x.shape[0]
+        assert b <= self.max_batch
+        out = self.out_dev if out is None else out
+        n_st = len(self.stages)
+        for i, lo in enumerate(range(0, b, self.mb)):
+            n = min(self.mb, b - lo)
+            src = x[lo:lo + n]
+            for k, st in enumerate(self.stages):
+                s = self.compute[k]
+                if k == 0 and ready is not None:
+                    s.wait_event(ready[i])
+                if k > 0:
+                    s.wait_event(prev_done)
+                if k < n_st - 1 and i in self._consumed[k]:
+                    s.wait_event(self._consumed[k][i])
+                dst = out[lo:lo + n] if k == n_st - 1 else self.stage_out[k][lo:lo + n]
+                st.forward_ptr(src.data_ptr(), dst.data_ptr(), n, seq, s.cuda_stream)
+                if k > 0:
+                    done = torch.cuda.Event()
+                    done.record(s)
+                    self._consumed[k - 1][i] = done
+                if k < n_st - 1:
+                    if self.stage_out[k] is not self.hidden[k]:
+                        with torch.cuda.stream(s):         # NVLink peer copy on the producer's stream
+                            self.hidden[k][lo:lo + n].copy_(dst, non_blocking=True)
+                    prev_done = torch.cuda.Event()
+                    prev_done.record(s)
+                    src = self.hidden[k][lo:lo + n]
+        return out[:b]
+
+    # -- host-facing schedule ---------------------------------------------------------------
+    def run_host(self, x_host: torch.Tensor, seq: int = 0, sync: bool = True) -> torch.Tensor:
+        """x_host: pinned host tensor [B, *in_shape].  Returns the pinned host result
+        [B, *out_shape] (a view of an internal buffer, overwritten by the next call)."""
+        b = x_host.shape[0]
+        assert b <= self.max_batch
+        flip = self._flip
+        xd = self.x_dev[flip]
+        self._flip ^= 1
+        ready = []
+        # the copy stream must not overwrite xd while the run before last still reads it
+        # (double buffer: the copy of step s+1 overlaps the compute of step s)
+        if self._x_free[flip] is not None:
+            self.copy_in.wait_event(self._x_free[flip])
+        with torch.cuda.stream(self.copy_in):
+            for lo in range(0, b, self.mb):
+                n = min(self.mb, b - lo)
+                xd[lo:lo + n].copy_(x_host[lo:lo + n], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.copy_in)
+                ready.append(ev)
+        out = self.run_device(xd[:b], seq=seq, ready=ready)
+        ev = torch.cuda.Event()
+        ev.record(self.compute[0])
+        self._x_free[flip] = ev
+        last = self.compute[-1]
+        with torch.cuda.stream(last):
+            self.out_host[:b].copy_(out, non_blocking=True)
+        if sync:
+            last.synchronize()
+        return self.out_host[:b]
+
+    def synchronize(self):
+        for s in self.compute:
+            s.synchronize()
+
+
+def cifar_pipeline(parts, microbatch: int = 128, max_batch: int = 1024) -> LocalPipeline:
+    """BASELINE config 2: CIFAR conv | FC, batch 1024 in microbatches of 128."""
+    return LocalPipeline(list(parts), microbatch, (3, 32, 32), torch.float32, (10,), [(4096,)], max_batch)

@@ -224,7 +224,7 @@ class ModelPart0_2Node(_CifarPart):
         if x.dim() != 4 or tuple(x.shape[1:]) != (3, 32, 32):
             raise RuntimeError(f"expected input [B,3,32,32], got {list(x.shape)}")
         out = torch.empty((x.shape[0], 4096), dtype=torch.float32, device=self._device)
-        return self._run(x, out, x.shape[0], 0)
+        return self._run(x, out, x.shape[0], 0) if x.shape[0] else out
 
 
 class ModelPart1_2Node(_CifarPart):
@@ -239,7 +239,7 @@ class ModelPart1_2Node(_CifarPart):
         if x.dim() != 2 or x.shape[1] != 4096:
             raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({list(x.shape)} and 4096x512)")
         out = torch.empty((x.shape[0], 10), dtype=torch.float32, device=self._device)
-        return self._run(x, out, x.shape[0], 0)
+        return self._run(x, out, x.shape[0], 0) if x.shape[0] else out
 
 
 class NeuralNetwork(nn.Module):

@@ -1,0 +1,143 @@
+"""CIFAR parity on the GPU: the engine's CUDA parts, called through the C ABI, against
+(i) golden vectors produced by the reference's own classes and (ii) the CPU oracle on
+seeded inputs.  Tolerances (fp32 arithmetic, differs from oneDNN only by summation
+order): activations |d| <= 2e-5, probabilities |d| <= 1e-5, arg-max class bit-exact
+wherever the oracle's top-2 probability gap exceeds 1e-5 (near-ties are counted and
+reported, not hidden)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cifar_oracle as co
+
+pytestmark = pytest.mark.gpu
+ACT_TOL, PROB_TOL, TIE = 2e-5, 1e-5, 1e-5
+
+
+@pytest.fixture(scope="module")
+def parts(cuda_engine):
+    sd = co.init_state_dict(1234)
+    full = cuda_engine.NeuralNetwork()
+    out = []
+    for k in (0, 1):                       # the reference's exact sequence, node.py:300-317
+        p = cuda_engine.MODEL_PARTS_CLASSES[k](full).to("cuda:0")
+        missing, unexpected = p.load_state_dict(sd, strict=False)
+        assert not missing and len(unexpected) == 4
+        out.append(p.eval())
+    return sd, out[0], out[1]
+
+
+def test_golden_from_reference_classes(parts, golden_dir):
+    _, p0, p1 = parts
+    g = np.load(os.path.join(golden_dir, "cifar_b8.npz"))
+    with torch.no_grad():
+        act = p0(torch.from_numpy(g["x"]).cuda())
+        probs = p1(act)
+        probs_from_golden_act = p1(torch.from_numpy(g["part0"]).cuda())
+    assert act.shape == (8, 4096) and act.dtype == torch.float32 and act.is_contiguous()
+    np.testing.assert_allclose(act.cpu().numpy(), g["part0"], rtol=0, atol=ACT_TOL)
+    np.testing.assert_allclose(probs.cpu().numpy(), g["probs"], rtol=0, atol=PROB_TOL)
+    np.testing.assert_allclose(probs_from_golden_act.cpu().numpy(), g["probs"], rtol=0, atol=PROB_TOL)
+    assert np.array_equal(probs.argmax(1).cpu().numpy(), g["probs"].argmax(1))
+
+
+@pytest.mark.parametrize("batch", [1, 3, 64, 128, 130, 1024])
+def test_parity_vs_oracle(parts, batch):
+    sd, p0, p1 = parts
+    x = co.make_input(batch, seed=100 + batch)
+    with torch.no_grad():
+        act = p0(x.cuda())
+        probs = p1(act).cpu()
+    want_act, want = co.part0(x, sd), co.full(x, sd)
+    assert (act.cpu() - want_act).abs().max().item() <= ACT_TOL
+    assert (probs - want).abs().max().item() <= PROB_TOL
+    decided = co.top2_margin(want) > TIE
+    assert torch.equal(probs.argmax(1)[decided], want.argmax(1)[decided])
+    np.testing.assert_allclose(probs.sum(1).numpy(), np.ones(batch), atol=1e-6)
+
+
+def test_argmax_bit_exact_over_10k_samples(parts):
+    sd, p0, p1 = parts
+    n, flips, ties = 10240, 0, 0
+    for chunk in range(n // 1024):
+        x = co.make_input(1024, seed=5000 + chunk)
+        with torch.no_grad():
+            probs = p1(p0(x.cuda())).cpu()
+        want = co.full(x, sd)
+        decided = co.top2_margin(want) > TIE
+        ties += int((~decided).sum())
+        flips += int((probs.argmax(1)[decided] != want.argmax(1)[decided]).sum())
+        assert (probs - want).abs().max().item() <= PROB_TOL
+    print(f"\n10240 samples: {flips} arg-max flips among decided rows, {ties} near-ties (gap<={TIE})")
+    assert flips == 0
+    assert ties <= 10          # near-ties are rare for random-init weights; report if not
+
+
+def test_microbatching_is_bit_exact_at_full_size(parts):
+    """BASELINE config 2: batch 1024 as 8 microbatches of 128 == one batch of 1024."""
+    _, p0, p1 = parts
+    x = co.make_input(1024, seed=77).cuda()
+    with torch.no_grad():
+        whole = p1(p0(x))
+        pieces = torch.cat([p1(p0(x[i:i + 128])) for i in range(0, 1024, 128)])
+    assert torch.equal(whole, pieces)
+
+
+def test_pipeline_equals_full_model_and_is_deterministic(cuda_engine, parts):
+    sd, p0, p1 = parts
+    full = cuda_engine.NeuralNetwork()
+    full.load_state_dict(sd)
+    full = full.to("cuda:0")
+    x = co.make_input(256, seed=9).cuda()
+    with torch.no_grad():
+        a, b, c = p1(p0(x)), full(x), p1(p0(x))
+    assert torch.equal(a, b) and torch.equal(a, c)
+
+
+def test_edge_inputs(parts):
+    _, p0, p1 = parts
+    with torch.no_grad():
+        assert p0(torch.zeros(0, 3, 32, 32)).shape == (0, 4096)
+        assert p1(torch.zeros(0, 4096)).shape == (0, 10)
+        # all-zero image: conv output = bias path only, still a valid distribution
+        z = p1(p0(torch.zeros(2, 3, 32, 32)))
+        assert torch.allclose(z.sum(1), torch.ones(2, device=z.device), atol=1e-6)
+        assert torch.equal(z[0], z[1])
+        # non-contiguous (channels-last strided) input is accepted like torch would
+        x = co.make_input(4, seed=1)
+        nc = x.permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+        assert not nc.is_contiguous()
+        assert torch.equal(p0(nc.cuda()), p0(x.cuda()))
+        # host tensors are moved to the stage's device (node.py:48 does .to(DEVICE))
+        assert p0(x).is_cuda
+    with pytest.raises(RuntimeError):
+        p0(torch.zeros(2, 3, 31, 32).cuda())
+    with pytest.raises(RuntimeError):
+        p1(torch.zeros(2, 4095).cuda())
+    with pytest.raises(RuntimeError):
+        p0(torch.zeros(2, 3, 32, 32, dtype=torch.float64).cuda())
+
+
+def test_weights_reload_takes_effect(cuda_engine):
+    sd = co.init_state_dict(1234)
+    sd2 = co.init_state_dict(4321)
+    p1 = cuda_engine.ModelPart1_2Node(cuda_engine.NeuralNetwork()).to("cuda:0")
+    x = torch.rand(5, 4096)
+    p1.load_state_dict(sd, strict=False)
+    a = p1.eval()(x).cpu()
+    p1.load_state_dict(sd2, strict=False)
+    b = p1(x).cpu()
+    assert (a - co.part1(x, sd)).abs().max() <= PROB_TOL
+    assert (b - co.part1(x, sd2)).abs().max() <= PROB_TOL
+    assert not torch.equal(a, b)
+
+
+def test_native_library_is_what_ran(cuda_engine, parts):
+    _, p0, _ = parts
+    before = cuda_engine.launch_count()
+    p0(torch.zeros(1, 3, 32, 32).cuda())
+    assert cuda_engine.launch_count() == before + 1
+    maps = open("/proc/self/maps").read()
+    assert "libb200pipe.so" in maps
