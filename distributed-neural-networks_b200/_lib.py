@@ -18,6 +18,7 @@ MATH_FP32, MATH_TF32X3, MATH_TF32, MATH_BF16 = range(4)
 MATH_NAMES = {"fp32": MATH_FP32, "tf32x3": MATH_TF32X3, "tf32": MATH_TF32, "bf16": MATH_BF16}
 DT_F32, DT_BF16, DT_I64 = range(3)
 RING_HANDLE_BYTES = 256
+NOALLOC_MAX_BATCH = 256
 
 
 class StageDesc(C.Structure):
@@ -48,6 +49,7 @@ _PROTOTYPES = {
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_stage_forward_argmax": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "b2p_cifar_part1_forward_noalloc": (C.c_int, [C.c_void_p] * 6 + [C.c_int64, C.c_void_p]),
     "b2p_ring_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_size_t]),
     "b2p_ring_export": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_ring_open": (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int]),

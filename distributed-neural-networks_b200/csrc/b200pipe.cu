@@ -414,3 +414,73 @@ int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev
 }  // extern "C"
 
 #include "handoff.cuh"
+
+// =====================================================================================
+// Allocation-free variant of the CIFAR part-1 forward (fc1 split-K + tail).
+//
+// b2p_stage_forward() keeps the fc1 split-K partial sums in a buffer it obtains with
+// cudaMalloc the first time a batch of a given size shows up.  Some hosts cannot let a
+// library do that: a serving thread with a latency budget must never run into the
+// device-wide synchronisation cudaMalloc/cudaFree imply, and a process whose device
+// memory was handed out in full to its own pool at start-up has nothing left for a
+// library to allocate behind its back (the call would fail, or break the host's
+// accounting).  For them the partial sums live in the fixed array below, which is part of
+// the library image: every GPU that loads libb200pipe.so holds these 4 MiB until the
+// process exits, whether or not this entry point is ever called.
+//
+// Sharing rules.  There is ONE array per GPU and every call on that GPU uses it, keeping
+// whatever the previous call left there.  Nothing in it has to start at zero: a call with
+// batch M first overwrites every partial sum of rows 0..M-1 (all 8 K-slices, all 512
+// columns) and only then reads exactly those, so stale rows are never observed.  Two
+// calls whose kernels can overlap on the GPU (different streams, no ordering between
+// them) race on the array and corrupt each other's result: order them on one stream or
+// with events.
+// =====================================================================================
+static __device__ __align__(256) float g_noalloc_fc_scratch[FC1_SPLITS * B2P_NOALLOC_MAX_BATCH * FC1_N];
+
+namespace {
+// In host code the array's name is only a stand-in for the symbol, not a device address.
+// The address valid on a given GPU is obtained once, with that GPU current, and cached.
+constexpr int kMaxNoallocDevices = 64;
+float* g_noalloc_ptr[kMaxNoallocDevices] = {};
+std::atomic<bool> g_noalloc_ready[kMaxNoallocDevices];
+
+int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B2P_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxNoallocDevices) return fail(B2P_ELIMIT, "device ordinal %d not supported", dev);
+  if (!g_noalloc_ready[dev].load(std::memory_order_acquire)) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_fc_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(B2P_ECUDA, "cudaGetSymbolAddress(g_noalloc_fc_scratch) on device %d failed: %s", dev,
+                  cudaGetErrorString(e));
+    g_noalloc_ptr[dev] = p;     // racing first calls compute the same address
+    g_noalloc_ready[dev].store(true, std::memory_order_release);
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* fc1_weight_dev,
+                                               const float* fc1_bias_dev, const float* fc2_weight_dev,
+                                               const float* fc2_bias_dev, float* out_dev, int64_t batch,
+                                               void* stream) {
+  if (!x_dev || !fc1_weight_dev || !fc1_bias_dev || !fc2_weight_dev || !fc2_bias_dev || !out_dev)
+    return fail(B2P_EINVAL, "null argument");
+  if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  if (batch > B2P_NOALLOC_MAX_BATCH)
+    return fail(B2P_ELIMIT,
+                "batch %lld exceeds the fixed scratch of the allocation-free entry point (at most %d rows per "
+                "call); split the batch or use b2p_stage_forward",
+                (long long)batch, B2P_NOALLOC_MAX_BATCH);
+  float* scratch = nullptr;
+  B2P_TRY(noalloc_scratch_for_current_device(&scratch));   // first call on a GPU: one-time set-up
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  dim3 grid(FC1_N / 64, ceil_div(batch, 64), FC1_SPLITS);
+  B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, x_dev, fc1_weight_dev, scratch, (int)batch, FC1_K / FC1_SPLITS);
+  B2P_LAUNCH(fc_tail_f32, (int)batch, 128, 0, s, scratch, FC1_SPLITS, (int)batch, fc1_bias_dev, fc2_weight_dev,
+             fc2_bias_dev, out_dev);
+  return 0;
+}

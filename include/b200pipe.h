@@ -142,6 +142,30 @@ B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
                              int64_t batch, int64_t seq, void* stream);
 
+/* ---- allocation-free variant (no counterpart in the reference) ----------------
+ * Same arithmetic as b2p_stage_forward on a B2P_CIFAR_PART1 stage (fc1+ReLU, fc2,
+ * softmax; fp32), for hosts that cannot let a library allocate device memory: a
+ * serving thread that must never meet the device-wide synchronisation cudaMalloc and
+ * cudaFree imply, or a process that gave all device memory to its own pool at
+ * start-up.  The call allocates nothing and frees nothing.  The caller passes every
+ * buffer, weights included, as device pointers on the CURRENT device:
+ *   x [batch,4096], fc1_weight [512,4096], fc1_bias [512], fc2_weight [10,512],
+ *   fc2_bias [10]  ->  out [batch,10] (probabilities).
+ * The fc1 split-K partial sums go to a fixed 4 MiB array inside the library image
+ * (held by every GPU that loads the library, until exit), so
+ *   - batch is limited to B2P_NOALLOC_MAX_BATCH rows; larger returns B2P_ELIMIT;
+ *   - all calls on a GPU share that array: calls that may overlap on the GPU
+ *     (unordered streams) race and must be ordered by the caller; stale contents
+ *     from an earlier call are harmless (every value read is first rewritten);
+ *   - the first call on each GPU looks the array's device address up once
+ *     (cudaGetSymbolAddress); make that first call before starting any stream
+ *     capture on that GPU. */
+#define B2P_NOALLOC_MAX_BATCH 256
+B2P_API int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* fc1_weight_dev,
+                                            const float* fc1_bias_dev, const float* fc2_weight_dev,
+                                            const float* fc2_bias_dev, float* out_dev,
+                                            int64_t batch, void* stream);
+
 /* ---- activation handoff (replaces node.py:73-89 / :170-181) ------------------
  * A ring is a set of `slots` fixed-size receive buffers living on the CONSUMER's
  * GPU plus two 64-bit sequence flags per slot (full / free).  The consumer
