@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "gpt_simt.cuh"
 #include "stage.cuh"
+#include "tc_gemm.cuh"
 
 using namespace b2p;
 
@@ -385,6 +386,17 @@ int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev, int64_t 
     default:
       return gpt_forward(st, in_dev, out_dev, batch, seq, s, nullptr);
   }
+}
+
+int b2p_linear(int operand_kind, const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw,
+               const float* bias_dev, const float* res_dev, int64_t ld_res, void* out_dev, int64_t ldo,
+               int out_bf16, int act, int64_t M, int64_t N, int64_t K, void* stream) {
+  if (!a_dev || !w_dev || !out_dev) return fail(B2P_EINVAL, "null argument");
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return fail(B2P_ELIMIT, "dimension too large");
+  if (act < 0 || act > 2) return fail(B2P_EINVAL, "unknown activation %d", act);
+  tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act};
+  return tc::linear_tc_dispatch(operand_kind, a_dev, lda, w_dev, ldw, ep, (int)M, (int)N, (int)K,
+                                static_cast<cudaStream_t>(stream));
 }
 
 int b2p_stage_check(b2p_stage* st, void* stream) {

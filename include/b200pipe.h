@@ -142,6 +142,22 @@ B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
                              int64_t batch, int64_t seq, void* stream);
 
+/* ---- dense contraction building block (tcgen05 tensor cores) ------------------------
+ *   out[m,n] = act( sum_k A[m,k] * W[n,k] + bias[n] ) + res[m,n]
+ * i.e. every nn.Linear call site on the path (cifar_model_parts.py:13-14,55-56; the
+ * c_attn / c_proj / c_fc / lm_head linears of the block the reference imports at
+ * partitions/gpt_model_parts.py:4).  A [M,K] and W [N,K] are row-major with K contiguous
+ * (nn.Linear's own [out,in] weight layout), row pitches lda/ldw in elements.
+ *   operand_kind 0: A and W are bf16;  1: A and W are fp32, multiplied as tf32.
+ *   bias [N] fp32 or NULL; res [M,ld_res] fp32 or NULL (added after the activation);
+ *   act 0 none, 1 ReLU, 2 exact-erf GELU; out [M,ldo] fp32 (out_bf16=0) or bf16 (=1).
+ * Accumulation is fp32 in tensor memory.  Pointers 16-byte aligned, lda/ldw multiples
+ * of 16 bytes.  Used by the stages in the tensor-core math modes; exported because it
+ * is also the unit the parity tests exercise directly. */
+B2P_API int b2p_linear(int operand_kind, const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw,
+                       const float* bias_dev, const float* res_dev, int64_t ld_res, void* out_dev,
+                       int64_t ldo, int out_bf16, int act, int64_t M, int64_t N, int64_t K, void* stream);
+
 /* ---- allocation-free variant (no counterpart in the reference) ----------------
  * Same arithmetic as b2p_stage_forward on a B2P_CIFAR_PART1 stage (fc1+ReLU, fc2,
  * softmax; fp32), for hosts that cannot let a library allocate device memory: a

@@ -1,0 +1,126 @@
+"""b2p_linear (tcgen05/TMEM/TMA GEMM) through the C ABI against a float64 reference.
+
+Layout bugs (swizzle / descriptor / TMEM lane mapping) give O(1) errors, so two kinds of
+check are used: (a) small-integer operands, where every product and partial sum is
+exactly representable -> results must be bit-exact in both operand kinds; (b) random
+operands against float64 on the same (bf16-rounded) inputs with a tolerance that only
+leaves room for fp32 accumulation order (bf16) or the tf32 input rounding (tf32)."""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _linear(engine, kind, a, w, bias=None, res=None, act=0, out_bf16=False):
+    M, K = a.shape
+    N = w.shape[0]
+    out = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16 if out_bf16 else torch.float32)
+    p = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+    stream = torch.cuda.current_stream(torch.device(DEV)).cuda_stream
+    rc = engine._lib.lib().b2p_linear(kind, p(a), a.stride(0), p(w), w.stride(0), p(bias), p(res),
+                                      res.stride(0) if res is not None else 0, p(out), out.stride(0),
+                                      int(out_bf16), act, M, N, K, C.c_void_p(stream))
+    assert rc == 0, engine._lib.lib().b2p_last_error()
+    torch.cuda.synchronize()
+    return out
+
+
+def _ref(a, w, bias, res, act):
+    y = a.double() @ w.double().t()
+    if bias is not None:
+        y = y + bias.double()
+    if act == 1:
+        y = torch.relu(y)
+    elif act == 2:
+        y = torch.nn.functional.gelu(y)
+    if res is not None:
+        y = y + res.double()
+    return y
+
+
+SHAPES = [(128, 128, 64), (128, 128, 512), (256, 384, 256), (200, 136, 72), (1, 10, 64), (130, 1001, 768),
+          (2048, 3072, 768), (128, 512, 4096)]
+
+
+@pytest.mark.parametrize("kind", [0, 1])
+@pytest.mark.parametrize("shape", SHAPES)
+def test_exact_on_small_integers(cuda_engine, kind, shape):
+    M, N, K = shape
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K)
+    dt = torch.bfloat16 if kind == 0 else torch.float32
+    a = torch.randint(-2, 3, (M, K), generator=g).to(dt).to(DEV)
+    w = torch.randint(-2, 3, (N, K), generator=g).to(dt).to(DEV)
+    bias = torch.randint(-3, 4, (N,), generator=g).float().to(DEV)
+    res = torch.randint(-3, 4, (M, N), generator=g).float().to(DEV)
+    out = _linear(cuda_engine, kind, a, w, bias, res, act=1)
+    want = _ref(a, w, bias, res, 1).float()
+    assert torch.equal(out, want), f"max diff {(out - want).abs().max().item()}"
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("act,use_res,out_bf16", [(0, False, False), (2, False, True), (0, True, False)])
+def test_bf16_random(cuda_engine, shape, act, use_res, out_bf16):
+    M, N, K = shape
+    if out_bf16 and N % 2:
+        pytest.skip("bf16 output needs even N")
+    g = torch.Generator().manual_seed(K + N)
+    a = torch.randn(M, K, generator=g).to(torch.bfloat16).to(DEV)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(torch.bfloat16).to(DEV)
+    bias = torch.randn(N, generator=g).to(DEV)
+    res = torch.randn(M, N, generator=g).to(DEV) if use_res else None
+    out = _linear(cuda_engine, 0, a, w, bias, res, act, out_bf16)
+    want = _ref(a, w, bias, res, act)
+    tol = 2e-2 if out_bf16 else 1e-4
+    assert (out.double() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.parametrize("shape", [(128, 128, 256), (200, 136, 72), (2048, 3072, 768)])
+def test_tf32_random(cuda_engine, shape):
+    M, N, K = shape
+    g = torch.Generator().manual_seed(K)
+    a = torch.randn(M, K, generator=g).to(DEV)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(DEV)
+    out = _linear(cuda_engine, 1, a, w)
+    want = _ref(a, w, None, None, 0)
+    assert (out.double() - want).abs().max().item() <= 2e-2       # tf32 inputs: 2^-10 relative per product
+
+
+def test_strided_operands_and_argument_errors(cuda_engine):
+    L = cuda_engine._lib
+    g = torch.Generator().manual_seed(1)
+    big = torch.randn(256, 1024, generator=g).to(torch.bfloat16).to(DEV)
+    a = big[:, 256:768]                                      # lda = 1024, offset 512 B
+    w = torch.randn(128, 512, generator=g).to(torch.bfloat16).to(DEV)
+    out = _linear(cuda_engine, 0, a, w)
+    assert (out.double() - _ref(a, w, None, None, 0)).abs().max().item() <= 1e-3
+    bad = big[:, 1:513]                                      # 2-byte offset: not 16-byte aligned
+    o = torch.empty(256, 128, device=DEV)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    rc = L.lib().b2p_linear(0, p(bad), 1024, p(w), 512, None, None, 0, p(o), 128, 0, 0, 256, 128, 512, None)
+    assert rc == L.EINVAL and b"16-byte" in L.lib().b2p_last_error()
+    assert L.lib().b2p_linear(7, p(a), 1024, p(w), 512, None, None, 0, p(o), 128, 0, 0, 256, 128, 512, None) == L.EINVAL
+
+
+def test_throughput_report(cuda_engine):
+    """Not an assertion on speed -- prints achieved TFLOP/s for the GPT shapes (pytest -s)."""
+    for (M, N, K) in [(4096, 4096, 4096), (2048, 3072, 1024), (2048, 1024, 4096), (2048, 50304, 1024)]:
+        a = torch.randn(M, K, device=DEV).to(torch.bfloat16)
+        w = torch.randn(N, K, device=DEV).to(torch.bfloat16)
+        out = torch.empty(M, N, device=DEV)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        s = torch.cuda.current_stream().cuda_stream
+        run = lambda: cuda_engine._lib.lib().b2p_linear(0, p(a), K, p(w), K, None, None, 0, p(out), N, 0, 0,
+                                                        M, N, K, C.c_void_p(s))
+        for _ in range(3):
+            assert run() == 0
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        print(f"\nlinear bf16 {M}x{N}x{K}: {ms * 1e3:.1f} us  {2 * M * N * K / ms / 1e9:.1f} TFLOP/s")
