@@ -49,9 +49,10 @@ _PROTOTYPES = {
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_stage_forward_argmax": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
-    "b2p_linear": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
-                             C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int64, C.c_int64,
-                             C.c_int64, C.c_void_p]),
+    "b2p_linear": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                             C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int, C.c_int,
+                             C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "b2p_split_tf32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b2p_cifar_part1_forward_noalloc": (C.c_int, [C.c_void_p] * 6 + [C.c_int64, C.c_void_p]),
     "b2p_ring_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_size_t]),
     "b2p_ring_export": (C.c_int, [C.c_void_p, C.c_void_p]),

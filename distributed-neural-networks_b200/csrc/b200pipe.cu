@@ -84,7 +84,9 @@ int declare_weights(b2p_stage* st) {
 }
 
 int alloc_gpt_workspace(b2p_stage* st) {
-  B2P_CUDA(cudaFuncSetAttribute(attention_causal_f32, cudaFuncAttributeMaxDynamicSharedMemorySize,
+  B2P_CUDA(cudaFuncSetAttribute(attention_causal_f32<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(AttnSmem)));
+  B2P_CUDA(cudaFuncSetAttribute(attention_causal_f32<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)sizeof(AttnSmem)));
   const size_t M = (size_t)st->d.max_tokens, C = (size_t)st->d.n_embd;
   B2P_TRY(dev_alloc(&st->ws_ln, M * C));
@@ -115,8 +117,16 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
 constexpr int FC1_SPLITS = 8;
 int fc1_splits(int64_t) { return FC1_SPLITS; }
 
+// Tensor-core modes use more, shorter K slices: the 128x512 fc1 output is only 4 tiles,
+// so the K dimension is what spreads the 8.4 MB weight read over the SMs.
+constexpr int FC1_SPLITS_TC = 16;
+
+int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
+                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits = 1, int64_t split_stride = 0);
+
 int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
-  const int splits = fc1_splits(batch);
+  const bool tcm = st->d.math != B2P_MATH_FP32;
+  const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);
   const size_t need = (size_t)splits * batch * FC1_N * sizeof(float);
   if (need > st->fc_ws_bytes) {
     // grow the split-K scratch; synchronous, happens only when a larger batch shows up
@@ -126,8 +136,13 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     B2P_CUDA(cudaMalloc((void**)&st->fc_ws, need));
     st->fc_ws_bytes = need;
   }
-  dim3 grid(FC1_N / 64, ceil_div(batch, 64), splits);
-  B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, in, st->dev(0), st->fc_ws, (int)batch, FC1_K / splits);
+  if (tcm) {
+    B2P_TRY(stage_linear(st, EPI_NONE, in, 0, -1, nullptr, st->fc_ws, false, (int)batch, FC1_N, FC1_K, s, splits,
+                         (int64_t)batch * FC1_N));
+  } else {
+    dim3 grid(FC1_N / 64, ceil_div(batch, 64), splits);
+    B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, in, st->dev(0), st->fc_ws, (int)batch, FC1_K / splits);
+  }
   B2P_LAUNCH(fc_tail_f32, (int)batch, 128, 0, s, st->fc_ws, splits, (int)batch, st->dev(1),
              st->dev(2), st->dev(3), out);
   return 0;
@@ -146,30 +161,85 @@ int linear(int epi, const float* A, const float* W, const float* bias, const flo
   return 0;
 }
 
-int layernorm(const float* x, const float* g, const float* b, float* y, int M, int C, cudaStream_t s) {
-  B2P_LAUNCH(layernorm_rows<float>, ceil_div((int64_t)M * 32, 256), 256, 0, s, x, g, b, y, M, C);
+int elementwise_grid(size_t n) { return (int)std::min<size_t>((n + 255) / 256, 148 * 8); }
+
+// hi | lo planes of an fp32 activation for the 3xTF32 contraction (grows on demand)
+int split_activation(b2p_stage* st, const float* A, size_t n, cudaStream_t s) {
+  if (n > st->ws_split_elems) {
+    if (st->ws_split) B2P_CUDA(cudaFree(st->ws_split));
+    st->ws_split = nullptr;
+    st->ws_split_elems = 0;
+    B2P_CUDA(cudaMalloc((void**)&st->ws_split, 2 * n * sizeof(float)));
+    st->ws_split_elems = n;
+  }
+  B2P_LAUNCH(split_tf32, elementwise_grid(n), 256, 0, s, A, st->ws_split, st->ws_split + st->ws_split_elems, n);
+  return 0;
+}
+
+// One nn.Linear call site in the stage's math mode.  A is fp32 except in BF16 mode,
+// where the producer wrote it as bf16; `out` is fp32 unless out_bf16.
+int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
+                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits, int64_t split_stride) {
+  const float* bias = st->dev(bidx);
+  const b2p_weight& w = st->w[widx];
+  tc::EpiParams ep{bias, res, out, N, N, out_bf16 ? 1 : 0, act, split_stride};
+  int rc = 0;
+  switch (st->d.math) {
+    case B2P_MATH_FP32:
+      return linear(act, static_cast<const float*>(A), w.dev, bias, res, static_cast<float*>(out), M, N, K, s);
+    case B2P_MATH_TF32:
+      rc = tc::linear_tc_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, 0, s);
+      break;
+    case B2P_MATH_TF32X3:
+      B2P_TRY(split_activation(st, static_cast<const float*>(A), (size_t)M * K, s));
+      rc = tc::linear_tc_dispatch(2, st->ws_split, st->ws_split + st->ws_split_elems, K, w.packed, w.packed_lo, K,
+                                  ep, M, N, K, splits, 0, s);
+      break;
+    case B2P_MATH_BF16:
+      rc = tc::linear_tc_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, 0, s);
+      break;
+    default:
+      return fail(B2P_EINVAL, "unknown math mode %d", st->d.math);
+  }
+  return rc < 0 ? rc : 0;
+}
+
+int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int C, cudaStream_t s) {
+  const int grid = ceil_div((int64_t)M * 32, 256);
+  if (st->d.math == B2P_MATH_BF16)
+    B2P_LAUNCH(layernorm_rows<__nv_bfloat16>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi),
+               static_cast<__nv_bfloat16*>(y), M, C);
+  else
+    B2P_LAUNCH(layernorm_rows<float>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi), static_cast<float*>(y), M, C);
   return 0;
 }
 
 // Runs this stage's blocks.  `x` is the stage input (never written); the result of
 // the last block lands in `final_out` (caller-provided) -- intermediates ping-pong
-// between the two workspace activations.
+// between the two workspace activations.  The residual stream stays fp32 in every
+// math mode; in BF16 mode the GEMM A operands (LN output, attention output, GELU
+// output) are written as bf16 by their producers.
 int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s) {
   const int C = st->d.n_embd, H = st->d.n_head, M = B * T;
+  const bool bf = st->d.math == B2P_MATH_BF16;
   const float* cur = x;
   const size_t nb = st->blocks.size();
   for (size_t i = 0; i < nb; ++i) {
     const b2p_gpt_block& k = st->blocks[i];
     float* x1 = st->ws_x[0];
     float* x2 = (i + 1 == nb) ? final_out : st->ws_x[1];
-    B2P_TRY(layernorm(cur, st->dev(k.ln1_w), st->dev(k.ln1_b), st->ws_ln, M, C, s));
-    B2P_TRY(linear(EPI_NONE, st->ws_ln, st->dev(k.attn_w), st->dev(k.attn_b), nullptr, st->ws_qkv, M, 3 * C, C, s));
+    B2P_TRY(layernorm(st, cur, k.ln1_w, k.ln1_b, st->ws_ln, M, C, s));
+    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, k.attn_w, k.attn_b, nullptr, st->ws_qkv, false, M, 3 * C, C, s));
     dim3 agrid(ceil_div(T, 64), H, B);
-    B2P_LAUNCH(attention_causal_f32, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv, st->ws_att, T, C);
-    B2P_TRY(linear(EPI_NONE, st->ws_att, st->dev(k.proj_w), st->dev(k.proj_b), cur, x1, M, C, C, s));
-    B2P_TRY(layernorm(x1, st->dev(k.ln2_w), st->dev(k.ln2_b), st->ws_ln, M, C, s));
-    B2P_TRY(linear(EPI_GELU, st->ws_ln, st->dev(k.fc_w), st->dev(k.fc_b), nullptr, st->ws_h, M, 4 * C, C, s));
-    B2P_TRY(linear(EPI_NONE, st->ws_h, st->dev(k.fc2_w), st->dev(k.fc2_b), x1, x2, M, C, 4 * C, s));
+    if (bf)
+      B2P_LAUNCH(attention_causal_f32<__nv_bfloat16>, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv,
+                 reinterpret_cast<__nv_bfloat16*>(st->ws_att), T, C);
+    else
+      B2P_LAUNCH(attention_causal_f32<float>, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv, st->ws_att, T, C);
+    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_att, k.proj_w, k.proj_b, cur, x1, false, M, C, C, s));
+    B2P_TRY(layernorm(st, x1, k.ln2_w, k.ln2_b, st->ws_ln, M, C, s));
+    B2P_TRY(stage_linear(st, EPI_GELU, st->ws_ln, k.fc_w, k.fc_b, nullptr, st->ws_h, bf, M, 4 * C, C, s));
+    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_h, k.fc2_w, k.fc2_b, x1, x2, false, M, C, 4 * C, s));
     cur = x2;
   }
   if (nb == 0 && final_out != x)
@@ -210,9 +280,8 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
     B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s));          // ws_att is free after the last block's proj
     hx = st->ws_att;
   }
-  B2P_TRY(layernorm(hx, st->dev(st->lnf_w), st->dev(st->lnf_b), st->ws_ln, M, C, s));
-  if (!ids_out)
-    return linear(EPI_NONE, st->ws_ln, st->dev(st->head), nullptr, nullptr, static_cast<float*>(out), M, V, C, s);
+  B2P_TRY(layernorm(st, hx, st->lnf_w, st->lnf_b, st->ws_ln, M, C, s));
+  if (!ids_out) return stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, out, false, M, V, C, s);
   // greedy ids: logits in row chunks through a bounded scratch buffer, then row arg-max
   const size_t chunk = std::min<size_t>((size_t)M, 2048);
   if (st->ws_logits_rows < chunk) {
@@ -224,7 +293,9 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
   }
   for (size_t m0 = 0; m0 < (size_t)M; m0 += chunk) {
     const int rows = (int)std::min(chunk, (size_t)M - m0);
-    B2P_TRY(linear(EPI_NONE, st->ws_ln + m0 * C, st->dev(st->head), nullptr, nullptr, st->ws_logits, rows, V, C, s));
+    const char* a_rows = reinterpret_cast<const char*>(st->ws_ln) +
+                         m0 * C * (st->d.math == B2P_MATH_BF16 ? sizeof(__nv_bfloat16) : sizeof(float));
+    B2P_TRY(stage_linear(st, EPI_NONE, a_rows, st->head, -1, nullptr, st->ws_logits, false, rows, V, C, s));
     B2P_LAUNCH(argmax_rows, rows, 256, 0, s, st->ws_logits, ids_out + m0, V, (int64_t)V);
   }
   return 0;
@@ -252,8 +323,9 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
   if (!out || !desc) return fail(B2P_EINVAL, "null argument");
   *out = nullptr;
   if (!is_cifar(desc->kind) && !is_gpt(desc->kind)) return fail(B2P_EINVAL, "unknown stage kind %d", desc->kind);
-  if (desc->math != B2P_MATH_FP32)
-    return fail(B2P_EINVAL, "math mode %d is not available in this build for kind %d", desc->math, desc->kind);
+  if (desc->math < B2P_MATH_FP32 || desc->math > B2P_MATH_BF16) return fail(B2P_EINVAL, "unknown math mode %d", desc->math);
+  if (is_cifar(desc->kind) && desc->math == B2P_MATH_BF16)
+    return fail(B2P_EINVAL, "the CIFAR parts compute in fp32, tf32x3 or tf32 (the reference is fp32); bf16 is a GPT mode");
   if (is_gpt(desc->kind)) {
     if (desc->n_embd <= 0 || desc->n_embd % 128 || desc->n_embd > 2048)
       return fail(B2P_EINVAL, "n_embd=%d must be a positive multiple of 128, at most 2048", desc->n_embd);
@@ -297,7 +369,8 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
 int b2p_stage_destroy(b2p_stage* st) {
   if (!st) return 0;
   DeviceGuard g(st->d.device);
-  for (auto& w : st->w) cudaFree(w.dev);
+  for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
+  cudaFree(st->ws_split);
   cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
@@ -355,6 +428,23 @@ int b2p_stage_finalize(b2p_stage* st) {
     B2P_LAUNCH(transpose2d_f32, ceil_div(32 * 27, 256), 256, 0, 0, st->dev(0), st->w1t, 32, 27);
     B2P_LAUNCH(transpose2d_f32, ceil_div(64 * 288, 256), 256, 0, 0, st->dev(2), st->w2t, 64, 288);
   }
+  // math-mode copies of the matrices that feed the tensor cores
+  for (auto& w : st->w) {
+    if (!w.loaded || w.shape.size() != 2) continue;
+    const bool gemm_operand = is_gpt(st->d.kind) ? (w.name.find("wpe") == std::string::npos &&
+                                                   (st->d.kind != B2P_GPT_FIRST || w.name.find("wte") == std::string::npos))
+                                                 : w.name == "fc1.weight";
+    if (!gemm_operand) continue;
+    const size_t n = w.elems();
+    if (st->d.math == B2P_MATH_BF16) {
+      if (!w.packed) B2P_CUDA(cudaMalloc(&w.packed, n * sizeof(__nv_bfloat16)));
+      B2P_LAUNCH(f32_to_bf16, elementwise_grid(n), 256, 0, 0, w.dev, static_cast<__nv_bfloat16*>(w.packed), n);
+    } else if (st->d.math == B2P_MATH_TF32X3) {
+      if (!w.packed) B2P_CUDA(cudaMalloc(&w.packed, n * sizeof(float)));
+      if (!w.packed_lo) B2P_CUDA(cudaMalloc((void**)&w.packed_lo, n * sizeof(float)));
+      B2P_LAUNCH(split_tf32, elementwise_grid(n), 256, 0, 0, w.dev, static_cast<float*>(w.packed), w.packed_lo, n);
+    }
+  }
   B2P_CUDA(cudaDeviceSynchronize());
   st->finalized = true;
   return 0;
@@ -388,15 +478,25 @@ int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev, int64_t 
   }
 }
 
-int b2p_linear(int operand_kind, const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw,
-               const float* bias_dev, const float* res_dev, int64_t ld_res, void* out_dev, int64_t ldo,
-               int out_bf16, int act, int64_t M, int64_t N, int64_t K, void* stream) {
+int b2p_split_tf32(const float* x_dev, float* hi_dev, float* lo_dev, int64_t n, void* stream) {
+  if (!x_dev || !hi_dev || !lo_dev || n < 0) return fail(B2P_EINVAL, "bad argument");
+  if (n == 0) return 0;
+  B2P_LAUNCH(split_tf32, elementwise_grid((size_t)n), 256, 0, static_cast<cudaStream_t>(stream), x_dev, hi_dev, lo_dev,
+             (size_t)n);
+  return 0;
+}
+
+int b2p_linear(int operand_kind, const void* a_dev, const void* a_lo_dev, int64_t lda, const void* w_dev,
+               const void* w_lo_dev, int64_t ldw, const float* bias_dev, const float* res_dev, int64_t ld_res,
+               void* out_dev, int64_t ldo, int out_bf16, int act, int64_t M, int64_t N, int64_t K, void* stream) {
   if (!a_dev || !w_dev || !out_dev) return fail(B2P_EINVAL, "null argument");
   if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return fail(B2P_ELIMIT, "dimension too large");
   if (act < 0 || act > 2) return fail(B2P_EINVAL, "unknown activation %d", act);
-  tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act};
-  return tc::linear_tc_dispatch(operand_kind, a_dev, lda, w_dev, ldw, ep, (int)M, (int)N, (int)K,
-                                static_cast<cudaStream_t>(stream));
+  tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act, 0};
+  const int tile_n = (operand_kind >> 8) & 0xfff;       // test hook: force the tile width (0 = pick)
+  int rc = tc::linear_tc_dispatch(operand_kind & 0xff, a_dev, a_lo_dev, lda, w_dev, w_lo_dev, ldw, ep, (int)M, (int)N,
+                                  (int)K, 1, tile_n, static_cast<cudaStream_t>(stream));
+  return rc < 0 ? rc : 0;
 }
 
 int b2p_stage_check(b2p_stage* st, void* stream) {

@@ -5,6 +5,8 @@
 // the reference imports at partitions/gpt_model_parts.py:4; semantics pinned in
 // oracle/gpt_model.py).
 #pragma once
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace b2p {
@@ -44,6 +46,42 @@ __device__ __forceinline__ void store4(OutT* p, float a, float b, float c, float
 template <>
 __device__ __forceinline__ void store4<float>(float* p, float a, float b, float c, float d) {
   *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+}
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, float a, float b, float c, float d) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  uint2 v;
+  v.x = *reinterpret_cast<uint32_t*>(&lo);
+  v.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = v;
+}
+__device__ __forceinline__ void store1(float* p, float v) { *p = v; }
+__device__ __forceinline__ void store1(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+
+// fp32 -> bf16 copy (weights at finalize time)
+__global__ void __launch_bounds__(256)
+f32_to_bf16(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// x = hi + lo with hi, lo exactly representable in tf32 (10-bit mantissa): the operand
+// planes of the 3xTF32 contraction.  |x - hi - lo| <= 2^-22 |x|.
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__global__ void __launch_bounds__(256)
+split_tf32(const float* __restrict__ in, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const float x = in[i], h = round_tf32(x);
+    hi[i] = h;
+    lo[i] = round_tf32(x - h);
+  }
 }
 
 template <typename OutT>
@@ -154,8 +192,9 @@ struct AttnSmem {
   float P[64][64 + 1];     // [query][key]
 };
 
+template <typename OutT>
 __global__ void __launch_bounds__(256)
-attention_causal_f32(const float* __restrict__ qkv, float* __restrict__ y, int T, int C) {
+attention_causal_f32(const float* __restrict__ qkv, OutT* __restrict__ y, int T, int C) {
   extern __shared__ __align__(16) unsigned char attn_smem_raw[];
   AttnSmem& sm = *reinterpret_cast<AttnSmem*>(attn_smem_raw);
   float (*Qs)[65] = sm.Q;
@@ -253,9 +292,9 @@ attention_causal_f32(const float* __restrict__ qkv, float* __restrict__ y, int T
   for (int i = 0; i < 4; ++i) {
     const int qi = q0 + ty * 4 + i;
     if (qi >= T) continue;
-    float* yr = y + ((size_t)b * T + qi) * C + h * 64;
+    OutT* yr = y + ((size_t)b * T + qi) * C + h * 64;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) yr[tx + 16 * j] = o[i][j] / lrow[i];
+    for (int j = 0; j < 4; ++j) store1(yr + tx + 16 * j, o[i][j] / lrow[i]);
   }
 }
 

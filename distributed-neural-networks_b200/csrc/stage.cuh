@@ -12,6 +12,8 @@ struct b2p_weight {
   bool required = true;
   bool loaded = false;
   float* dev = nullptr;             // fp32 copy in the original layout
+  void* packed = nullptr;           // math-mode copy: bf16 (BF16) or tf32 hi plane (TF32X3)
+  float* packed_lo = nullptr;       // TF32X3: lo plane
   size_t elems() const {
     size_t n = 1;
     for (auto d : shape) n *= (size_t)d;
@@ -40,6 +42,8 @@ struct b2p_stage {
   int wte = -1, wpe = -1, lnf_w = -1, lnf_b = -1, head = -1;
   float *ws_ln = nullptr, *ws_qkv = nullptr, *ws_att = nullptr, *ws_h = nullptr;
   float *ws_x[2] = {nullptr, nullptr};
+  float* ws_split = nullptr;        // TF32X3: hi | lo planes of the current GEMM's A operand
+  size_t ws_split_elems = 0;        // elements per plane
   float* ws_logits = nullptr;       // forward_argmax chunk buffer
   size_t ws_logits_rows = 0;
   int* bad_flag = nullptr;          // device flag: out-of-range token id seen

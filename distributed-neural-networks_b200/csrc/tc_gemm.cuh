@@ -19,7 +19,11 @@
 // Ragged M, N and K need no masks on the load side: TMA zero-fills out-of-bounds box
 // elements; stores are guarded.
 //
-// KIND 0: bf16 operands (kind::f16), KIND 1: fp32 storage read as tf32 (kind::tf32).
+// KIND 0: bf16 operands (kind::f16), KIND 1: fp32 storage read as tf32 (kind::tf32),
+// KIND 2: "3xTF32" -- each fp32 operand is given as two tf32-exact planes hi + lo
+//         (x = hi + lo up to 2^-22 relative) and every K step issues three MMAs
+//         lo*hi + hi*lo + hi*hi into the same fp32 accumulator: fp32-grade products on the
+//         tensor cores (the engine's tensor-core parity mode).
 #pragma once
 #include <cuda_bf16.h>
 
@@ -170,19 +174,23 @@ struct EpiParams {
   int64_t ldo, ld_res;
   int out_bf16;
   int act;
+  int64_t split_stride;  // split-K: elements between the partial outputs of consecutive K slices
 };
 
 template <int KIND, int BN>
 struct GemmCfg {
   static constexpr int BM = 128;
+  static constexpr bool SPLIT = KIND == 2;     // hi/lo planes
   static constexpr int ELEM = KIND == 0 ? 2 : 4;
   static constexpr int BK = 128 / ELEM;        // one 128-byte swizzle row of K per stage
   static constexpr int UMMA_K = 32 / ELEM;     // 16 (bf16) or 8 (tf32)
-  static constexpr int A_BYTES = BM * 128;
-  static constexpr int B_BYTES = BN * 128;
+  static constexpr int A_PLANE = BM * 128, B_PLANE = BN * 128;
+  static constexpr int A_BYTES = A_PLANE * (SPLIT ? 2 : 1);
+  static constexpr int B_BYTES = B_PLANE * (SPLIT ? 2 : 1);
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN <= 128 ? 5 : 4;
-  static constexpr int EPI_BYTES = 4 * 32 * 33 * 4;
+  static constexpr int STAGES = SPLIT ? (BN <= 128 ? 3 : 2) : (BN <= 128 ? 5 : 4);
+  static constexpr int EPI_PITCH = 36;       // floats; 16-byte aligned rows, conflict-free float4 stores
+  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
   static constexpr int BAR_BYTES = 256;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
   static constexpr int TMEM_COLS = 2 * BN;     // two accumulator stages (power of two >= 32)
@@ -192,7 +200,8 @@ struct GemmCfg {
 template <int KIND, int BN>
 __global__ void __launch_bounds__(192, 1)
 linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-          EpiParams ep, int M, int N, int K) {
+          const __grid_constant__ CUtensorMap tmap_a_lo, const __grid_constant__ CUtensorMap tmap_w_lo,
+          EpiParams ep, int M, int N, int K, int splits, int kb_per_split) {
   using Cfg = GemmCfg<KIND, BN>;
   extern __shared__ unsigned char smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte alignment (the XOR pattern is a function of the address)
@@ -209,8 +218,8 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (M + Cfg::BM - 1) / Cfg::BM, tiles_n = (N + BN - 1) / BN;
-  const int num_tiles = tiles_m * tiles_n;
-  const int num_kb = (K + Cfg::BK - 1) / Cfg::BK;
+  const int num_tiles = tiles_m * tiles_n * splits;        // work items: (output tile, K slice)
+  const int total_kb = (K + Cfg::BK - 1) / Cfg::BK;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_a)) : "memory");
@@ -231,15 +240,21 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   if (warp == 0) {
     // ===================== TMA producer =====================
     uint32_t stage = 0, phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
+      const int z = item % splits, tile = item / splits;
       const int m0 = (tile % tiles_m) * Cfg::BM, n0 = (tile / tiles_m) * BN;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const int kb0 = z * kb_per_split, kb1 = min(total_kb, kb0 + kb_per_split);
+      for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1);
         if (lane == 0) {
           unsigned char* sa = tiles + stage * Cfg::STAGE_BYTES;
           mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
           tma_load_2d(sa, &tmap_a, &full[stage], kb * Cfg::BK, m0);
           tma_load_2d(sa + Cfg::A_BYTES, &tmap_w, &full[stage], kb * Cfg::BK, n0);
+          if (Cfg::SPLIT) {
+            tma_load_2d(sa + Cfg::A_PLANE, &tmap_a_lo, &full[stage], kb * Cfg::BK, m0);
+            tma_load_2d(sa + Cfg::A_BYTES + Cfg::B_PLANE, &tmap_w_lo, &full[stage], kb * Cfg::BK, n0);
+          }
         }
         __syncwarp();
         if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -249,7 +264,9 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = make_idesc(KIND, Cfg::BM, BN);
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
+      const int z = item % splits;
+      const int kb0 = z * kb_per_split, num_kb = min(total_kb, kb0 + kb_per_split) - kb0;
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
@@ -260,8 +277,17 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
           const uint32_t a_addr = smem_u32(tiles + stage * Cfg::STAGE_BYTES);
           const uint64_t da = make_desc_sw128(a_addr), db = make_desc_sw128(a_addr + Cfg::A_BYTES);
 #pragma unroll
-          for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k)   // +32 B along K inside the swizzle row = +2 (>>4)
-            umma<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k) {  // +32 B along K inside the swizzle row = +2 (>>4)
+            if (Cfg::SPLIT) {
+              const uint64_t da_lo = make_desc_sw128(a_addr + Cfg::A_PLANE);
+              const uint64_t db_lo = make_desc_sw128(a_addr + Cfg::A_BYTES + Cfg::B_PLANE);
+              umma<KIND>(tmem_d, da_lo + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);   // small terms first
+              umma<KIND>(tmem_d, da + 2 * k, db_lo + 2 * k, idesc, 1u);
+              umma<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, 1u);
+            } else {
+              umma<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+          }
           umma_commit(&empty[stage]);                        // smem slot free once these MMAs retire
           if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
         }
@@ -272,14 +298,23 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
+    constexpr int P = Cfg::EPI_PITCH;
     const int q = warp & 3;                         // TMEM lane quarter this warp may read
-    float* stg = epi_smem + (warp - 2) * 32 * 33;   // private [32][33] transpose buffer
+    float* stg = epi_smem + (warp - 2) * 32 * P;    // private [32][P] transpose buffer
+    const bool vec_f32 = !ep.out_bf16 && (ep.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
+                         (ep.split_stride & 3) == 0 &&
+                         (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
+    const bool vec_bf16 = ep.out_bf16 && (ep.ldo & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
+                          (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
+    const bool bias_vec = ep.bias && (reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0;
     uint32_t acc = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
+      const int z = item % splits, tile = item / splits;
       const int m0 = (tile % tiles_m) * Cfg::BM, n0 = (tile / tiles_m) * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const int row_base = m0 + q * 32;
+      float* out_f32 = static_cast<float*>(ep.out) + static_cast<int64_t>(z) * ep.split_stride;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         const int col0 = n0 + c * 32;
@@ -287,25 +322,79 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
         uint32_t r[32];
         tmem_ld32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
         tmem_ld_wait();
+        const bool full_cols = col0 + 32 <= N;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float v = __uint_as_float(r[j]);
-          if (ep.bias && col0 + j < N) v += __ldg(ep.bias + col0 + j);
-          if (ep.act == ACT_RELU) v = fmaxf(v, 0.f);
-          else if (ep.act == ACT_GELU) v = gelu_erf(v);
-          stg[lane * 33 + j] = v;
+        for (int j4 = 0; j4 < 8; ++j4) {
+          float v[4] = {__uint_as_float(r[4 * j4]), __uint_as_float(r[4 * j4 + 1]), __uint_as_float(r[4 * j4 + 2]),
+                        __uint_as_float(r[4 * j4 + 3])};
+          if (ep.bias) {
+            if (bias_vec && full_cols) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col0) + j4);
+              v[0] += b4.x; v[1] += b4.y; v[2] += b4.z; v[3] += b4.w;
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (col0 + 4 * j4 + e < N) v[e] += __ldg(ep.bias + col0 + 4 * j4 + e);
+            }
+          }
+          if (ep.act == ACT_RELU) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
+          } else if (ep.act == ACT_GELU) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) v[e] = gelu_erf(v[e]);
+          }
+          *reinterpret_cast<float4*>(&stg[lane * P + 4 * j4]) = make_float4(v[0], v[1], v[2], v[3]);
         }
         __syncwarp();
-        if (!ep.out_bf16) {
-          float* out = static_cast<float*>(ep.out);
+        if (vec_f32 && full_cols) {
+          // 8 lanes x 16 B cover one 128-byte row segment; 4 rows per instruction
+          const int cg = (lane & 7) * 4;
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + (lane >> 3), row = row_base + rr;
+            if (row < M) {
+              float4 v = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+              if (ep.res) {
+                const float4 rv = *reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res + col0 + cg);
+                v.x += rv.x; v.y += rv.y; v.z += rv.z; v.w += rv.w;
+              }
+              *reinterpret_cast<float4*>(out_f32 + static_cast<int64_t>(row) * ep.ldo + col0 + cg) = v;
+            }
+          }
+        } else if (vec_bf16 && full_cols) {
+          // 4 lanes x 16 B (8 bf16) cover one 64-byte row segment; 8 rows per instruction
+          __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
+          const int cg = (lane & 3) * 8;
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int rr = it * 8 + (lane >> 2), row = row_base + rr;
+            if (row < M) {
+              float4 a = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+              float4 b = *reinterpret_cast<const float4*>(&stg[rr * P + cg + 4]);
+              if (ep.res) {
+                const float4* rp = reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res + col0 + cg);
+                const float4 ra = rp[0], rb = rp[1];
+                a.x += ra.x; a.y += ra.y; a.z += ra.z; a.w += ra.w;
+                b.x += rb.x; b.y += rb.y; b.z += rb.z; b.w += rb.w;
+              }
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
+              uint4 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+              pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+              *reinterpret_cast<uint4*>(out + static_cast<int64_t>(row) * ep.ldo + col0 + cg) = pk;
+            }
+          }
+        } else if (!ep.out_bf16) {
           const int col = col0 + lane;
 #pragma unroll 4
           for (int rr = 0; rr < 32; ++rr) {
             const int row = row_base + rr;
             if (row < M && col < N) {
-              float v = stg[rr * 33 + lane];
+              float v = stg[rr * P + lane];
               if (ep.res) v += ep.res[static_cast<int64_t>(row) * ep.ld_res + col];
-              out[static_cast<int64_t>(row) * ep.ldo + col] = v;
+              out_f32[static_cast<int64_t>(row) * ep.ldo + col] = v;
             }
           }
         } else {
@@ -315,7 +404,7 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
           for (int it = 0; it < 16; ++it) {
             const int rr = it * 2 + half, row = row_base + rr;
             if (row < M && col < N) {                // N is even for bf16 outputs (checked on the host)
-              float v0 = stg[rr * 33 + cj], v1 = stg[rr * 33 + cj + 1];
+              float v0 = stg[rr * P + cj], v1 = stg[rr * P + cj + 1];
               if (ep.res) {
                 const float* rp = ep.res + static_cast<int64_t>(row) * ep.ld_res + col;
                 v0 += rp[0]; v1 += rp[1];
@@ -360,6 +449,7 @@ inline EncodeTiledFn encode_tiled_fn() {
 
 // 2-D K-major tensor [rows, k] with row pitch ld (elements); box = [128 bytes of K] x [box_rows].
 inline int make_tmap(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t k, int64_t ld, int box_rows) {
+  if (kind == 2) kind = 1;     // tf32x3 planes are plain fp32 arrays
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail(B2P_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
   const int elem = kind == 0 ? 2 : 4;
@@ -379,8 +469,8 @@ inline int make_tmap(CUtensorMap* map, int kind, const void* ptr, int64_t rows, 
 }
 
 template <int KIND, int BN>
-int launch_linear_tc(const void* A, int64_t lda, const void* W, int64_t ldw, const EpiParams& ep, int M, int N,
-                     int K, int sms, cudaStream_t s) {
+int launch_linear_tc(const void* A, const void* A_lo, int64_t lda, const void* W, const void* W_lo, int64_t ldw,
+                     const EpiParams& ep, int M, int N, int K, int splits, int sms, cudaStream_t s) {
   using Cfg = GemmCfg<KIND, BN>;
   static bool configured[64] = {};
   int dev = 0;
@@ -390,26 +480,57 @@ int launch_linear_tc(const void* A, int64_t lda, const void* W, int64_t ldw, con
                                   Cfg::SMEM_BYTES));
     configured[dev] = true;
   }
-  CUtensorMap ta, tw;
+  CUtensorMap ta, tw, ta_lo, tw_lo;
   B2P_TRY(make_tmap(&ta, KIND, A, M, K, lda, Cfg::BM));
   B2P_TRY(make_tmap(&tw, KIND, W, N, K, ldw, BN));
-  const int num_tiles = ceil_div(M, Cfg::BM) * ceil_div(N, BN);
-  const int grid = std::min(num_tiles, sms);
-  B2P_LAUNCH((linear_tc<KIND, BN>), grid, Cfg::THREADS, Cfg::SMEM_BYTES, s, ta, tw, ep, M, N, K);
-  return 0;
+  if (Cfg::SPLIT) {
+    if (!A_lo || !W_lo) return fail(B2P_EINVAL, "linear: tf32x3 needs the lo planes of both operands");
+    B2P_TRY(make_tmap(&ta_lo, KIND, A_lo, M, K, lda, Cfg::BM));
+    B2P_TRY(make_tmap(&tw_lo, KIND, W_lo, N, K, ldw, BN));
+  } else {
+    ta_lo = ta;
+    tw_lo = tw;
+  }
+  const int total_kb = ceil_div(K, Cfg::BK);
+  splits = std::max(1, std::min(splits, total_kb));
+  const int kb_per_split = ceil_div(total_kb, splits);
+  splits = ceil_div(total_kb, kb_per_split);            // no empty K slice
+  const int items = ceil_div(M, Cfg::BM) * ceil_div(N, BN) * splits;
+  const int grid = std::min(items, sms);
+  B2P_LAUNCH((linear_tc<KIND, BN>), grid, Cfg::THREADS, Cfg::SMEM_BYTES, s, ta, tw, ta_lo, tw_lo, ep, M, N, K, splits,
+             kb_per_split);
+  return splits;
 }
 
-// kind: 0 bf16 operands, 1 fp32 operands multiplied as tf32
-inline int linear_tc_dispatch(int kind, const void* A, int64_t lda, const void* W, int64_t ldw,
-                              const EpiParams& ep, int M, int N, int K, cudaStream_t s) {
+// kind: 0 bf16 operands, 1 fp32 operands multiplied as tf32.  splits > 1: split-K, partial
+// sums of slice z go to out + z*split_stride (fp32, no bias/act/res).  Returns the number of
+// K slices actually used (>= 1) or a negative error.  bn: 0 = pick, else 128 or 256.
+inline int linear_tc_dispatch(int kind, const void* A, const void* A_lo, int64_t lda, const void* W,
+                              const void* W_lo, int64_t ldw, const EpiParams& ep, int M, int N, int K, int splits,
+                              int bn, cudaStream_t s) {
   if (M <= 0 || N <= 0 || K <= 0) return fail(B2P_EINVAL, "linear: M, N, K must be positive");
   if (ep.out_bf16 && ((N & 1) || (ep.ldo & 1))) return fail(B2P_EINVAL, "linear: bf16 output needs even N and ldo");
+  if (splits > 1 && (ep.out_bf16 || ep.bias || ep.res || ep.act))
+    return fail(B2P_EINVAL, "linear: split-K writes raw fp32 partial sums (no bias/activation/residual)");
   int dev = 0, sms = 148;
   B2P_CUDA(cudaGetDevice(&dev));
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (kind == 0) return launch_linear_tc<0, 128>(A, lda, W, ldw, ep, M, N, K, sms, s);
-  if (kind == 1) return launch_linear_tc<1, 128>(A, lda, W, ldw, ep, M, N, K, sms, s);
-  return fail(B2P_EINVAL, "linear: unknown operand kind %d", kind);
+  if (kind == 2) bn = 128;
+  if (bn == 0) {
+    // 256-wide tiles halve the shared-memory traffic per MMA (the BN=128 tile sits exactly at
+    // the 128 B/clk smem limit) but only pay off when they still fill the machine
+    const int64_t tiles256 = (int64_t)ceil_div(M, 128) * ceil_div(N, 256) * std::max(1, splits);
+    bn = (N >= 256 && tiles256 >= sms) ? 256 : 128;
+  }
+#define B2P_TC_CASE(KD, TN) \
+  if (kind == KD && bn == TN) return launch_linear_tc<KD, TN>(A, A_lo, lda, W, W_lo, ldw, ep, M, N, K, splits, sms, s)
+  B2P_TC_CASE(0, 128);
+  B2P_TC_CASE(0, 256);
+  B2P_TC_CASE(1, 128);
+  B2P_TC_CASE(1, 256);
+  B2P_TC_CASE(2, 128);
+#undef B2P_TC_CASE
+  return fail(B2P_EINVAL, "linear: unknown operand kind %d / tile width %d", kind, bn);
 }
 
 }  // namespace tc

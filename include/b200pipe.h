@@ -148,15 +148,21 @@ B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t*
  * c_attn / c_proj / c_fc / lm_head linears of the block the reference imports at
  * partitions/gpt_model_parts.py:4).  A [M,K] and W [N,K] are row-major with K contiguous
  * (nn.Linear's own [out,in] weight layout), row pitches lda/ldw in elements.
- *   operand_kind 0: A and W are bf16;  1: A and W are fp32, multiplied as tf32.
+ *   operand_kind 0: A and W are bf16;  1: A and W are fp32, multiplied as tf32;
+ *                2: "3xTF32": a_dev/w_dev are the tf32-exact hi planes and a_lo_dev/w_lo_dev
+ *                   the lo planes made by b2p_split_tf32 (lo*hi + hi*lo + hi*hi, fp32-grade).
+ *   a_lo_dev / w_lo_dev are ignored (may be NULL) for kinds 0 and 1.
  *   bias [N] fp32 or NULL; res [M,ld_res] fp32 or NULL (added after the activation);
  *   act 0 none, 1 ReLU, 2 exact-erf GELU; out [M,ldo] fp32 (out_bf16=0) or bf16 (=1).
  * Accumulation is fp32 in tensor memory.  Pointers 16-byte aligned, lda/ldw multiples
  * of 16 bytes.  Used by the stages in the tensor-core math modes; exported because it
  * is also the unit the parity tests exercise directly. */
-B2P_API int b2p_linear(int operand_kind, const void* a_dev, int64_t lda, const void* w_dev, int64_t ldw,
-                       const float* bias_dev, const float* res_dev, int64_t ld_res, void* out_dev,
-                       int64_t ldo, int out_bf16, int act, int64_t M, int64_t N, int64_t K, void* stream);
+B2P_API int b2p_linear(int operand_kind, const void* a_dev, const void* a_lo_dev, int64_t lda,
+                       const void* w_dev, const void* w_lo_dev, int64_t ldw, const float* bias_dev,
+                       const float* res_dev, int64_t ld_res, void* out_dev, int64_t ldo, int out_bf16,
+                       int act, int64_t M, int64_t N, int64_t K, void* stream);
+/* x = hi + lo, both exactly representable in tf32 (|x-hi-lo| <= 2^-22 |x|); n elements. */
+B2P_API int b2p_split_tf32(const float* x_dev, float* hi_dev, float* lo_dev, int64_t n, void* stream);
 
 /* ---- allocation-free variant (no counterpart in the reference) ----------------
  * Same arithmetic as b2p_stage_forward on a B2P_CIFAR_PART1 stage (fc1+ReLU, fc2,

@@ -141,3 +141,26 @@ def test_native_library_is_what_ran(cuda_engine, parts):
     assert cuda_engine.launch_count() == before + 1
     maps = open("/proc/self/maps").read()
     assert "libb200pipe.so" in maps
+
+
+@pytest.mark.parametrize("mode,tol", [("tf32x3", PROB_TOL), ("tf32", 2e-3)])
+def test_tensor_core_fc_stage(cuda_engine, mode, tol):
+    """Part 1 with fc1 on the tensor cores (split-K tcgen05 GEMM + the same fused tail).
+    tf32x3 is held to the fp32 probability tolerance; single-pass tf32 to 2e-3."""
+    sd = co.init_state_dict(1234)
+    p1 = cuda_engine.ModelPart1_2Node(cuda_engine.NeuralNetwork(), math=mode).to("cuda:0")
+    p1.load_state_dict(sd, strict=False)
+    p1.eval()
+    for batch in (1, 128, 130, 1024):
+        x = co.part0(co.make_input(batch, seed=300 + batch), sd)
+        with torch.no_grad():
+            probs = p1(x.cuda()).cpu()
+        want = co.part1(x, sd)
+        err = (probs - want).abs().max().item()
+        decided = co.top2_margin(want) > 2 * tol
+        assert err <= tol, f"{mode} batch {batch}: {err}"
+        assert torch.equal(probs.argmax(1)[decided], want.argmax(1)[decided])
+    # micro-batching stays bit-exact on the tensor-core path too (fixed K split)
+    x = co.part0(co.make_input(256, seed=5), sd).cuda()
+    with torch.no_grad():
+        assert torch.equal(p1(x), torch.cat([p1(x[:128]), p1(x[128:])]))

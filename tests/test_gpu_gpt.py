@@ -106,3 +106,47 @@ def test_input_errors(cuda_engine, golden_dir):
     mid = cuda_engine.ModelPartIntermediate(model, 1, 1).to("cuda:0").eval()
     with pytest.raises(RuntimeError):
         mid(torch.zeros(1, 4, dims[4] + 1).cuda())
+
+
+# tensor-core math modes: (mode, logit tolerance).  tf32x3 is the tensor-core PARITY mode and is
+# held to the fp32 tolerance; tf32 and bf16 are throughput modes with the input-rounding error of
+# their operand type (north_star: "logits within a stated fp32/bf16 tolerance").
+TC_MODES = [("tf32x3", 1e-4), ("tf32", 5e-3), ("bf16", 3e-2)]
+
+
+@pytest.mark.parametrize("mode,tol", TC_MODES)
+def test_tensor_core_modes_golden(cuda_engine, golden_dir, mode, tol):
+    g, dims, sd = _golden(golden_dir)
+    model = _engine_model(cuda_engine, dims, sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 3, math=mode)]
+    x = torch.from_numpy(g["idx"]).cuda()
+    with torch.no_grad():
+        for p in parts:
+            x = p(x)
+    want = torch.from_numpy(g["logits"])
+    err = (x.cpu() - want).abs().max().item()
+    top2 = want.topk(2, -1).values
+    gap = top2[..., 0] - top2[..., 1]
+    decided = gap > 2 * tol
+    flips = int((x.argmax(-1).cpu()[decided] != want.argmax(-1)[decided]).sum())
+    print(f"\n{mode}: max|dlogit|={err:.2e}, decided rows {int(decided.sum())}/{decided.numel()}, flips {flips}")
+    assert err <= tol
+    assert flips == 0
+
+
+@pytest.mark.parametrize("mode,tol", TC_MODES)
+def test_tensor_core_modes_ragged(cuda_engine, mode, tol):
+    cfg = gpt_model.GPTConfig(block_size=160, vocab_size=1000, n_layer=2, n_head=4, n_embd=256)
+    sd = gpt_oracle.init_state_dict(cfg, seed=11)
+    idx = gpt_oracle.make_tokens(2, 77, cfg.vocab_size, seed=2)
+    want = gpt_oracle.pipeline(idx, sd, cfg, 2)
+    model = _engine_model(cuda_engine, (160, 1000, 2, 4, 256), sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math=mode)]
+    x = idx.cuda()
+    with torch.no_grad():
+        for p in parts[:-1]:
+            x = p(x)
+        logits = parts[-1](x)
+        ids = parts[-1].greedy_ids(x)
+    assert (logits.cpu() - want).abs().max().item() <= tol
+    assert torch.equal(ids, logits.argmax(-1))
