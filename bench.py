@@ -181,32 +181,34 @@ def engine_arm(args):
     W, K = max(args.warmup, 3), args.steps
     last = pipe.compute[-1]
 
-    # -- (1) device-resident throughput --------------------------------------------------------------
-    for i in range(W):
-        pipe.run_device(dev_pool[i % n_pool])
+    # -- (1) device-resident throughput: one CUDA-graph launch per step ---------------------------------
+    use_graph = not args.no_graph
+    run_dev = pipe.run_device_graph if use_graph else pipe.run_device
+    for i in range(max(W, n_pool if use_graph else 0)):      # warm-up (captures one graph per input buffer)
+        run_dev(dev_pool[i % n_pool])
     pipe.synchronize()
-    launches0 = engine.launch_count()
+    launches0 = engine.launch_count() + pipe.graph_kernel_launches
     sampler.active.set()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     t0.record(pipe.compute[0])
     for i in range(K):
-        pipe.run_device(dev_pool[(W + i) % n_pool])
+        run_dev(dev_pool[(W + i) % n_pool])
     last.wait_stream(pipe.compute[0])
     t1.record(last)
     torch.cuda.synchronize()
     ms_dev = t0.elapsed_time(t1)
-    launches = engine.launch_count() - launches0
+    launches = engine.launch_count() + pipe.graph_kernel_launches - launches0
 
     # -- (2) end to end through the host-facing call ----------------------------------------------------
     for i in range(W):
-        pipe.run_host(host_pool[i % n_pool], sync=False)
+        pipe.run_host(host_pool[i % n_pool], sync=False, graph=use_graph)
     pipe.synchronize()
     torch.cuda.synchronize()
     w0 = time.perf_counter()
     for i in range(K):
-        pipe.run_host(host_pool[(W + i) % n_pool], sync=False)
-    last.synchronize()
+        pipe.run_host(host_pool[(W + i) % n_pool], sync=False, graph=use_graph)
+    pipe.synchronize()
     torch.cuda.synchronize()
     ms_e2e = 1e3 * (time.perf_counter() - w0)
     checksum = float(pipe.out_host.sum())          # a real read of the last step's result
@@ -216,7 +218,7 @@ def engine_arm(args):
     lats = []
     for i in range(20 + 200):
         q0 = time.perf_counter()
-        pipe.run_host(one, sync=True)
+        pipe.run_host(one, sync=True, graph=use_graph)
         if i >= 20:
             lats.append(1e3 * (time.perf_counter() - q0))
 
@@ -248,7 +250,7 @@ def engine_arm(args):
 
     cpu = None
     if not args.no_cpu_baseline:
-        r = time_cpu_pipeline(n_requests=40, warmup=3, budget_s=25.0)
+        r = time_cpu_pipeline(n_requests=600, warmup=5, budget_s=15.0)
         cpu = {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                "p50_request_latency_ms": r["p50_ms"],
                "sample": f"{r['requests']} requests of {r['batch']} samples through the CPU port of the reference's "
@@ -261,6 +263,7 @@ def engine_arm(args):
         "data": "synthetic",
         "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH, "stages": 2,
                    "placement": "both stages on one GPU", "math": args.math,
+                   "launch": "cuda_graph_per_step" if use_graph else "per_kernel",
                    "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
         "e2e": {"value": BATCH * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4,
                 "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
@@ -279,6 +282,7 @@ def main():
     ap.add_argument("--impl", choices=["engine", "reference"], default="engine")
     ap.add_argument("--math", default="fp32", choices=["fp32", "tf32x3", "tf32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch kernel by kernel instead of replaying CUDA graphs")
     args = ap.parse_args()
     return reference_arm(args) if args.impl == "reference" else engine_arm(args)
 

@@ -8,6 +8,7 @@
 #include <new>
 
 #include "cifar_simt.cuh"
+#include "cifar_tc.cuh"
 #include "common.cuh"
 #include "gpt_simt.cuh"
 #include "stage.cuh"
@@ -107,8 +108,12 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int grid = (int)std::min<int64_t>(batch, sms);
-  B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
-             st->dev(3), out, (int)batch);
+  if (st->d.math == B2P_MATH_FP32)
+    B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
+               st->dev(3), out, (int)batch);
+  else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
+    B2P_LAUNCH(cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
+               st->w2img, st->dev(3), out, (int)batch);
   return 0;
 }
 
@@ -357,9 +362,11 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
     // per-device function attribute: set with the stage's device current
     cudaError_t e = cudaFuncSetAttribute(part0_fused_f32, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sizeof(Part0Smem));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(cifar_tc::part0_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, cifar_tc::SMEM_BYTES);
     if (e != cudaSuccess) {
       b2p_stage_destroy(st);
-      return fail(B2P_ECUDA, "cudaFuncSetAttribute(part0_fused_f32): %s", cudaGetErrorString(e));
+      return fail(B2P_ECUDA, "cudaFuncSetAttribute(part0 kernels): %s", cudaGetErrorString(e));
     }
   }
   *out = st;
@@ -371,7 +378,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split);
-  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->fc_ws);
+  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -427,6 +434,10 @@ int b2p_stage_finalize(b2p_stage* st) {
     if (!st->w2t) B2P_TRY(dev_alloc(&st->w2t, 288 * 64));
     B2P_LAUNCH(transpose2d_f32, ceil_div(32 * 27, 256), 256, 0, 0, st->dev(0), st->w1t, 32, 27);
     B2P_LAUNCH(transpose2d_f32, ceil_div(64 * 288, 256), 256, 0, 0, st->dev(2), st->w2t, 64, 288);
+    if (st->d.math != B2P_MATH_FP32) {
+      if (!st->w2img) B2P_CUDA(cudaMalloc((void**)&st->w2img, cifar_tc::W2_BYTES));
+      B2P_LAUNCH(cifar_tc::pack_conv2_f16x2, ceil_div(9 * 64 * 8, 256), 256, 0, 0, st->dev(2), st->w2img);
+    }
   }
   // math-mode copies of the matrices that feed the tensor cores
   for (auto& w : st->w) {

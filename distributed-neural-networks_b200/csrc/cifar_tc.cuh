@@ -1,0 +1,328 @@
+// cifar_tc.cuh -- CIFAR part 0 (ModelPart0_2Node.forward, cifar_model_parts.py:37-42)
+// with conv2 as an implicit GEMM on the 5th-gen tensor cores.
+//
+// One persistent CTA per SM, one sample at a time, three warp roles running concurrently:
+//
+//   warps 0..7   conv1 producers (CUDA cores, packed fp32 FMA):
+//                  conv1(3->32)+bias+ReLU+maxpool for one pooled pixel per thread, exact
+//                  fp32; the 32-channel result is written as ONE 128-byte K-major row
+//                  [hi fp16 x32 | lo fp16 x32] into three x-shifted, y-padded NHWC copies
+//                  of the activation in shared memory (copy kw holds pixel (y, x+kw-1)).
+//   warp 8       MMA issuer: conv2 = sum over 9 taps of [128 px x 32 ic] x [32 ic x 64 oc].
+//                  Because copy kw is shifted by the tap's x offset and rows are 16 px
+//                  wide, the A operand of tap (kh,kw) for output rows y0..y0+7 is simply
+//                  the 128 consecutive smem rows starting at row (y0+kh)*16 of copy kw --
+//                  a plain 128B-swizzled K-major UMMA descriptor, no im2col is ever built.
+//   warps 9..12  epilogue: TMEM -> registers, + bias, ReLU, 2x2 maxpool with two warp
+//                  shuffles (a warp holds exactly two image rows), NCHW-flatten order
+//                  (index c*64 + h*8 + w) staged in smem, 16 KB coalesced store per sample.
+//
+// fp32-grade arithmetic on fp16 tensor-core inputs ("split fp16"): every fp32 operand x is
+// carried as hi = fp16(x) and lo = fp16((x - hi) * 2^11); three MMAs per K step
+// (hi*hi -> acc0, hi*lo and lo*hi -> acc1) and the epilogue forms acc0 + 2^-11 * acc1.
+// fp16 products are exact in the fp32 accumulator, so the only loss is the dropped lo*lo
+// term and the 2^-22 representation error: same tolerance as the fp32 CUDA-core kernel.
+// Compared with 3xTF32 this halves the shared-memory footprint (what makes the weights
+// AND a whole sample of activations fit) and doubles the MMA rate.  Range: |x| < 65504
+// (inputs are normalised images; conv1 outputs of a sane model are far below that).
+#pragma once
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "tc_gemm.cuh"
+
+namespace b2p {
+namespace cifar_tc {
+
+using namespace tc;
+
+constexpr int kProducerWarps = 8, kProducerThreads = 256;
+constexpr int kMmaWarp = 8;
+constexpr int kEpiWarp0 = 9, kEpiThreads = 128;
+constexpr int kThreads = (kEpiWarp0 + 4) * 32;       // 416
+
+constexpr int W2_TAP_BYTES = 64 * 128;               // [64 oc rows][128 B]
+constexpr int W2_BYTES = 9 * W2_TAP_BYTES;           // 73 728
+constexpr int ACT_COPY_BYTES = 18 * 16 * 128;        // 36 864: 18 rows (y halo) x 16 px x 128 B
+constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;        // 110 592
+
+struct Smem {
+  unsigned char w2[W2_BYTES];                        // pre-swizzled image from global
+  unsigned char act[ACT_BYTES];                      // 3 shifted copies, swizzled rows
+  float out[64 * 64];                                // one sample, flatten order
+  float in[3][34][34];                               // zero-padded input image
+  float w1[27][32];                                  // [c*9+kh*3+kw][oc]
+  float b1[32];
+  float b2[64];
+  uint64_t bar_w2, bar_act_full, bar_act_empty, bar_tmem_full[2], bar_tmem_empty[2];
+  uint32_t tmem_slot;
+};
+constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
+
+__device__ __forceinline__ void named_bar(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// packed fp32 FMA (two independent fp32 FMAs per lane per instruction, sm_100)
+__device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long long a, unsigned long long b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// x -> (hi, lo) with x ~= hi + lo * 2^-11
+__device__ __forceinline__ void split_f16(float x, __half& hi, __half& lo) {
+  hi = __float2half_rn(x);
+  lo = __float2half_rn((x - __half2float(hi)) * 2048.0f);
+}
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {   // kind::f16, A/B = F16 (format 0), fp32 accumulate
+  return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+// One-off weight repack (b2p_stage_finalize): conv2.weight [64,32,3,3] fp32 -> the exact
+// byte image of the B-operand tiles in shared memory: per tap a [64 oc][128 B] K-major tile,
+// row = [hi ic0..31 | lo ic0..31] fp16, 16-byte chunk c of row n stored at chunk c^(n&7).
+__global__ void pack_conv2_f16x2(const float* __restrict__ w2, unsigned char* __restrict__ img) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;       // one 16-byte chunk each
+  if (i >= 9 * 64 * 8) return;
+  const int tap = i / 512, n = (i / 8) % 64, c = i % 8;
+  const int kh = tap / 3, kw = tap % 3;
+  __half v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int ic = 8 * (c & 3) + e;
+    __half hi, lo;
+    split_f16(w2[((n * 32 + ic) * 3 + kh) * 3 + kw], hi, lo);
+    v[e] = c < 4 ? hi : lo;
+  }
+  *reinterpret_cast<uint4*>(img + tap * W2_TAP_BYTES + n * 128 + ((c ^ (n & 7)) * 16)) =
+      *reinterpret_cast<const uint4*>(v);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+part0_tc(const float* __restrict__ x,                // [B,3,32,32]
+         const float* __restrict__ w1t,              // [27][32]
+         const float* __restrict__ b1, const unsigned char* __restrict__ w2img,
+         const float* __restrict__ b2, float* __restrict__ out,   // [B,4096]
+         int batch) {
+  extern __shared__ unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- one-time set-up -----------------------------------------------------------------
+  for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
+  for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = w1t[i];
+  if (tid < 32) s.b1[tid] = b1[tid];
+  if (tid < 64) s.b2[tid] = b2[tid];
+  if (warp == kMmaWarp) {
+    if (lane == 0) {
+      mbar_init(&s.bar_w2, 1);
+      mbar_init(&s.bar_act_full, kProducerWarps);
+      mbar_init(&s.bar_act_empty, 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&s.bar_tmem_full[i], 1); mbar_init(&s.bar_tmem_empty[i], 4); }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(&s.tmem_slot, 512);
+    tmem_relinquish();
+  }
+  fence_proxy_async();               // the zeroed activation halo must be visible to the tensor core
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s.tmem_slot;
+
+  if (warp < kProducerWarps) {
+    // =========================== conv1 producers ===========================================
+    const int py = tid >> 4, px = tid & 15;
+    float4 pre[3];
+    if ((int)blockIdx.x < batch) {
+      const float4* xin = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 3072);
+#pragma unroll
+      for (int j = 0; j < 3; ++j) pre[j] = __ldg(xin + tid + 256 * j);
+    }
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      named_bar(1, kProducerThreads);                       // previous sample's window reads are done
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const int e = (tid + 256 * j) * 4;
+        const int c = e >> 10, r = (e >> 5) & 31, col = e & 31;
+        float* d = &s.in[c][r + 1][col + 1];
+        d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
+      }
+      named_bar(1, kProducerThreads);
+      if (b + (int)gridDim.x < batch) {                     // next image: in flight during the FMAs
+        const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) pre[j] = __ldg(xin + tid + 256 * j);
+      }
+      // ---- conv1 + ReLU + pool, 32 channels in two passes of 16 (8 packed pairs) --------------
+      uint32_t hi_pk[16], lo_pk[16];                        // fp16x2 words: channels (2i, 2i+1)
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        unsigned long long acc[8][4];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          const float2 bb = *reinterpret_cast<const float2*>(&s.b1[pass * 16 + 2 * p]);
+          const unsigned long long bv = pack2(bb.x, bb.y);
+          acc[p][0] = bv; acc[p][1] = bv; acc[p][2] = bv; acc[p][3] = bv;
+        }
+#pragma unroll 1
+        for (int c = 0; c < 3; ++c) {
+          float win[4][4];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * px]);
+            const float2 a = rp[0], bq = rp[1];
+            win[r][0] = a.x; win[r][1] = a.y; win[r][2] = bq.x; win[r][3] = bq.y;
+          }
+#pragma unroll
+          for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+              const unsigned long long x00 = pack2(win[kh][kw], win[kh][kw]);
+              const unsigned long long x01 = pack2(win[kh][kw + 1], win[kh][kw + 1]);
+              const unsigned long long x10 = pack2(win[kh + 1][kw], win[kh + 1][kw]);
+              const unsigned long long x11 = pack2(win[kh + 1][kw + 1], win[kh + 1][kw + 1]);
+              const unsigned long long* wrow =
+                  reinterpret_cast<const unsigned long long*>(&s.w1[c * 9 + kh * 3 + kw][pass * 16]);
+#pragma unroll
+              for (int p = 0; p < 8; ++p) {
+                const unsigned long long w = wrow[p];
+                ffma2(acc[p][0], x00, w);
+                ffma2(acc[p][1], x01, w);
+                ffma2(acc[p][2], x10, w);
+                ffma2(acc[p][3], x11, w);
+              }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          float a0, a1, b0, b1v, c0, c1, d0, d1;
+          unpack2(acc[p][0], a0, a1); unpack2(acc[p][1], b0, b1v);
+          unpack2(acc[p][2], c0, c1); unpack2(acc[p][3], d0, d1);
+          const float v0 = fmaxf(fmaxf(fmaxf(a0, b0), fmaxf(c0, d0)), 0.f);   // relu(max) == max(relu)
+          const float v1 = fmaxf(fmaxf(fmaxf(a1, b1v), fmaxf(c1, d1)), 0.f);
+          __half h0, l0, h1, l1;
+          split_f16(v0, h0, l0);
+          split_f16(v1, h1, l1);
+          __half2 hh = __halves2half2(h0, h1), ll = __halves2half2(l0, l1);
+          hi_pk[pass * 8 + p] = *reinterpret_cast<uint32_t*>(&hh);
+          lo_pk[pass * 8 + p] = *reinterpret_cast<uint32_t*>(&ll);
+        }
+      }
+      // ---- publish the pixel's row into the three shifted copies -----------------------------
+      mbar_wait(&s.bar_act_empty, (n & 1) ^ 1);             // MMAs of the previous sample are done
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int xc = px - kw + 1;                          // column of this pixel in copy kw
+        if (xc < 0 || xc > 15) continue;
+        const int R = (py + 1) * 16 + xc;
+        unsigned char* row = s.act + kw * ACT_COPY_BYTES + R * 128;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const uint32_t* src = (c < 4) ? &hi_pk[4 * c] : &lo_pk[4 * (c - 4)];
+          *reinterpret_cast<uint4*>(row + ((c ^ (R & 7)) * 16)) = make_uint4(src[0], src[1], src[2], src[3]);
+        }
+      }
+      fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.bar_act_full);
+    }
+  } else if (warp == kMmaWarp) {
+    // =========================== MMA issuer ====================================================
+    if (lane == 0) {
+      mbar_expect_tx(&s.bar_w2, W2_BYTES);
+      for (int t = 0; t < 9; ++t) bulk_g2s(s.w2 + t * W2_TAP_BYTES, w2img + t * W2_TAP_BYTES, W2_TAP_BYTES, &s.bar_w2);
+    }
+    __syncwarp();
+    mbar_wait(&s.bar_w2, 0);
+    constexpr uint32_t idesc = make_idesc_f16(128, 64);
+    const uint32_t act_addr = smem_u32(s.act), w2_addr = smem_u32(s.w2);
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      const uint32_t set = n & 1, use = n >> 1;
+      mbar_wait(&s.bar_tmem_empty[set], (use & 1) ^ 1);
+      mbar_wait(&s.bar_act_full, n & 1);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll 1
+        for (int t = 0; t < 2; ++t) {
+          const uint32_t acc0 = tmem_base + set * 256 + t * 128, acc1 = acc0 + 64;
+#pragma unroll 1
+          for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap % 3;
+            const uint64_t da = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 * t + kh) * 16 * 128);
+            const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
+            // K = 32 channels = 2 MMAs of K=16; descriptor units are 16 B: +2 = 32 B, +4 = the lo half
+            umma<0>(acc0, da, db, idesc, tap != 0);                 // hi * hi
+            umma<0>(acc0, da + 2, db + 2, idesc, 1u);
+            umma<0>(acc1, da, db + 4, idesc, tap != 0);             // hi * lo
+            umma<0>(acc1, da + 2, db + 6, idesc, 1u);
+            umma<0>(acc1, da + 4, db, idesc, 1u);                   // lo * hi
+            umma<0>(acc1, da + 6, db + 2, idesc, 1u);
+          }
+        }
+        umma_commit(&s.bar_act_empty);                       // activation copies may be overwritten
+        umma_commit(&s.bar_tmem_full[set]);
+      }
+      __syncwarp();
+    }
+  } else {
+    // =========================== epilogue =======================================================
+    const int q = warp & 3;                                  // TMEM lane quarter: image rows 2q, 2q+1 of the tile
+    const int et = tid - kEpiWarp0 * 32;                     // 0..127
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      const uint32_t set = n & 1, use = n >> 1;
+      mbar_wait(&s.bar_tmem_full[set], use & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int t = 0; t < 2; ++t) {
+#pragma unroll 1
+        for (int ch = 0; ch < 2; ++ch) {                     // 32 output channels at a time
+          uint32_t r0[32], r1[32];
+          const uint32_t ta = tmem_base + set * 256 + t * 128 + ch * 32 + (static_cast<uint32_t>(q * 32) << 16);
+          tmem_ld32(ta, r0);
+          tmem_ld32(ta + 64, r1);
+          tmem_ld_wait();
+          const int pooled = (t * 4 + q) * 8 + ((lane & 15) >> 1);    // h*8 + w of the pooled pixel
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float v = fmaf(__uint_as_float(r1[j]), 1.0f / 2048.0f, __uint_as_float(r0[j])) + s.b2[ch * 32 + j];
+            v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));         // x neighbour
+            v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 16));        // y neighbour
+            if ((lane & 17) == 0) s.out[(ch * 32 + j) * 64 + pooled] = fmaxf(v, 0.f);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.bar_tmem_empty[set]);
+      named_bar(2, kEpiThreads);                              // the sample's 4096 outputs are staged
+      float4* dst = reinterpret_cast<float4*>(out + (size_t)b * 4096);
+      const float4* src = reinterpret_cast<const float4*>(s.out);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
+      named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace cifar_tc
+}  // namespace b2p

@@ -59,6 +59,9 @@ class LocalPipeline:
         self._consumed = [dict() for _ in hidden_shapes]
         for s in stages:
             s._finalize()
+        # CUDA graphs of the whole device-resident schedule, keyed by (input address, batch, seq)
+        self._graphs: dict = {}
+        self.graph_kernel_launches = 0      # kernels executed through graph replays (for accounting)
 
     # -- device-resident schedule -------------------------------------------------------
     def run_device(self, x: torch.Tensor, out: torch.Tensor | None = None, seq: int = 0,
@@ -96,10 +99,41 @@ class LocalPipeline:
                     src = self.hidden[k][lo:lo + n]
         return out[:b]
 
+    # -- the same schedule as one CUDA graph ---------------------------------------------------
+    def run_device_graph(self, x: torch.Tensor, seq: int = 0) -> torch.Tensor:
+        """Like run_device, but the whole micro-batched schedule (all stages, all streams,
+        their events) is captured once per distinct input buffer and replayed with a single
+        launch: the CIFAR step is ~25 kernels of a few microseconds each, so per-kernel
+        launch latency would otherwise dominate.  The result is complete when
+        ``self.compute[0]`` has drained (the capture joins every stage stream back)."""
+        from . import _lib
+        key = (x.data_ptr(), x.shape[0], seq)
+        entry = self._graphs.get(key)
+        main = self.compute[0]
+        if entry is None:
+            self.run_device(x, seq=seq)                 # warm-up outside capture: lazy allocations
+            self.synchronize()
+            self._consumed = [dict() for _ in self._consumed]    # no events from outside the capture
+            g = torch.cuda.CUDAGraph()
+            before = _lib.launch_count()
+            with torch.cuda.graph(g, stream=main):
+                self.run_device(x, seq=seq)
+                for st in self.compute[1:]:
+                    main.wait_stream(st)
+            entry = (g, _lib.launch_count() - before)
+            self._graphs[key] = entry
+            self._consumed = [dict() for _ in self._consumed]
+        with torch.cuda.stream(main):
+            entry[0].replay()
+        self.graph_kernel_launches += entry[1]
+        return self.out_dev[:x.shape[0]]
+
     # -- host-facing schedule ---------------------------------------------------------------
-    def run_host(self, x_host: torch.Tensor, seq: int = 0, sync: bool = True) -> torch.Tensor:
+    def run_host(self, x_host: torch.Tensor, seq: int = 0, sync: bool = True, graph: bool = False) -> torch.Tensor:
         """x_host: pinned host tensor [B, *in_shape].  Returns the pinned host result
-        [B, *out_shape] (a view of an internal buffer, overwritten by the next call)."""
+        [B, *out_shape] (a view of an internal buffer, overwritten by the next call).
+        graph=True replays the captured schedule (one launch per step); the H2D copy of step
+        s+1 still overlaps the compute of step s through the double-buffered device input."""
         b = x_host.shape[0]
         assert b <= self.max_batch
         flip = self._flip
@@ -117,13 +151,18 @@ class LocalPipeline:
                 ev = torch.cuda.Event()
                 ev.record(self.copy_in)
                 ready.append(ev)
-        out = self.run_device(xd[:b], seq=seq, ready=ready)
+        if graph:
+            self.compute[0].wait_event(ready[-1])
+            out = self.run_device_graph(xd[:b], seq=seq)
+        else:
+            out = self.run_device(xd[:b], seq=seq, ready=ready)
         ev = torch.cuda.Event()
         ev.record(self.compute[0])
         self._x_free[flip] = ev
-        last = self.compute[-1]
+        last = self.compute[0] if graph else self.compute[-1]
         with torch.cuda.stream(last):
             self.out_host[:b].copy_(out, non_blocking=True)
+        self._last_stream = last
         if sync:
             last.synchronize()
         return self.out_host[:b]

@@ -164,3 +164,71 @@ def test_tensor_core_fc_stage(cuda_engine, mode, tol):
     x = co.part0(co.make_input(256, seed=5), sd).cuda()
     with torch.no_grad():
         assert torch.equal(p1(x), torch.cat([p1(x[:128]), p1(x[128:])]))
+
+
+@pytest.fixture(scope="module")
+def tc_parts(cuda_engine):
+    """Both parts in the tensor-core parity mode: conv2 as a split-fp16 implicit GEMM
+    (tcgen05), fc1 as a 3xTF32 split-K GEMM."""
+    sd = co.init_state_dict(1234)
+    full = cuda_engine.NeuralNetwork()
+    out = []
+    for k in (0, 1):
+        p = cuda_engine.MODEL_PARTS_CLASSES[k](full, math="tf32x3").to("cuda:0")
+        p.load_state_dict(sd, strict=False)
+        out.append(p.eval())
+    return sd, out[0], out[1]
+
+
+@pytest.mark.parametrize("batch", [1, 2, 3, 128, 149, 300, 1024])
+def test_tensor_core_part0_parity(tc_parts, batch):
+    """Same tolerances as the fp32 CUDA-core path: the split-fp16 contraction is fp32-grade."""
+    sd, p0, p1 = tc_parts
+    x = co.make_input(batch, seed=700 + batch)
+    with torch.no_grad():
+        act = p0(x.cuda())
+        probs = p1(act).cpu()
+    want_act, want = co.part0(x, sd), co.full(x, sd)
+    assert act.shape == (batch, 4096)
+    err = (act.cpu() - want_act).abs().max().item()
+    assert err <= ACT_TOL, f"activation error {err}"
+    assert (probs - want).abs().max().item() <= PROB_TOL
+    decided = co.top2_margin(want) > TIE
+    assert torch.equal(probs.argmax(1)[decided], want.argmax(1)[decided])
+
+
+def test_tensor_core_golden_and_10k(tc_parts, golden_dir):
+    sd, p0, p1 = tc_parts
+    g = np.load(os.path.join(golden_dir, "cifar_b8.npz"))
+    with torch.no_grad():
+        act = p0(torch.from_numpy(g["x"]).cuda())
+        probs = p1(act)
+    np.testing.assert_allclose(act.cpu().numpy(), g["part0"], rtol=0, atol=ACT_TOL)
+    np.testing.assert_allclose(probs.cpu().numpy(), g["probs"], rtol=0, atol=PROB_TOL)
+    flips = ties = 0
+    worst = 0.0
+    for chunk in range(10):
+        x = co.make_input(1024, seed=9000 + chunk)
+        with torch.no_grad():
+            probs = p1(p0(x.cuda())).cpu()
+        want = co.full(x, sd)
+        decided = co.top2_margin(want) > TIE
+        ties += int((~decided).sum())
+        flips += int((probs.argmax(1)[decided] != want.argmax(1)[decided]).sum())
+        worst = max(worst, (probs - want).abs().max().item())
+    print(f"\ntensor-core mode, 10240 samples: {flips} flips, {ties} near-ties, max|dprob|={worst:.2e}")
+    assert flips == 0 and worst <= PROB_TOL
+
+
+def test_tensor_core_microbatching_bit_exact_and_matches_fp32_path(tc_parts, parts):
+    _, p0, p1 = tc_parts
+    _, f0, f1 = parts
+    x = co.make_input(1024, seed=78).cuda()
+    with torch.no_grad():
+        whole = p1(p0(x))
+        pieces = torch.cat([p1(p0(x[i:i + 128])) for i in range(0, 1024, 128)])
+        ref = f1(f0(x))
+        a_tc, a_f32 = p0(x), f0(x)
+    assert torch.equal(whole, pieces)
+    assert (a_tc - a_f32).abs().max().item() <= ACT_TOL      # device-side check at full size
+    assert (whole - ref).abs().max().item() <= PROB_TOL
