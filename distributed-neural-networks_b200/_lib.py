@@ -47,6 +47,7 @@ _PROTOTYPES = {
     "b2p_stage_finalize": (C.c_int, [C.c_void_p]),
     "b2p_stage_out_elems": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "b2p_stage_trace": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong), C.c_int]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_stage_forward_argmax": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_linear": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
@@ -59,6 +60,9 @@ _PROTOTYPES = {
     "b2p_ring_open": (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int]),
     "b2p_ring_open_local": (C.c_int, [C.POINTER(C.c_void_p), C.c_void_p, C.c_int]),
     "b2p_ring_destroy": (C.c_int, [C.c_void_p]),
+    "b2p_ring_set_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2p_ring_acquire": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.c_void_p]),
+    "b2p_ring_publish": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     "b2p_ring_send": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]),
     "b2p_ring_recv": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.c_void_p]),
     "b2p_ring_release": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),

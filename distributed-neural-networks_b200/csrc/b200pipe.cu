@@ -113,7 +113,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH(cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
-               st->w2img, st->dev(3), out, (int)batch);
+               st->w2img, st->dev(3), out, (int)batch, st->trace);
   return 0;
 }
 
@@ -378,7 +378,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split);
-  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->fc_ws);
+  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->trace); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -508,6 +508,21 @@ int b2p_linear(int operand_kind, const void* a_dev, const void* a_lo_dev, int64_
   int rc = tc::linear_tc_dispatch(operand_kind & 0xff, a_dev, a_lo_dev, lda, w_dev, w_lo_dev, ldw, ep, (int)M, (int)N,
                                   (int)K, 1, tile_n, static_cast<cudaStream_t>(stream));
   return rc < 0 ? rc : 0;
+}
+
+int b2p_stage_trace(b2p_stage* st, long long* host_out, int n) {
+  // developer aid: clock64 timeline of CTA 0 of the CIFAR part-0 tensor-core kernel
+  if (!st || !host_out || n < 256) return fail(B2P_EINVAL, "trace buffer must hold at least 256 entries");
+  DeviceGuard g(st->d.device);
+  if (!st->trace) {
+    B2P_CUDA(cudaMalloc((void**)&st->trace, 256 * sizeof(long long)));
+    B2P_CUDA(cudaMemset(st->trace, 0, 256 * sizeof(long long)));
+    memset(host_out, 0, 256 * sizeof(long long));
+    return 0;
+  }
+  B2P_CUDA(cudaDeviceSynchronize());
+  B2P_CUDA(cudaMemcpy(host_out, st->trace, 256 * sizeof(long long), cudaMemcpyDeviceToHost));
+  return 0;
 }
 
 int b2p_stage_check(b2p_stage* st, void* stream) {

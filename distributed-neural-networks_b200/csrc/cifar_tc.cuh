@@ -113,9 +113,14 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
          const float* __restrict__ w1t,              // [27][32]
          const float* __restrict__ b1, const unsigned char* __restrict__ w2img,
          const float* __restrict__ b2, float* __restrict__ out,   // [B,4096]
-         int batch) {
-  extern __shared__ unsigned char smem_raw[];
-  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+         int batch, long long* __restrict__ dbg) {   // dbg: optional [3 roles][8 samples][8 events] clock64 trace of CTA 0
+#define B2P_TRACE(role, n, ev, cond) \
+  do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
+  // (offset arithmetic on the __shared__ array itself, not on a uintptr_t: the compiler keeps
+  //  the shared address space and emits LDS/STS instead of generic LD/ST -- with generic
+  //  accesses it also has to assume every store may alias every load, which serialises them)
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // ---- one-time set-up -----------------------------------------------------------------
@@ -141,6 +146,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s.tmem_slot;
+  if (dbg && blockIdx.x == 0 && tid == 0) dbg[3 * 64] = clock64();      // end of set-up
 
   if (warp < kProducerWarps) {
     // =========================== conv1 producers ===========================================
@@ -153,6 +159,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     }
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      B2P_TRACE(0, n, 0, tid == 0);
       named_bar(1, kProducerThreads);                       // previous sample's window reads are done
 #pragma unroll
       for (int j = 0; j < 3; ++j) {
@@ -167,6 +174,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
 #pragma unroll
         for (int j = 0; j < 3; ++j) pre[j] = __ldg(xin + tid + 256 * j);
       }
+      B2P_TRACE(0, n, 1, tid == 0);
       // ---- conv1 + ReLU + pool, 32 channels in two passes of 16 (8 packed pairs) --------------
       uint32_t hi_pk[16], lo_pk[16];                        // fp16x2 words: channels (2i, 2i+1)
 #pragma unroll
@@ -223,7 +231,9 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
         }
       }
       // ---- publish the pixel's row into the three shifted copies -----------------------------
+      B2P_TRACE(0, n, 2, tid == 0);
       mbar_wait(&s.bar_act_empty, (n & 1) ^ 1);             // MMAs of the previous sample are done
+      B2P_TRACE(0, n, 3, tid == 0);
 #pragma unroll
       for (int kw = 0; kw < 3; ++kw) {
         const int xc = px - kw + 1;                          // column of this pixel in copy kw
@@ -239,6 +249,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_act_full);
+      B2P_TRACE(0, n, 4, tid == 0);
     }
   } else if (warp == kMmaWarp) {
     // =========================== MMA issuer ====================================================
@@ -253,9 +264,12 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       const uint32_t set = n & 1, use = n >> 1;
+      B2P_TRACE(1, n, 0, lane == 0);
       mbar_wait(&s.bar_tmem_empty[set], (use & 1) ^ 1);
+      B2P_TRACE(1, n, 1, lane == 0);
       mbar_wait(&s.bar_act_full, n & 1);
       tc_fence_after();
+      B2P_TRACE(1, n, 2, lane == 0);
       if (lane == 0) {
 #pragma unroll 1
         for (int t = 0; t < 2; ++t) {
@@ -277,6 +291,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
         umma_commit(&s.bar_act_empty);                       // activation copies may be overwritten
         umma_commit(&s.bar_tmem_full[set]);
       }
+      B2P_TRACE(1, n, 3, lane == 0);
       __syncwarp();
     }
   } else {
@@ -286,8 +301,11 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       const uint32_t set = n & 1, use = n >> 1;
+      B2P_TRACE(2, n, 0, et == 0);
       mbar_wait(&s.bar_tmem_full[set], use & 1);
       tc_fence_after();
+      B2P_TRACE(2, n, 1, et == 0);
+      const bool xo = (lane & 1) != 0, yo = (lane & 16) != 0;
 #pragma unroll 1
       for (int t = 0; t < 2; ++t) {
 #pragma unroll 1
@@ -297,31 +315,47 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           tmem_ld32(ta, r0);
           tmem_ld32(ta + 64, r1);
           tmem_ld_wait();
+          // 2x2 max-pool across lanes.  A lane owns one conv2 pixel (x = lane&15, row = lane>>4);
+          // pool partners are lane^1 (x) and lane^16 (y).  Instead of two shuffles per channel
+          // with 3/4 of the lanes ending up redundant, partners SWAP channels: after the x step
+          // the even-x lane keeps channel 2p and the odd-x lane channel 2p+1, after the y step
+          // likewise -- 24 shuffles per 32 channels and every lane ends with 8 distinct results.
+          float u[16];
+#pragma unroll
+          for (int p = 0; p < 16; ++p) {
+            const float a = fmaf(__uint_as_float(r1[2 * p]), 1.0f / 2048.0f, __uint_as_float(r0[2 * p]));
+            const float b = fmaf(__uint_as_float(r1[2 * p + 1]), 1.0f / 2048.0f, __uint_as_float(r0[2 * p + 1]));
+            const float recv = __shfl_xor_sync(0xffffffffu, xo ? a : b, 1);
+            u[p] = fmaxf(xo ? b : a, recv);                  // channel 2p + xo, pooled in x
+          }
           const int pooled = (t * 4 + q) * 8 + ((lane & 15) >> 1);    // h*8 + w of the pooled pixel
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float v = fmaf(__uint_as_float(r1[j]), 1.0f / 2048.0f, __uint_as_float(r0[j])) + s.b2[ch * 32 + j];
-            v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));         // x neighbour
-            v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 16));        // y neighbour
-            if ((lane & 17) == 0) s.out[(ch * 32 + j) * 64 + pooled] = fmaxf(v, 0.f);
+          for (int g = 0; g < 8; ++g) {
+            const float recv = __shfl_xor_sync(0xffffffffu, yo ? u[2 * g] : u[2 * g + 1], 16);
+            const float m = fmaxf(yo ? u[2 * g + 1] : u[2 * g], recv);
+            const int c = ch * 32 + 4 * g + (yo ? 2 : 0) + (xo ? 1 : 0);
+            s.out[c * 64 + pooled] = fmaxf(m + s.b2[c], 0.f);         // max(a)+b == max(a+b)
           }
         }
       }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_tmem_empty[set]);
+      B2P_TRACE(2, n, 2, et == 0);
       named_bar(2, kEpiThreads);                              // the sample's 4096 outputs are staged
       float4* dst = reinterpret_cast<float4*>(out + (size_t)b * 4096);
       const float4* src = reinterpret_cast<const float4*>(s.out);
 #pragma unroll
       for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
       named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
+      B2P_TRACE(2, n, 3, et == 0);
     }
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+#undef B2P_TRACE
 }
 
 }  // namespace cifar_tc

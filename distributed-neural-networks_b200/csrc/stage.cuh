@@ -34,6 +34,7 @@ struct b2p_stage {
   float* w1t = nullptr;             // [27][32]
   float* w2t = nullptr;             // [288][64]
   unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's B tiles (split fp16)
+  long long* trace = nullptr;       // optional kernel timeline buffer (b2p_stage_trace)
   // ---- CIFAR part 1 ----
   float* fc_ws = nullptr;           // split-K partials [splits][M][512]
   size_t fc_ws_bytes = 0;

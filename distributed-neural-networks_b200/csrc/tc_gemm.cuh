@@ -203,10 +203,11 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
           const __grid_constant__ CUtensorMap tmap_a_lo, const __grid_constant__ CUtensorMap tmap_w_lo,
           EpiParams ep, int M, int N, int K, int splits, int kb_per_split) {
   using Cfg = GemmCfg<KIND, BN>;
-  extern __shared__ unsigned char smem_raw[];
-  // SWIZZLE_128B tiles need 1024-byte alignment (the XOR pattern is a function of the address)
-  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                                         ~static_cast<uintptr_t>(1023));
+  // SWIZZLE_128B tiles need 1024-byte alignment (the XOR pattern is a function of the address).
+  // The fix-up is an offset on the __shared__ array (not uintptr_t arithmetic) so the compiler
+  // keeps the shared address space: LDS/STS instead of generic LD/ST in the epilogue.
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* tiles = smem;
   float* epi_smem = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + Cfg::EPI_BYTES);

@@ -1,0 +1,243 @@
+"""One process per GPU: stage k of the pipeline on rank k, activations handed over NVLink.
+
+Reference counterpart: one ``node.py`` process per machine, stage = ``part_index``
+(node.py:239-260), next hop = the node with ``part_index + 1`` (node.py:262-271), one gRPC
+``SendTensor`` per request per hop (node.py:73-89).  Here the hop is a peer-memory ring
+(handoff.py): the producer stage's kernel stores its output straight into the consumer
+GPU's receive slot, and one-thread wait/flag kernels order the two streams -- the host of
+neither rank ever blocks inside a step.
+
+Launched with ``python -m torch.distributed.run --nproc-per-node N ...``; torch.distributed
+is used for rendezvous, the exchange of ring handles and the max-over-ranks of the timing.
+"""
+from __future__ import annotations
+
+import json
+import os
+import statistics
+import time
+from dataclasses import dataclass
+
+import torch
+
+
+@dataclass(frozen=True)
+class RankRole:
+    rank: int
+    replica: int        # which independent pipeline this rank belongs to
+    stage: int          # 0 .. stages-1 within the replica
+    stages: int
+    prev_rank: int | None
+    next_rank: int | None
+    active: bool = True
+
+
+def plan(world: int, stages: int) -> list[RankRole]:
+    """Ranks [r*stages, (r+1)*stages) form replica r; left-over ranks stay idle.  For the
+    CIFAR workload stages == 2 (4 and 8 GPUs run 2 and 4 independent pipelines)."""
+    roles = []
+    replicas = world // stages
+    for rank in range(world):
+        rep, st = divmod(rank, stages)
+        if rep >= replicas:
+            roles.append(RankRole(rank, rep, st, stages, None, None, active=False))
+            continue
+        roles.append(RankRole(rank, rep, st, stages,
+                              rank - 1 if st > 0 else None, rank + 1 if st < stages - 1 else None))
+    return roles
+
+
+def exchange_handles(my_handle: bytes | None, group=None) -> list:
+    """Every rank contributes the export handle of the ring it consumes from (or None)."""
+    import torch.distributed as dist
+    out = [None] * dist.get_world_size(group)
+    dist.all_gather_object(out, my_handle, group=group)
+    return out
+
+
+class CifarRankPipeline:
+    """BASELINE config 2 across ranks: even stage = conv part, odd stage = FC part."""
+
+    ACT_BYTES = 4096 * 4            # per sample, the reference's fp32 [B,4096] handoff tensor
+
+    def __init__(self, role: RankRole, device: torch.device, math: str, batch: int, microbatch: int,
+                 slots: int = 8, group=None):
+        import dnn_b200 as engine
+        from .handoff import Ring
+        self.role, self.dev, self.batch, self.mb = role, device, batch, microbatch
+        self.n_mb = (batch + microbatch - 1) // microbatch
+        self.seq = 0
+        self.stream = torch.cuda.Stream(device=device)
+        self.copy_stream = torch.cuda.Stream(device=device)
+        torch.manual_seed(1234)
+        full = engine.NeuralNetwork()
+        sd = full.state_dict()
+        self.part = engine.MODEL_PARTS_CLASSES[role.stage](full, math=math).to(device)
+        self.part.load_state_dict(sd, strict=False)
+        self.part.eval()
+        slot_bytes = microbatch * self.ACT_BYTES
+        self.ring = None
+        mine = None
+        if role.active and role.stage == 1:
+            self.ring = Ring.create(device.index, slots, slot_bytes)
+            mine = self.ring.export()
+        handles = exchange_handles(mine, group)
+        if role.active and role.stage == 0:
+            self.ring = Ring.open(handles[role.next_rank], device.index, slots, slot_bytes)
+        if role.stage == 0:
+            self.x_dev = [torch.empty((batch, 3, 32, 32), device=device) for _ in range(2)]
+            self._x_free = [None, None]
+            self._flip = 0
+        else:
+            self.out_dev = torch.empty((batch, 10), device=device)
+            self.out_host = torch.empty((batch, 10)).pin_memory()
+
+    # ---- one step = one batch through this rank's stage ------------------------------------------
+    def step_device(self, x: torch.Tensor | None, ready=None):
+        s = self.stream.cuda_stream
+        for i, lo in enumerate(range(0, self.batch, self.mb)):
+            n = min(self.mb, self.batch - lo)
+            if self.role.stage == 0:
+                if ready is not None:
+                    self.stream.wait_event(ready[i])
+                slot = self.ring.acquire(self.seq, s)                 # peer memory on the next GPU
+                self.part.forward_ptr(x[lo:].data_ptr(), slot, n, 0, s)   # epilogue stores cross NVLink
+                self.ring.publish(self.seq, s)
+            else:
+                slot = self.ring.recv(self.seq, s)
+                self.part.forward_ptr(slot, self.out_dev[lo:].data_ptr(), n, 0, s)
+                self.ring.release(self.seq, s)
+            self.seq += 1
+
+    def step_host(self, x_host: torch.Tensor | None):
+        """Stage 0: pinned host batch -> H2D per microbatch -> stage; stage 1: stage -> D2H."""
+        if self.role.stage == 0:
+            flip = self._flip
+            self._flip ^= 1
+            xd = self.x_dev[flip]
+            if self._x_free[flip] is not None:
+                self.copy_stream.wait_event(self._x_free[flip])
+            ready = []
+            with torch.cuda.stream(self.copy_stream):
+                for lo in range(0, self.batch, self.mb):
+                    xd[lo:lo + self.mb].copy_(x_host[lo:lo + self.mb], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(self.copy_stream)
+                    ready.append(ev)
+            self.step_device(xd, ready)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+            self._x_free[flip] = ev
+        else:
+            self.step_device(None)
+            with torch.cuda.stream(self.stream):
+                self.out_host.copy_(self.out_dev, non_blocking=True)
+
+
+def bench_main(args) -> int:
+    """bench.py --gpus N under torchrun (N >= 2)."""
+    import torch.distributed as dist
+    import dnn_b200 as engine
+    from bench import (BATCH, MICROBATCH, METRIC, UNIT, WORKLOAD, FLOP_PART0, BYTES_PART0, ClockSampler, _peaks)
+
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    roles = plan(world, 2)
+    role = roles[rank]
+    pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH)
+    replicas = world // 2
+    W, K = max(args.warmup, 3), args.steps
+    n_pool = 16
+    g = torch.Generator().manual_seed(rank)
+    host_pool = dev_pool = None
+    if role.active and role.stage == 0:
+        host_pool = [torch.randn(BATCH, 3, 32, 32, generator=g).pin_memory() for _ in range(n_pool)]
+        dev_pool = [h.to(dev) for h in host_pool]
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    def timed(fn):
+        for i in range(W):
+            fn(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.perf_counter()
+        e0.record(pipe.stream)
+        for i in range(K):
+            fn(W + i)
+        e1.record(pipe.stream)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - w0
+        dist.barrier()
+        t = torch.tensor([e0.elapsed_time(e1), 1e3 * wall], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
+        return float(t[0]), float(t[1])
+
+    launches0 = engine.launch_count()
+    sampler.active.set()
+    if role.active:
+        ms_dev, _ = timed(lambda i: pipe.step_device(dev_pool[i % n_pool] if dev_pool else None))
+    else:
+        ms_dev, _ = timed(lambda i: None)
+    launches = engine.launch_count() - launches0
+    if role.active:
+        _, ms_e2e = timed(lambda i: pipe.step_host(host_pool[i % n_pool] if host_pool else None))
+    else:
+        _, ms_e2e = timed(lambda i: None)
+    sampler.active.clear()
+    clocks = sampler.finish()
+    lt = torch.tensor([float(launches)], device=dev)
+    dist.all_reduce(lt)
+    checksum = float(pipe.out_host.sum()) if role.active and role.stage == 1 else 0.0
+    ct = torch.tensor([checksum], device=dev)
+    dist.all_reduce(ct)
+
+    # roofline: stage-0 kernel timed alone on rank 0's launch stream
+    roofline = None
+    if rank == 0:
+        peaks, kind = _peaks()
+        s = pipe.stream
+        act = torch.empty(BATCH, 4096, device=dev)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 0
+        torch.cuda.synchronize()
+        r0.record(s)
+        for i in range(K):
+            x = dev_pool[i % n_pool]
+            for lo in range(0, BATCH, MICROBATCH):
+                pipe.part.forward_ptr(x[lo:].data_ptr(), act[lo:].data_ptr(), MICROBATCH, 0, s.cuda_stream)
+                n += 1
+        r1.record(s)
+        torch.cuda.synchronize()
+        us = 1e3 * r0.elapsed_time(r1) / n
+        tf = FLOP_PART0 * MICROBATCH / (us * 1e-6) / 1e12
+        roofline = {"kernel": "part0 (conv1+ReLU+pool+conv2+ReLU+pool), one launch per 128-sample microbatch",
+                    "bound": "tensor", "achieved": tf, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                    "frac": tf / peaks["bf16_tflops_sustained"], "traffic": None,
+                    "peak_source": f"bf16_tflops_sustained of {kind}", "us_per_launch": us,
+                    "hbm_view": {"achieved_gbs": BYTES_PART0 * MICROBATCH / (us * 1e-6) / 1e9, "peak_gbs": peaks["hbm_gbs"]}}
+    dist.barrier()
+    if rank == 0:
+        total = BATCH * K * replicas
+        line = {
+            "metric": METRIC, "value": total / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "f32"}.get(args.math, args.math), "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH, "stages": 2,
+                       "placement": f"{replicas} pipeline(s) of 2 stages, stage k on GPU 2r+k; activations stored by the "
+                                    "stage-0 kernel directly into a peer-memory ring on the stage-1 GPU (NVLink)",
+                       "math": args.math, "launch": "per_kernel",
+                       "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
+            "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
+                    "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0])},
+            "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None,
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0

@@ -137,6 +137,11 @@ B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
  * nn.Embedding, gpt_model_parts.py:17).  Returns 0 when clean. */
 B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 
+/* Developer aid (no reference counterpart): the first call arms a per-stage trace buffer,
+ * later calls synchronise and copy out 256 clock64 stamps of CTA 0 of the CIFAR part-0
+ * tensor-core kernel ([role 0..2][sample 0..7][event 0..7], entry 192 = end of set-up). */
+B2P_API int b2p_stage_trace(b2p_stage* st, long long* host_out, int n);
+
 /* GPT final only: greedy token ids (row arg-max of the logits) without
  * materialising [B,T,V]; out int64 [batch,seq].  (north_star: "greedy token ids") */
 B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
@@ -201,6 +206,15 @@ B2P_API int b2p_ring_export(b2p_ring* ring, void* handle_out /* B2P_RING_HANDLE_
 B2P_API int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device);
 B2P_API int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_device);
 B2P_API int b2p_ring_destroy(b2p_ring* ring);
+/* How b2p_ring_send moves the payload: 0 = cudaMemcpyAsync (copy engine),
+ * 1 = SM copy kernel with 128-bit peer stores (default). */
+B2P_API int b2p_ring_set_mode(b2p_ring* ring, int mode);
+/* Zero-copy variant for a producer whose kernel can write its output anywhere: acquire
+ * waits (on the stream) until slot (seq % slots) is free and returns its address -- mapped
+ * memory of the consumer's GPU; run the producing stage with out = that address, then
+ * publish(seq).  The transfer then rides on the stage kernel's own stores over NVLink. */
+B2P_API int b2p_ring_acquire(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream);
+B2P_API int b2p_ring_publish(b2p_ring* ring, uint64_t seq, void* stream);
 /* producer: wait until slot (seq % slots) is free, copy `bytes` from src_dev into
  * it and publish sequence number seq (seq counts from 0, strictly increasing). */
 B2P_API int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uint64_t seq, void* stream);
