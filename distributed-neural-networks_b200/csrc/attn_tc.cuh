@@ -1,0 +1,260 @@
+// attn_tc.cuh -- causal self-attention on the 5th-gen tensor cores (bf16, head dim 64).
+//
+//   y[b,t,h*64:(h+1)*64] = softmax_{j<=t}( q_t . k_j / 8 ) v_j          (oracle/gpt_model.py,
+//   the CausalSelfAttention of the block the reference imports at gpt_model_parts.py:4)
+//
+// qkv is the c_attn output as bf16 [B*T, 3C] (q | k | v, head h at column h*64); nothing
+// is transposed or re-laid-out: Q, K and V tiles are fetched by TMA straight out of that
+// buffer (128B-swizzled boxes of 64 columns).
+//
+// One CTA = one (128-query tile, head, batch element); key/value tiles of 64:
+//   warp 0      TMA producer: Q once, then K_j / V_j through a 2-stage ring
+//   warp 1      MMA issuer  : S = Q K_j^T   (M128 N64 K64, A and B K-major)      -> TMEM S
+//                             O_j = P_j V_j (M128 N64 K64, A K-major from smem,
+//                                            B = V tile as MN-major operand)      -> TMEM O
+//   warps 2..5  softmax     : one query row per thread.  Reads S from TMEM, online softmax
+//                             in exp2 domain, writes P (bf16) as a swizzled K-major A tile,
+//                             then folds the fresh O_j into fp32 registers with the usual
+//                             running-max correction.  Rescaling in registers means the
+//                             tensor core never has to wait for a TMEM read-modify-write.
+// Heavy (late) query tiles are scheduled first.  2 CTAs per SM overlap each other's phases.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "tc_gemm.cuh"
+
+namespace b2p {
+namespace attn {
+
+using namespace tc;
+
+constexpr int BQ = 128, BKV = 64, HD = 64;
+constexpr int Q_BYTES = BQ * 128, KV_BYTES = BKV * 128, P_BYTES = BQ * 128;
+constexpr int KV_STAGES = 2;
+
+struct Smem {
+  unsigned char q[Q_BYTES];
+  unsigned char k[KV_STAGES][KV_BYTES];
+  unsigned char v[KV_STAGES][KV_BYTES];
+  unsigned char p[P_BYTES];
+  uint64_t q_full, kv_full[KV_STAGES], kv_empty[KV_STAGES], s_full, p_full, o_full;
+  uint32_t tmem_slot;
+};
+constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
+constexpr int THREADS = 192;
+
+// bf16 operands, fp32 accumulate; b_mn_major selects an MN-major B operand (V tile: d contiguous)
+__host__ __device__ constexpr uint32_t idesc_bf16(int m, int n, bool b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (b_mn_major ? (1u << 16) : 0u) |
+         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+__global__ void __launch_bounds__(THREADS, 2)
+attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 cols, 128 rows] over qkv
+                    const __grid_constant__ CUtensorMap tmap_kv,    // box [64 cols,  64 rows] over qkv
+                    __nv_bfloat16* __restrict__ y, int T, int C) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_qt = gridDim.x;
+  const int qt = n_qt - 1 - blockIdx.x;                 // heavy tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qt * BQ;
+  const int row0 = b * T;                                // first row of this sequence in qkv
+  const int n_kv = min((q0 + BQ + BKV - 1) / BKV, (T + BKV - 1) / BKV);   // causal: keys <= last query
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_q)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_kv)) : "memory");
+    mbar_init(&s.q_full, 1);
+    for (int i = 0; i < KV_STAGES; ++i) { mbar_init(&s.kv_full[i], 1); mbar_init(&s.kv_empty[i], 1); }
+    mbar_init(&s.s_full, 1);
+    mbar_init(&s.p_full, 4);
+    mbar_init(&s.o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(&s.tmem_slot, 128);                       // S: cols 0..63, O: cols 64..127
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s.tmem_slot;
+  const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 64;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      mbar_expect_tx(&s.q_full, Q_BYTES);
+      tma_load_2d(s.q, &tmap_q, &s.q_full, h * HD, row0 + q0);
+    }
+    uint32_t stage = 0, phase = 0;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s.kv_empty[stage], phase ^ 1);
+      if (lane == 0) {
+        mbar_expect_tx(&s.kv_full[stage], 2 * KV_BYTES);
+        tma_load_2d(s.k[stage], &tmap_kv, &s.kv_full[stage], C + h * HD, row0 + j * BKV);
+        tma_load_2d(s.v[stage], &tmap_kv, &s.kv_full[stage], 2 * C + h * HD, row0 + j * BKV);
+      }
+      __syncwarp();
+      if (++stage == KV_STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc_s = idesc_bf16(BQ, BKV, false);
+    constexpr uint32_t idesc_o = idesc_bf16(BQ, HD, true);
+    mbar_wait(&s.q_full, 0);
+    uint32_t stage = 0, phase = 0;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s.kv_full[stage], phase);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint64_t dq = make_desc_sw128(smem_u32(s.q)), dk = make_desc_sw128(smem_u32(s.k[stage]));
+#pragma unroll
+        for (int k = 0; k < HD / 16; ++k) umma<0>(tmem_s, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+        umma_commit(&s.s_full);
+      }
+      __syncwarp();
+      mbar_wait(&s.p_full, j & 1);                       // P_j is in smem (and S, O_{j-1} have been read)
+      tc_fence_after();
+      if (lane == 0) {
+        const uint64_t dp = make_desc_sw128(smem_u32(s.p)), dv = make_desc_sw128(smem_u32(s.v[stage]));
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k)               // A: +32 B per 16 keys; B (MN-major): +16 key rows = 2048 B
+          umma<0>(tmem_o, dp + 2 * k, dv + 128 * k, idesc_o, k != 0);
+        umma_commit(&s.o_full);
+        umma_commit(&s.kv_empty[stage]);
+      }
+      __syncwarp();
+      if (++stage == KV_STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    // ===================== softmax / accumulate (one query row per thread) =====================
+    const int qw = warp & 3;                             // TMEM lane quarter
+    const int r = qw * 32 + lane;                        // row within the tile
+    const int qi = q0 + r;                               // query position in the sequence
+    const uint32_t lane_sel = static_cast<uint32_t>(qw * 32) << 16;
+    constexpr float kScale = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
+    float o[HD];
+#pragma unroll
+    for (int d = 0; d < HD; ++d) o[d] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    unsigned char* prow = s.p + r * 128;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s.s_full, j & 1);
+      tc_fence_after();
+      uint32_t sr[64];
+      {
+        uint32_t a[32], c[32];
+        tmem_ld32(tmem_s + lane_sel, a);
+        tmem_ld32(tmem_s + lane_sel + 32, c);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) { sr[i] = a[i]; sr[32 + i] = c[i]; }
+      }
+      const int k0 = j * BKV;
+      const bool diag = k0 + BKV - 1 > q0;               // tile may contain keys beyond some query of the tile
+      float mx = m_run;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        float v = __uint_as_float(sr[i]) * kScale;
+        if (diag && k0 + i > qi) v = -INFINITY;
+        sr[i] = __float_as_uint(v);
+        mx = fmaxf(mx, v);
+      }
+      // (key 0 is never masked for a real query, so mx is finite whenever it matters)
+      const float corr = exp2f(m_run - mx);
+      float psum = 0.f;
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float p0 = exp2f(__uint_as_float(sr[2 * i]) - mx);
+        const float p1 = exp2f(__uint_as_float(sr[2 * i + 1]) - mx);
+        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+        // the row sum uses the bf16-rounded probabilities: numerator and denominator match
+        psum += __low2float(pb) + __high2float(pb);
+        pk[i] = *reinterpret_cast<const uint32_t*>(&pb);
+      }
+      l_run = l_run * corr + psum;
+      // O_{j-1} must have been folded in before P (and, via p_full, the next PV MMA) may
+      // overwrite TMEM O: it was, at the end of the previous iteration.
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(prow + ((c ^ (r & 7)) * 16)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.p_full);
+      // rescale what is accumulated so far while the tensor core runs P_j V_j
+#pragma unroll
+      for (int d = 0; d < HD; ++d) o[d] *= corr;
+      m_run = mx;
+      mbar_wait(&s.o_full, j & 1);
+      tc_fence_after();
+      {
+        uint32_t a[32], c[32];
+        tmem_ld32(tmem_o + lane_sel, a);
+        tmem_ld32(tmem_o + lane_sel + 32, c);
+        tmem_ld_wait();
+#pragma unroll
+        for (int d = 0; d < 32; ++d) { o[d] += __uint_as_float(a[d]); o[32 + d] += __uint_as_float(c[d]); }
+      }
+    }
+    if (qi < T) {
+      const float inv = 1.0f / l_run;
+      __nv_bfloat16* yr = y + (static_cast<size_t>(row0 + qi)) * C + h * HD;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const __nv_bfloat162 t2 = __floats2bfloat162_rn(o[8 * c + 2 * e] * inv, o[8 * c + 2 * e + 1] * inv);
+          w[e] = *reinterpret_cast<const uint32_t*>(&t2);
+        }
+        *reinterpret_cast<uint4*>(yr + 8 * c) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 128);
+}
+
+// qkv: bf16 [M, 3C]; y: bf16 [M, C]
+inline int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* y, int B, int T, int C, int H,
+                               cudaStream_t st) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B2P_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !configured[dev]) {
+    B2P_CUDA(cudaFuncSetAttribute(attention_causal_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    configured[dev] = true;
+  }
+  const int64_t M = static_cast<int64_t>(B) * T;
+  CUtensorMap tq, tkv;
+  {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return fail(B2P_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t gdim[2] = {(cuuint64_t)(3 * C), (cuuint64_t)M};
+    cuuint64_t gstride[1] = {(cuuint64_t)(3 * C) * 2};
+    cuuint32_t estr[2] = {1, 1};
+    cuuint32_t boxq[2] = {64, (cuuint32_t)BQ}, boxkv[2] = {64, (cuuint32_t)BKV};
+    CUresult r1 = enc(&tq, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(qkv), gdim, gstride, boxq, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r2 = enc(&tkv, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(qkv), gdim, gstride, boxkv, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r1 != CUDA_SUCCESS || r2 != CUDA_SUCCESS)
+      return fail(B2P_ECUDA, "cuTensorMapEncodeTiled (attention) failed: %d / %d", (int)r1, (int)r2);
+  }
+  dim3 grid(ceil_div(T, BQ), H, B);
+  B2P_LAUNCH(attention_causal_tc, grid, THREADS, SMEM_BYTES, st, tq, tkv, y, T, C);
+  return 0;
+}
+
+}  // namespace attn
+}  // namespace b2p

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <new>
 
+#include "attn_tc.cuh"
 #include "cifar_simt.cuh"
 #include "cifar_tc.cuh"
 #include "common.cuh"
@@ -234,13 +235,14 @@ int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cu
     float* x1 = st->ws_x[0];
     float* x2 = (i + 1 == nb) ? final_out : st->ws_x[1];
     B2P_TRY(layernorm(st, cur, k.ln1_w, k.ln1_b, st->ws_ln, M, C, s));
-    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, k.attn_w, k.attn_b, nullptr, st->ws_qkv, false, M, 3 * C, C, s));
-    dim3 agrid(ceil_div(T, 64), H, B);
-    if (bf)
-      B2P_LAUNCH(attention_causal_f32<__nv_bfloat16>, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv,
-                 reinterpret_cast<__nv_bfloat16*>(st->ws_att), T, C);
-    else
+    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, k.attn_w, k.attn_b, nullptr, st->ws_qkv, bf, M, 3 * C, C, s));
+    if (bf) {
+      B2P_TRY(attn::launch_attention_tc(reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
+                                        reinterpret_cast<__nv_bfloat16*>(st->ws_att), B, T, C, H, s));
+    } else {
+      dim3 agrid(ceil_div(T, 64), H, B);
       B2P_LAUNCH(attention_causal_f32<float>, agrid, 256, sizeof(AttnSmem), s, st->ws_qkv, st->ws_att, T, C);
+    }
     B2P_TRY(stage_linear(st, EPI_NONE, st->ws_att, k.proj_w, k.proj_b, cur, x1, false, M, C, C, s));
     B2P_TRY(layernorm(st, x1, k.ln2_w, k.ln2_b, st->ws_ln, M, C, s));
     B2P_TRY(stage_linear(st, EPI_GELU, st->ws_ln, k.fc_w, k.fc_b, nullptr, st->ws_h, bf, M, 4 * C, C, s));

@@ -1,0 +1,150 @@
+"""BASELINE config 5: inter-stage activation handoff sweep, 64 KiB .. 256 MiB.
+
+Run with 2 ranks on one box:
+  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 scripts/handoff_sweep.py
+Rank 1 owns the ring (consumer), rank 0 produces.  For every size the payload is a counter
+pattern verified by checksum on the consumer; bandwidth = bytes / device time (CUDA events on
+the producer stream, max over ranks).  Three transports are compared:
+  ring/copy_engine  cudaMemcpyAsync into the mapped slot
+  ring/sm_copy      SM copy kernel with 128-bit peer stores
+  nccl send/recv    torch.distributed (the library baseline)
+plus, on rank 0's host cores, the reference's own hop (tobytes -> TensorRequest -> gRPC loopback
+SendTensor -> frombuffer().copy(), node.py:73-89,45-48) with the unmodified 4 MiB cap and with
+the cap raised in the harness only.
+"""
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+import dnn_b200 as engine
+from importlib import import_module
+
+Ring = import_module("distributed-neural-networks_b200.handoff").Ring
+SIZES = [64 << 10, 256 << 10, 1 << 20, 4 << 20, 16 << 20, 64 << 20, 256 << 20]
+
+
+def reference_hop(sizes, raise_cap):
+    """The reference's serialisation path over a real localhost gRPC channel."""
+    import grpc
+    from concurrent import futures
+    w = engine.wire
+
+    class Sink(w.NodeServiceServicer):
+        def SendTensor(self, request, context):
+            a = np.frombuffer(request.tensor.tensor_data, dtype=np.dtype(request.tensor.dtype)).reshape(
+                tuple(request.tensor.shape)).copy()
+            return w.TensorResponse(status=f"ok {a.shape[0]}")
+
+    opts = [("grpc.max_send_message_length", -1), ("grpc.max_receive_message_length", -1)] if raise_cap else []
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=1), options=opts)
+    w.add_NodeServiceServicer_to_server(Sink(), server)
+    port = server.add_insecure_port("127.0.0.1:0")
+    server.start()
+    out = {}
+    try:
+        for n in sizes:
+            if n > (64 << 20):
+                continue
+            a = np.arange(n // 4, dtype=np.float32)
+            reps = 3 if n >= (16 << 20) else 10
+            try:
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    with grpc.insecure_channel(f"127.0.0.1:{port}", options=opts) as ch:     # new channel per hop
+                        stub = w.NodeServiceStub(ch)
+                        stub.SendTensor(w.TensorRequest(request_id="s", tensor=w.Tensor(
+                            tensor_data=a.tobytes(), shape=list(a.shape), dtype=str(a.dtype))))
+                out[n] = n * reps / (time.perf_counter() - t0) / 1e9
+            except grpc.RpcError as e:
+                out[n] = f"fails: {e.code().name}"
+    finally:
+        server.stop(0)
+    return out
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    assert world == 2
+    results = []
+    stream = torch.cuda.Stream()
+    for n in SIZES:
+        reps = 20 if n <= (16 << 20) else 6
+        slots = 2
+        ring = handle = None
+        if rank == 1:
+            ring = Ring.create(local, slots, n)
+            handle = ring.export()
+        hs = [None, None]
+        dist.all_gather_object(hs, handle)
+        if rank == 0:
+            ring = Ring.open(hs[1], local, slots, n)
+        payload = (torch.arange(n // 8, dtype=torch.int64, device=dev) * 2654435761) if rank == 0 else None
+        want = int(((torch.arange(n // 8, dtype=torch.int64, device=dev) * 2654435761).sum()).item())
+        row = {"bytes": n}
+        seq = 0
+        for mode in ("copy_engine", "sm_copy"):
+            if rank == 0:
+                ring.set_mode(mode)
+            ok = True
+            torch.cuda.synchronize(); dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(stream):
+                e0.record(stream)
+                for i in range(reps):
+                    if rank == 0:
+                        ring.send(payload.data_ptr(), n, seq, stream.cuda_stream)
+                    else:
+                        ptr = ring.recv(seq, stream.cuda_stream)
+                        if i == reps - 1:
+                            class R:  # noqa
+                                __cuda_array_interface__ = {"shape": (n // 8,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+                            got = int(torch.as_tensor(R(), device=dev).sum().item())
+                            ok = got == want
+                        ring.release(seq, stream.cuda_stream)
+                    seq += 1
+                e1.record(stream)
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1), 0.0 if ok else 1.0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            row[f"ring_{mode}_GBps"] = n * reps / (float(t[0]) * 1e-3) / 1e9
+            row[f"ring_{mode}_ok"] = float(t[1]) == 0.0
+        # library baseline: NCCL send/recv
+        buf = payload if rank == 0 else torch.empty(n // 8, dtype=torch.int64, device=dev)
+        for _ in range(2):
+            dist.send(buf, 1) if rank == 0 else dist.recv(buf, 0)
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            dist.send(buf, 1) if rank == 0 else dist.recv(buf, 0)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        row["nccl_sendrecv_GBps"] = n * reps / (float(t[0]) * 1e-3) / 1e9
+        results.append(row)
+        ring.close()
+        dist.barrier()
+    if rank == 0:
+        ref = reference_hop(SIZES, raise_cap=False)
+        ref_raised = reference_hop(SIZES, raise_cap=True)
+        for row in results:
+            row["reference_grpc_GBps"] = ref.get(row["bytes"], "not run (>64 MiB)")
+            row["reference_grpc_cap_raised_GBps"] = ref_raised.get(row["bytes"], "not run (>64 MiB)")
+        print(json.dumps({"handoff_sweep": results, "n_gpus": 2, "host_cores": os.cpu_count()}, indent=1))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
