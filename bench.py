@@ -280,7 +280,9 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["engine", "reference"], default="engine")
-    ap.add_argument("--math", default="fp32", choices=["fp32", "tf32x3", "tf32", "bf16"])
+    ap.add_argument("--math", default="tf32x3", choices=["fp32", "tf32x3", "tf32"],
+                    help="tf32x3 (default): tensor-core parity mode, fp32-grade (split-fp16 conv2, 3xTF32 fc1); "
+                         "fp32: CUDA-core reference mode; tf32: single-pass fc1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernel by kernel instead of replaying CUDA graphs")
     args = ap.parse_args()

@@ -17,10 +17,11 @@ from .stages import (MODEL_PARTS_CLASSES, EngineStage, ModelPart0, ModelPart0_2N
                      NeuralNetwork, gpt_parts_for)
 from .topology import NodeConfig, Topology, load_config
 from . import wire
+from . import handoff, pipeline, service
 
 __all__ = [
     "EngineError", "launch_count", "GPT", "GPTConfig", "GPT2_SMALL", "GPT2_MEDIUM",
     "MODEL_PARTS_CLASSES", "EngineStage", "ModelPart0", "ModelPart0_2Node", "ModelPart1_2Node",
     "ModelPartFinal_GPT", "ModelPartIntermediate", "NeuralNetwork", "gpt_parts_for",
-    "NodeConfig", "Topology", "load_config", "wire",
+    "NodeConfig", "Topology", "load_config", "wire", "handoff", "pipeline", "service",
 ]

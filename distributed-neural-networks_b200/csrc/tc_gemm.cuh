@@ -8,14 +8,15 @@
 // contraction of the GPT parts (c_attn, attn.c_proj, mlp.c_fc, mlp.c_proj, lm_head;
 // oracle/gpt_model.py) and fc1 of the CIFAR part 1 (cifar_model_parts.py:55).
 //
-// Structure (one CTA per SM, persistent over output tiles, 192 threads):
+// Structure (one CTA per SM, persistent over output tiles, 320 threads):
 //   warp 0      TMA producer : cp.async.bulk.tensor 2-D, 128B-swizzled boxes
 //                              A [128 x 128B] + W [BN x 128B] per stage, mbarrier tx
 //   warp 1      MMA issuer   : one lane issues tcgen05.mma.cta_group::1 (M=128, N=BN),
 //                              accumulators in TMEM, 2 accumulator stages so the
 //                              epilogue of tile i overlaps the MMAs of tile i+1
-//   warps 2..5  epilogue     : tcgen05.ld 32x32b -> bias/activation in registers ->
-//                              per-warp smem transpose -> coalesced stores (+residual)
+//   warps 2..9  epilogue     : tcgen05.ld 32x32b -> bias/activation in registers ->
+//                              per-warp smem transpose -> coalesced stores (+residual);
+//                              two warps per TMEM lane quarter, half the columns each
 // Ragged M, N and K need no masks on the load side: TMA zero-fills out-of-bounds box
 // elements; stores are guarded.
 //
@@ -169,7 +170,7 @@ enum { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 
 struct EpiParams {
   const float* bias;     // [N] or null
-  const float* res;      // [M, ld_res] fp32 or null: added AFTER the activation
+  const float* res;      // [M, ld_res] fp32 or null: added AFTER the activation; must not overlap `out`
   void* out;             // [M, ldo] fp32 or bf16
   int64_t ldo, ld_res;
   int out_bf16;
@@ -189,16 +190,16 @@ struct GemmCfg {
   static constexpr int B_BYTES = B_PLANE * (SPLIT ? 2 : 1);
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = SPLIT ? (BN <= 128 ? 3 : 2) : (BN <= 128 ? 5 : 4);
-  static constexpr int EPI_PITCH = 36;       // floats; 16-byte aligned rows, conflict-free float4 stores
-  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+  static constexpr int EPI_PITCH = 20;       // floats: 16 columns + pad; 16-byte aligned rows, conflict-free float4 stores
+  static constexpr int EPI_BYTES = 8 * 32 * EPI_PITCH * 4;
   static constexpr int BAR_BYTES = 256;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
   static constexpr int TMEM_COLS = 2 * BN;     // two accumulator stages (power of two >= 32)
-  static constexpr int THREADS = 192;
+  static constexpr int THREADS = 320;     // TMA warp, MMA warp, 8 epilogue warps
 };
 
 template <int KIND, int BN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
           const __grid_constant__ CUtensorMap tmap_a_lo, const __grid_constant__ CUtensorMap tmap_w_lo,
           EpiParams ep, int M, int N, int K, int splits, int kb_per_split) {
@@ -226,7 +227,7 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_a)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w)) : "memory");
     for (int i = 0; i < Cfg::STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 8); }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -298,16 +299,22 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..9) =====================
+    // Eight warps: two per TMEM lane quarter, each taking half of the tile's columns, so a
+    // heavy epilogue (erf-GELU, residual add) keeps up with short-K main loops.  Data path per
+    // 32-column chunk: tcgen05.ld -> registers (bias, activation) -> per-warp [32][20] smem
+    // transpose in two 16-column halves -> row-contiguous 16-byte stores.
     constexpr int P = Cfg::EPI_PITCH;
     const int q = warp & 3;                         // TMEM lane quarter this warp may read
-    float* stg = epi_smem + (warp - 2) * 32 * P;    // private [32][P] transpose buffer
+    const int ew = warp - 2;                        // 0..7
+    const int col_half = ew >> 2;                   // which half of the tile's columns
+    float* stg = epi_smem + ew * 32 * P;
     const bool vec_f32 = !ep.out_bf16 && (ep.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
                          (ep.split_stride & 3) == 0 &&
                          (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
-    const bool vec_bf16 = ep.out_bf16 && (ep.ldo & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
-                          (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
+    const bool vec_bf16 = ep.out_bf16 && (ep.ldo & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 && !ep.res;
     const bool bias_vec = ep.bias && (reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0;
+    constexpr int CHUNKS = BN / 64;                 // 32-column chunks per warp
     uint32_t acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       const int z = item % splits, tile = item / splits;
@@ -317,105 +324,108 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
       const int row_base = m0 + q * 32;
       float* out_f32 = static_cast<float*>(ep.out) + static_cast<int64_t>(z) * ep.split_stride;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int cc = 0; cc < CHUNKS; ++cc) {
+        const int c = col_half * CHUNKS + cc;
         const int col0 = n0 + c * 32;
         if (col0 >= N) break;                        // warp-uniform
         uint32_t r[32];
         tmem_ld32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
-        tmem_ld_wait();
         const bool full_cols = col0 + 32 <= N;
+        // Residual values are fetched NOW -- while the TMEM load is in flight and before any store
+        // of this chunk.  A load issued after a may-alias store has to wait for it; leaving the
+        // loads inside the store loop serialised eight ~700-cycle round trips per chunk.
+        const bool res_vec = ep.res != nullptr && vec_f32 && full_cols;
+        float4 rv[2][4];
+        if (res_vec) {
+          const int cg = (lane & 3) * 4;
+#pragma unroll
+          for (int sub = 0; sub < 2; ++sub)
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+              const int row = row_base + it * 8 + (lane >> 2);
+              rv[sub][it] = row < M ? __ldg(reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res +
+                                                                              col0 + sub * 16 + cg))
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        tmem_ld_wait();
+        float v[32];
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
-          float v[4] = {__uint_as_float(r[4 * j4]), __uint_as_float(r[4 * j4 + 1]), __uint_as_float(r[4 * j4 + 2]),
-                        __uint_as_float(r[4 * j4 + 3])};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) v[4 * j4 + e] = __uint_as_float(r[4 * j4 + e]);
           if (ep.bias) {
             if (bias_vec && full_cols) {
               const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col0) + j4);
-              v[0] += b4.x; v[1] += b4.y; v[2] += b4.z; v[3] += b4.w;
+              v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
             } else {
 #pragma unroll
               for (int e = 0; e < 4; ++e)
-                if (col0 + 4 * j4 + e < N) v[e] += __ldg(ep.bias + col0 + 4 * j4 + e);
-            }
-          }
-          if (ep.act == ACT_RELU) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
-          } else if (ep.act == ACT_GELU) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) v[e] = gelu_erf(v[e]);
-          }
-          *reinterpret_cast<float4*>(&stg[lane * P + 4 * j4]) = make_float4(v[0], v[1], v[2], v[3]);
-        }
-        __syncwarp();
-        if (vec_f32 && full_cols) {
-          // 8 lanes x 16 B cover one 128-byte row segment; 4 rows per instruction
-          const int cg = (lane & 7) * 4;
-#pragma unroll
-          for (int it = 0; it < 8; ++it) {
-            const int rr = it * 4 + (lane >> 3), row = row_base + rr;
-            if (row < M) {
-              float4 v = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
-              if (ep.res) {
-                const float4 rv = *reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res + col0 + cg);
-                v.x += rv.x; v.y += rv.y; v.z += rv.z; v.w += rv.w;
-              }
-              *reinterpret_cast<float4*>(out_f32 + static_cast<int64_t>(row) * ep.ldo + col0 + cg) = v;
-            }
-          }
-        } else if (vec_bf16 && full_cols) {
-          // 4 lanes x 16 B (8 bf16) cover one 64-byte row segment; 8 rows per instruction
-          __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
-          const int cg = (lane & 3) * 8;
-#pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int rr = it * 8 + (lane >> 2), row = row_base + rr;
-            if (row < M) {
-              float4 a = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
-              float4 b = *reinterpret_cast<const float4*>(&stg[rr * P + cg + 4]);
-              if (ep.res) {
-                const float4* rp = reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res + col0 + cg);
-                const float4 ra = rp[0], rb = rp[1];
-                a.x += ra.x; a.y += ra.y; a.z += ra.z; a.w += ra.w;
-                b.x += rb.x; b.y += rb.y; b.z += rb.z; b.w += rb.w;
-              }
-              __nv_bfloat162 p0 = __floats2bfloat162_rn(a.x, a.y), p1 = __floats2bfloat162_rn(a.z, a.w);
-              __nv_bfloat162 p2 = __floats2bfloat162_rn(b.x, b.y), p3 = __floats2bfloat162_rn(b.z, b.w);
-              uint4 pk;
-              pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
-              pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
-              *reinterpret_cast<uint4*>(out + static_cast<int64_t>(row) * ep.ldo + col0 + cg) = pk;
-            }
-          }
-        } else if (!ep.out_bf16) {
-          const int col = col0 + lane;
-#pragma unroll 4
-          for (int rr = 0; rr < 32; ++rr) {
-            const int row = row_base + rr;
-            if (row < M && col < N) {
-              float v = stg[rr * P + lane];
-              if (ep.res) v += ep.res[static_cast<int64_t>(row) * ep.ld_res + col];
-              out_f32[static_cast<int64_t>(row) * ep.ldo + col] = v;
-            }
-          }
-        } else {
-          __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
-          const int half = lane >> 4, cj = (lane & 15) * 2, col = col0 + cj;
-#pragma unroll 4
-          for (int it = 0; it < 16; ++it) {
-            const int rr = it * 2 + half, row = row_base + rr;
-            if (row < M && col < N) {                // N is even for bf16 outputs (checked on the host)
-              float v0 = stg[rr * P + cj], v1 = stg[rr * P + cj + 1];
-              if (ep.res) {
-                const float* rp = ep.res + static_cast<int64_t>(row) * ep.ld_res + col;
-                v0 += rp[0]; v1 += rp[1];
-              }
-              *reinterpret_cast<__nv_bfloat162*>(out + static_cast<int64_t>(row) * ep.ldo + col) =
-                  __floats2bfloat162_rn(v0, v1);
+                if (col0 + 4 * j4 + e < N) v[4 * j4 + e] += __ldg(ep.bias + col0 + 4 * j4 + e);
             }
           }
         }
-        __syncwarp();
+        if (ep.act == ACT_RELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (ep.act == ACT_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        }
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          const int cs = col0 + sub * 16;
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4)
+            *reinterpret_cast<float4*>(&stg[lane * P + 4 * j4]) =
+                make_float4(v[sub * 16 + 4 * j4], v[sub * 16 + 4 * j4 + 1], v[sub * 16 + 4 * j4 + 2], v[sub * 16 + 4 * j4 + 3]);
+          __syncwarp();
+          if (vec_f32 && full_cols) {
+            // 4 lanes x 16 B = one 64-byte row segment; 8 rows per instruction
+            const int cg = (lane & 3) * 4;
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+              const int rr = it * 8 + (lane >> 2), row = row_base + rr;
+              if (row < M) {
+                float4 o = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+                if (res_vec) { o.x += rv[sub][it].x; o.y += rv[sub][it].y; o.z += rv[sub][it].z; o.w += rv[sub][it].w; }
+                *reinterpret_cast<float4*>(out_f32 + static_cast<int64_t>(row) * ep.ldo + cs + cg) = o;
+              }
+            }
+          } else if (vec_bf16 && full_cols) {
+            // 2 lanes x 16 B (8 bf16) = one 32-byte row segment; 16 rows per instruction
+            __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
+            const int cg = (lane & 1) * 8;
+#pragma unroll
+            for (int it = 0; it < 2; ++it) {
+              const int rr = it * 16 + (lane >> 1), row = row_base + rr;
+              if (row < M) {
+                const float4 x0 = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+                const float4 x1 = *reinterpret_cast<const float4*>(&stg[rr * P + cg + 4]);
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(x0.x, x0.y), p1 = __floats2bfloat162_rn(x0.z, x0.w);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(x1.x, x1.y), p3 = __floats2bfloat162_rn(x1.z, x1.w);
+                uint4 pk;
+                pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+                pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+                *reinterpret_cast<uint4*>(out + static_cast<int64_t>(row) * ep.ldo + cs + cg) = pk;
+              }
+            }
+          } else {
+            // generic path (ragged N, unaligned rows, bf16 + residual): one element per lane-iteration
+            const int cj = lane & 15, col = cs + cj;
+#pragma unroll 4
+            for (int it = 0; it < 16; ++it) {
+              const int rr = it * 2 + (lane >> 4), row = row_base + rr;
+              if (row < M && col < N) {
+                float o = stg[rr * P + cj];
+                if (ep.res) o += ep.res[static_cast<int64_t>(row) * ep.ld_res + col];
+                if (ep.out_bf16) static_cast<__nv_bfloat16*>(ep.out)[static_cast<int64_t>(row) * ep.ldo + col] = __float2bfloat16_rn(o);
+                else out_f32[static_cast<int64_t>(row) * ep.ldo + col] = o;
+              }
+            }
+          }
+          __syncwarp();
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -449,7 +459,7 @@ inline EncodeTiledFn encode_tiled_fn() {
 }
 
 // 2-D K-major tensor [rows, k] with row pitch ld (elements); box = [128 bytes of K] x [box_rows].
-inline int make_tmap(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t k, int64_t ld, int box_rows) {
+inline int make_tmap_uncached(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t k, int64_t ld, int box_rows) {
   if (kind == 2) kind = 1;     // tf32x3 planes are plain fp32 arrays
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return fail(B2P_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
@@ -466,6 +476,24 @@ inline int make_tmap(CUtensorMap* map, int kind, const void* ptr, int64_t rows, 
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(B2P_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+// cuTensorMapEncodeTiled costs a few microseconds of host time; weights and workspace buffers
+// recur with identical geometry on every call, so encoded maps are kept in a small per-thread
+// direct-mapped cache keyed by everything that goes into the encoding.
+inline int make_tmap(CUtensorMap* map, int kind, const void* ptr, int64_t rows, int64_t k, int64_t ld, int box_rows) {
+  struct Entry { const void* ptr; int64_t rows, k, ld; int kind, box; bool valid; CUtensorMap map; };
+  static thread_local Entry cache[256] = {};
+  const uint64_t h = (reinterpret_cast<uintptr_t>(ptr) >> 8) * 0x9E3779B97F4A7C15ull + (uint64_t)rows * 31 + (uint64_t)k * 17 +
+                     (uint64_t)box_rows * 7 + (uint64_t)kind;
+  Entry& e = cache[(h >> 32) & 255];
+  if (e.valid && e.ptr == ptr && e.rows == rows && e.k == k && e.ld == ld && e.kind == kind && e.box == box_rows) {
+    *map = e.map;
+    return 0;
+  }
+  B2P_TRY(make_tmap_uncached(map, kind, ptr, rows, k, ld, box_rows));
+  e.ptr = ptr; e.rows = rows; e.k = k; e.ld = ld; e.kind = kind; e.box = box_rows; e.map = *map; e.valid = true;
   return 0;
 }
 

@@ -241,3 +241,59 @@ def bench_main(args) -> int:
     dist.barrier()
     dist.destroy_process_group()
     return 0
+
+
+class GptRankPipeline:
+    """BASELINE configs 3/4: rank k runs the reference's part k (ModelPart0 | ModelPartIntermediate*
+    | ModelPartFinal_GPT, partitions/gpt_model_parts.py) over a contiguous layer range; hidden
+    states [microbatch*T, C] fp32 travel through peer-memory rings.  Each stage's last kernel
+    (the mlp.c_proj GEMM epilogue with the fused residual add) stores straight into the next
+    GPU's ring slot."""
+
+    def __init__(self, role: RankRole, device: torch.device, model, math: str, mb_seqs: int, seq: int,
+                 ranges=None, slots: int = 4, group=None):
+        import dnn_b200 as engine
+        from .handoff import Ring
+        self.role, self.dev, self.mb, self.seq_len = role, device, mb_seqs, seq
+        cfg = model.config
+        self.cfg = cfg
+        self.stream = torch.cuda.Stream(device=device)
+        parts = engine.gpt_parts_for(model, role.stages, math=math, max_tokens=mb_seqs * seq, ranges=ranges)
+        self.part = parts[role.stage].to(device).eval()
+        slot_bytes = mb_seqs * seq * cfg.n_embd * 4
+        self.ring_in = self.ring_out = None
+        mine = None
+        if role.stage > 0:
+            self.ring_in = Ring.create(device.index, slots, slot_bytes)
+            mine = self.ring_in.export()
+        handles = exchange_handles(mine, group)
+        if role.next_rank is not None:
+            self.ring_out = Ring.open(handles[role.next_rank], device.index, slots, slot_bytes)
+        self.seq_no = 0
+        self.is_last = role.next_rank is None
+        if self.is_last:
+            self.ids = torch.empty((mb_seqs, seq), dtype=torch.int64, device=device)
+            self.logits = None
+
+    def step(self, idx_batch: torch.Tensor | None, n_microbatches: int, head: str = "ids"):
+        """One batch = n_microbatches microbatches of mb_seqs sequences through this rank's stage."""
+        import ctypes as C
+        from . import _lib
+        s = self.stream.cuda_stream
+        for i in range(n_microbatches):
+            src = self.ring_in.recv(self.seq_no, s) if self.ring_in else idx_batch[i * self.mb:].data_ptr()
+            if not self.is_last:
+                dst = self.ring_out.acquire(self.seq_no, s)
+                self.part.forward_ptr(src, dst, self.mb, self.seq_len, s)
+                self.ring_out.publish(self.seq_no, s)
+            elif head == "ids":
+                _lib.check(_lib.lib().b2p_stage_forward_argmax(self.part._handle, C.c_void_p(src),
+                                                               C.c_void_p(self.ids.data_ptr()), self.mb, self.seq_len,
+                                                               C.c_void_p(s)))
+            else:
+                if self.logits is None:
+                    self.logits = torch.empty((self.mb, self.seq_len, self.cfg.vocab_size), device=self.dev)
+                self.part.forward_ptr(src, self.logits.data_ptr(), self.mb, self.seq_len, s)
+            if self.ring_in:
+                self.ring_in.release(self.seq_no, s)
+            self.seq_no += 1

@@ -1,0 +1,123 @@
+"""The NodeService front door (reference: node.py:34-133 servicer + serve, :137-200 initiator).
+
+An unmodified ``node_service.proto`` client calls ``SendTensor`` on the first node exactly as
+it would on the reference; behind the door the request's tensor goes
+bytes -> pinned host buffer -> H2D -> every stage of the chain on the GPU(s) -> D2H -> bytes.
+There is no per-hop gRPC, no per-request channel and no host staging between stages; the
+protobuf ``Tensor`` survives only at the two ends of the pipe.
+
+What is mirrored from the reference so that clients and log scrapers see the same thing:
+  * status strings: the last node says ``[id] Processing complete. Prediction: <k>`` with k the
+    flat ``np.argmax`` of the whole output array (node.py:61-63); every node in front of it
+    wraps that as ``[id] Forwarded. Next node status: ...`` (node.py:86);
+  * failures never surface as gRPC errors: any exception becomes ``[id] Error: ...`` with no
+    ``result_tensor`` (node.py:96-105);
+  * ``HealthCheck`` answers True, ``SendMessage`` echoes (node.py:107-113).
+Deliberate differences: the message-size cap is lifted (the reference dies at 4 MiB),
+and one process serves the whole chain (stage k on GPU k) instead of one process per stage.
+"""
+from __future__ import annotations
+
+from concurrent import futures
+from typing import Callable, Sequence
+
+import numpy as np
+
+from . import wire
+
+
+class NodeServiceImpl(wire.NodeServiceServicer):
+    """``run`` maps the request ndarray to the chain's output ndarray (e.g. ``ChainRunner``)."""
+
+    def __init__(self, node_ids: Sequence[str], run: Callable[[np.ndarray], np.ndarray]):
+        self.node_ids = list(node_ids)          # this node first, then every downstream node
+        self.run = run
+
+    def _status(self, prediction: int) -> str:
+        status = f"[{self.node_ids[-1]}] Processing complete. Prediction: {prediction}"
+        for nid in reversed(self.node_ids[:-1]):
+            status = f"[{nid}] Forwarded. Next node status: {status}"
+        return status
+
+    def SendTensor(self, request, context):
+        me = self.node_ids[0]
+        try:
+            x = wire.tensor_to_ndarray(request.tensor)                      # node.py:45-47
+            y = np.ascontiguousarray(self.run(x))
+            status = self._status(int(np.argmax(y)))                        # node.py:61
+            return wire.TensorResponse(status=status, result_tensor=wire.ndarray_to_tensor(y))
+        except Exception as e:                                              # node.py:96-100
+            return wire.TensorResponse(status=f"[{me}] Error: {e}")
+
+    def HealthCheck(self, request, context):
+        return wire.HealthCheckResponse(is_healthy=True)
+
+    def SendMessage(self, request, context):
+        return wire.MessageReply(confirmation_text=f"[{self.node_ids[0]}] got msg '{request.message_text}'")
+
+
+class ChainRunner:
+    """Host tensor in, host tensor out, through a ``LocalPipeline`` (pinned staging, async copies).
+    Batches larger than the pipeline's capacity are fed in capacity-sized pieces."""
+
+    def __init__(self, pipeline, in_dtype=np.float32):
+        import torch
+        self.pipe, self.torch = pipeline, torch
+        self.in_dtype = np.dtype(in_dtype)
+        self.stage_in = torch.empty((pipeline.max_batch, *pipeline.in_shape), dtype=pipeline.in_dtype).pin_memory()
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        torch, p = self.torch, self.pipe
+        if x.dtype != self.in_dtype:
+            raise TypeError(f"expected a {self.in_dtype} tensor, got {x.dtype}")
+        if tuple(x.shape[1:]) != tuple(p.in_shape):
+            raise ValueError(f"expected input [B,{','.join(map(str, p.in_shape))}], got {list(x.shape)}")
+        outs = []
+        for lo in range(0, x.shape[0], p.max_batch):
+            n = min(p.max_batch, x.shape[0] - lo)
+            self.stage_in[:n].copy_(torch.from_numpy(x[lo:lo + n]))        # the one host copy (node.py:48 makes two)
+            outs.append(p.run_host(self.stage_in[:n], sync=True).numpy().copy())
+        return np.concatenate(outs) if len(outs) != 1 else outs[0]
+
+
+def build_cifar_chain(topology, node_id: str, math: str = "tf32x3", microbatch: int = 128, max_batch: int = 1024,
+                      state_dict=None):
+    """What node.py:294-318 does for every node from ``node_id`` to the end of the chain, in one
+    process: ``MODEL_PARTS_CLASSES[k](NeuralNetwork()).to(cuda:k')``, ``load_state_dict(strict=False)``,
+    ``eval()``.  Returns (servicer, pipeline)."""
+    import torch
+    from .pipeline import LocalPipeline
+    from .stages import MODEL_PARTS_CLASSES, NeuralNetwork
+    me = topology.resolve(node_id)
+    chain = topology.chain()[me.part_index:]
+    if state_dict is None:
+        state_dict = torch.load(topology.model_weights, map_location=torch.device("cpu"))   # node.py:296
+    full = NeuralNetwork()
+    n_gpu = torch.cuda.device_count()
+    parts = []
+    for n in chain:
+        cls = MODEL_PARTS_CLASSES.get(n["part_index"])                     # node.py:300
+        if cls is None:
+            raise KeyError(f"No model part class defined for index {n['part_index']}")
+        dev = n.get("device", n["part_index"] % max(n_gpu, 1))
+        part = cls(full, math=math).to(f"cuda:{dev}")
+        part.load_state_dict(state_dict, strict=False)                     # node.py:306
+        parts.append(part.eval())
+    shapes = {0: ((3, 32, 32), (4096,)), 1: ((4096,), (10,))}
+    in_shape = shapes[chain[0]["part_index"]][0]
+    out_shape = shapes[chain[-1]["part_index"]][1]
+    hidden = [shapes[n["part_index"]][1] for n in chain[:-1]]
+    pipe = LocalPipeline(parts, microbatch, in_shape, torch.float32, out_shape, hidden, max_batch)
+    return NodeServiceImpl([n["id"] for n in chain], ChainRunner(pipe)), pipe
+
+
+def serve(servicer, port: int, max_message_bytes: int = -1):
+    """node.py:114-133 with a blocking server; one worker keeps the reference's
+    one-request-at-a-time behaviour (node.py:53 blocks its event loop)."""
+    import grpc
+    opts = [("grpc.max_send_message_length", max_message_bytes), ("grpc.max_receive_message_length", max_message_bytes)]
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=1), options=opts)
+    wire.add_NodeServiceServicer_to_server(servicer, server)
+    bound = server.add_insecure_port(f"[::]:{port}")
+    server.start()
+    return server, bound

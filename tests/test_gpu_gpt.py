@@ -150,3 +150,47 @@ def test_tensor_core_modes_ragged(cuda_engine, mode, tol):
         ids = parts[-1].greedy_ids(x)
     assert (logits.cpu() - want).abs().max().item() <= tol
     assert torch.equal(ids, logits.argmax(-1))
+
+
+@pytest.mark.parametrize("mode,tol", [("bf16", 5e-2), ("tf32x3", 2e-4)])
+def test_gpt2_small_shape_one_sequence(cuda_engine, mode, tol):
+    """BASELINE config 3 geometry (C=768, H=12, T=1024, 50257-way head) at a size the CPU oracle
+    finishes in seconds: 2 blocks, one sequence, split into first | final.  bf16 exercises the
+    tensor-core attention kernel over 8 query tiles and 16 key tiles."""
+    cfg = gpt_model.GPTConfig(block_size=1024, vocab_size=50257, n_layer=2, n_head=12, n_embd=768)
+    sd = gpt_oracle.init_state_dict(cfg, seed=21)
+    idx = gpt_oracle.make_tokens(1, 1024, cfg.vocab_size, seed=8)
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    want = gpt_oracle.pipeline(idx, sd, cfg, 2)
+    model = _engine_model(cuda_engine, (1024, 50257, 2, 12, 768), sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math=mode, max_tokens=1024)]
+    with torch.no_grad():
+        hidden = parts[0](idx.cuda())
+        logits = parts[1](hidden)
+        ids = parts[1].greedy_ids(hidden)
+    err = (logits.cpu() - want).abs().max().item()
+    top2 = want.topk(2, -1).values
+    gap = top2[..., 0] - top2[..., 1]
+    decided = gap > 2 * tol
+    flips = int((ids.cpu()[decided] != want.argmax(-1)[decided]).sum())
+    print(f"\ngpt2-small geometry, {mode}: max|dlogit|={err:.3e}; decided {int(decided.sum())}/{decided.numel()} "
+          f"positions (gap>{2 * tol:g}), greedy-id flips among them: {flips}")
+    assert err <= tol
+    assert flips == 0
+    assert torch.equal(ids, logits.argmax(-1))
+
+
+def test_bf16_attention_ragged_lengths(cuda_engine):
+    """Sequence lengths that are not multiples of the 128-query / 64-key tiles, batch > 1
+    (a key tile then straddles the next sequence's rows and must be masked)."""
+    cfg = gpt_model.GPTConfig(block_size=512, vocab_size=512, n_layer=1, n_head=2, n_embd=128)
+    sd = gpt_oracle.init_state_dict(cfg, seed=5)
+    model = _engine_model(cuda_engine, (512, 512, 1, 2, 128), sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math="bf16", max_tokens=3 * 512)]
+    for t in (1, 63, 64, 65, 129, 200, 512):
+        idx = gpt_oracle.make_tokens(3, t, cfg.vocab_size, seed=t)
+        want = gpt_oracle.pipeline(idx, sd, cfg, 2)
+        with torch.no_grad():
+            got = parts[1](parts[0](idx.cuda()))
+        err = (got.cpu() - want).abs().max().item()
+        assert err <= 3e-2, f"T={t}: {err}"

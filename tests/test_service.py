@@ -1,0 +1,110 @@
+"""The NodeService front door.  CPU tests use a stand-in chain (host logic only: status
+strings, error folding, the lifted message cap); the GPU test serves the real CIFAR chain and
+replays the request recorded from the unmodified reference (tests/golden/cifar_grpc.npz)."""
+import os
+from importlib import import_module
+
+import numpy as np
+import pytest
+
+
+def _svc():
+    import dnn_b200  # noqa: F401
+    return import_module("distributed-neural-networks_b200.service")
+
+
+def _client(engine, port, big=False):
+    import grpc
+    opts = [("grpc.max_send_message_length", -1), ("grpc.max_receive_message_length", -1)] if big else []
+    ch = grpc.insecure_channel(f"127.0.0.1:{port}", options=opts)
+    return ch, engine.wire.NodeServiceStub(ch)
+
+
+def test_status_strings_and_error_folding(engine):
+    svc = _svc()
+    w = engine.wire
+
+    def chain(x):
+        if x.shape[0] == 3:
+            raise ValueError("boom")
+        return np.tile(np.arange(10, dtype=np.float32), (x.shape[0], 1))
+
+    servicer = svc.NodeServiceImpl(["node1", "node2"], chain)
+    server, port = svc.serve(servicer, 0)
+    try:
+        ch, stub = _client(engine, port)
+        x = np.zeros((2, 3, 32, 32), np.float32)
+        rep = stub.SendTensor(w.TensorRequest(request_id="a", tensor=w.ndarray_to_tensor(x)))
+        # node.py:61 takes the FLAT argmax: row 0 already holds the maximum 9
+        assert rep.status == "[node1] Forwarded. Next node status: [node2] Processing complete. Prediction: 9"
+        assert rep.HasField("result_tensor") and w.tensor_to_ndarray(rep.result_tensor).shape == (2, 10)
+        bad = stub.SendTensor(w.TensorRequest(request_id="b", tensor=w.ndarray_to_tensor(np.zeros((3, 1), np.float32))))
+        assert bad.status == "[node1] Error: boom" and not bad.HasField("result_tensor")
+        garbage = stub.SendTensor(w.TensorRequest(request_id="c", tensor=w.Tensor(tensor_data=b"123", shape=[2], dtype="float32")))
+        assert garbage.status.startswith("[node1] Error:") and not garbage.HasField("result_tensor")
+        assert stub.HealthCheck(w.Empty()).is_healthy is True
+        assert stub.SendMessage(w.MessageRequest(sender_id="c", message_text="hi")).confirmation_text == "[node1] got msg 'hi'"
+        ch.close()
+    finally:
+        server.stop(0)
+    single = svc.NodeServiceImpl(["only"], chain)
+    assert single._status(4) == "[only] Processing complete. Prediction: 4"
+
+
+def test_messages_beyond_the_reference_cap(engine):
+    """The reference cannot carry > 4 MiB; the front door can."""
+    svc = _svc()
+    w = engine.wire
+    servicer = svc.NodeServiceImpl(["n"], lambda x: x[:, :2].copy())
+    server, port = svc.serve(servicer, 0)
+    try:
+        ch, stub = _client(engine, port, big=True)
+        x = np.ones((300, 4096), np.float32)                 # 4.9 MB
+        rep = stub.SendTensor(w.TensorRequest(request_id="big", tensor=w.ndarray_to_tensor(x)))
+        assert rep.HasField("result_tensor"), rep.status
+        assert w.tensor_to_ndarray(rep.result_tensor).shape == (300, 2)
+        ch.close()
+    finally:
+        server.stop(0)
+
+
+@pytest.mark.gpu
+def test_cifar_chain_replays_the_reference_recording(cuda_engine, golden_dir, tmp_path):
+    import json
+    import torch
+    from oracle import cifar_oracle as co
+    svc = _svc()
+    w = cuda_engine.wire
+    g = np.load(os.path.join(golden_dir, "cifar_grpc.npz"))
+    sd = co.init_state_dict(int(g["weight_seed"]))
+    pth = tmp_path / "w.pth"
+    torch.save(sd, pth)
+    cfg = {"nodes": [{"id": "node1", "address": "127.0.0.1:0", "part_index": 0, "device": 0},
+                     {"id": "node2", "address": "127.0.0.1:0", "part_index": 1, "device": 0}],
+           "model_weights": str(pth), "num_parts": 2, "return_to_node_id": "node1"}
+    cpath = tmp_path / "config.json"
+    cpath.write_text(json.dumps(cfg))
+    topo = cuda_engine.load_config(str(cpath))
+    servicer, pipe = svc.build_cifar_chain(topo, "node1", math="tf32x3", microbatch=128, max_batch=256)
+    server, port = svc.serve(servicer, 0)
+    try:
+        ch, stub = _client(cuda_engine, port, big=True)
+        for b in (1, 4):
+            x = g[f"x{b}"]
+            rep = stub.SendTensor(w.TensorRequest(request_id=f"golden_{b}", tensor=w.ndarray_to_tensor(x)))
+            assert rep.status == str(g[f"status{b}"])          # byte-for-byte the reference's status line
+            got = w.tensor_to_ndarray(rep.result_tensor)
+            assert got.dtype == np.float32 and got.shape == (b, 10)
+            np.testing.assert_allclose(got, g[f"probs{b}"], rtol=0, atol=1e-5)
+        # a batch larger than the pipeline capacity and than the reference's 4 MiB cap
+        x = co.make_input(600, seed=12).numpy()
+        rep = stub.SendTensor(w.TensorRequest(request_id="big", tensor=w.ndarray_to_tensor(x)))
+        got = w.tensor_to_ndarray(rep.result_tensor)
+        want = co.full(torch.from_numpy(x), sd).numpy()
+        np.testing.assert_allclose(got, want, rtol=0, atol=1e-5)
+        assert rep.status.endswith(f"Prediction: {int(np.argmax(want))}") or np.abs(want - got).max() > 0
+        wrong = stub.SendTensor(w.TensorRequest(request_id="w", tensor=w.ndarray_to_tensor(np.zeros((2, 5), np.float32))))
+        assert wrong.status.startswith("[node1] Error:") and not wrong.HasField("result_tensor")
+        ch.close()
+    finally:
+        server.stop(0)
