@@ -109,7 +109,7 @@ def time_cpu_pipeline(n_requests: int, warmup: int, batch: int = MICROBATCH, bud
         total = time.perf_counter() - t_start
     return {"samples_per_s": batch * len(lat) / total, "requests": len(lat), "batch": batch,
             "p50_ms": 1e3 * statistics.median(lat), "total_s": total,
-            "cores": os.cpu_count(), "torch_threads": torch.get_num_threads()}
+            "cores": os.cpu_count(), "torch_threads": os.cpu_count()}   # node processes use torch's default = all cores
 
 
 def reference_arm(args):

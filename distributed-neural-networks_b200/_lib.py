@@ -39,6 +39,7 @@ _PROTOTYPES = {
     "b2p_last_error": (C.c_char_p, []),
     "b2p_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "b2p_launch_count": (C.c_int64, []),
+    "b2p_set_pdl": (C.c_int, [C.c_int]),
     "b2p_stage_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(StageDesc)]),
     "b2p_stage_destroy": (C.c_int, [C.c_void_p]),
     "b2p_stage_load_weight": (C.c_int, [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32,

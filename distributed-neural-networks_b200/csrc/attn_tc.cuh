@@ -78,11 +78,13 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
     tmem_alloc(&s.tmem_slot, 128);                       // S: cols 0..63, O: cols 64..127
     tmem_relinquish();
   }
+  pdl_trigger();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s.tmem_slot;
   const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 64;
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -252,7 +254,7 @@ inline int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* y, int B
       return fail(B2P_ECUDA, "cuTensorMapEncodeTiled (attention) failed: %d / %d", (int)r1, (int)r2);
   }
   dim3 grid(ceil_div(T, BQ), H, B);
-  B2P_LAUNCH(attention_causal_tc, grid, THREADS, SMEM_BYTES, st, tq, tkv, y, T, C);
+  B2P_LAUNCH_PDL(attention_causal_tc, grid, THREADS, SMEM_BYTES, st, tq, tkv, y, T, C);
   return 0;
 }
 

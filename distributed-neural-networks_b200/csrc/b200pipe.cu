@@ -113,8 +113,8 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
-    B2P_LAUNCH(cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
-               st->w2img, st->dev(3), out, (int)batch, st->trace);
+    B2P_LAUNCH_PDL(cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
+                   st->w2img, st->dev(3), out, (int)batch, st->trace);
   return 0;
 }
 
@@ -149,8 +149,8 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     dim3 grid(FC1_N / 64, ceil_div(batch, 64), splits);
     B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, in, st->dev(0), st->fc_ws, (int)batch, FC1_K / splits);
   }
-  B2P_LAUNCH(fc_tail_f32, (int)batch, 128, 0, s, st->fc_ws, splits, (int)batch, st->dev(1),
-             st->dev(2), st->dev(3), out);
+  B2P_LAUNCH_PDL(fc_tail_f32, (int)batch, 128, 0, s, st->fc_ws, splits, (int)batch, st->dev(1), st->dev(2), st->dev(3),
+                 out);
   return 0;
 }
 
@@ -178,7 +178,7 @@ int split_activation(b2p_stage* st, const float* A, size_t n, cudaStream_t s) {
     B2P_CUDA(cudaMalloc((void**)&st->ws_split, 2 * n * sizeof(float)));
     st->ws_split_elems = n;
   }
-  B2P_LAUNCH(split_tf32, elementwise_grid(n), 256, 0, s, A, st->ws_split, st->ws_split + st->ws_split_elems, n);
+  B2P_LAUNCH_PDL(split_tf32, elementwise_grid(n), 256, 0, s, A, st->ws_split, st->ws_split + st->ws_split_elems, n);
   return 0;
 }
 
@@ -213,10 +213,10 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
 int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int C, cudaStream_t s) {
   const int grid = ceil_div((int64_t)M * 32, 256);
   if (st->d.math == B2P_MATH_BF16)
-    B2P_LAUNCH(layernorm_rows<__nv_bfloat16>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi),
-               static_cast<__nv_bfloat16*>(y), M, C);
+    B2P_LAUNCH_PDL(layernorm_rows<__nv_bfloat16>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi),
+                   static_cast<__nv_bfloat16*>(y), M, C);
   else
-    B2P_LAUNCH(layernorm_rows<float>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi), static_cast<float*>(y), M, C);
+    B2P_LAUNCH_PDL(layernorm_rows<float>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi), static_cast<float*>(y), M, C);
   return 0;
 }
 
@@ -325,6 +325,11 @@ int b2p_device_count(int* count) {
 }
 
 int64_t b2p_launch_count(void) { return launch_counter().load(); }
+
+int b2p_set_pdl(int enabled) {
+  const int prev = pdl_switch().exchange(enabled ? 1 : 0);
+  return prev;
+}
 
 int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
   if (!out || !desc) return fail(B2P_EINVAL, "null argument");

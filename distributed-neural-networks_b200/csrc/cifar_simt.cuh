@@ -212,7 +212,9 @@ fc_tail_f32(const float* __restrict__ ws, int splits, int M,
             const float* __restrict__ b2,
             float* __restrict__ out) {        // [M,10]
   const int m = blockIdx.x, tid = threadIdx.x;
-  float4 h = __ldg(reinterpret_cast<const float4*>(b1) + tid);
+  pdl_trigger();
+  float4 h = __ldg(reinterpret_cast<const float4*>(b1) + tid);      // constant weight: may precede the wait
+  pdl_wait();
   for (int z = 0; z < splits; ++z) {
     float4 p = __ldg(reinterpret_cast<const float4*>(ws + ((size_t)z * M + m) * FC1_N) + tid);
     h.x += p.x; h.y += p.y; h.z += p.z; h.w += p.w;

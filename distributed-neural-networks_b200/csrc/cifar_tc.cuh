@@ -123,7 +123,8 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  // ---- one-time set-up -----------------------------------------------------------------
+  // ---- one-time set-up (touches only constant weights: runs before pdl_wait) --------------
+  pdl_trigger();
   for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
   for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = w1t[i];
@@ -147,6 +148,8 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   tc_fence_after();
   const uint32_t tmem_base = s.tmem_slot;
   if (dbg && blockIdx.x == 0 && tid == 0) dbg[3 * 64] = clock64();      // end of set-up
+  if (warp != kMmaWarp) pdl_wait();   // producers read the input, the epilogue writes the output: both may belong
+                                      // to the previous kernel of the stream; the MMA warp meanwhile streams in W2
 
   if (warp < kProducerWarps) {
     // =========================== conv1 producers ===========================================

@@ -7,6 +7,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <atomic>
 #include <string>
 
@@ -59,6 +60,54 @@ inline std::atomic<int64_t>& launch_counter() {
     if (_e != cudaSuccess)                                                          \
       return ::b2p::fail(B2P_ECUDA, "launch of %s failed: %s (%s:%d)", #kernel,     \
                          cudaGetErrorString(_e), __FILE__, __LINE__);               \
+  } while (0)
+
+// ---- programmatic dependent launch (PDL) --------------------------------------------------
+// The stages are chains of short kernels (a few microseconds each), so the ~2.5 us it takes to
+// launch a grid and run its prologue (barrier init, TMEM allocation, weight staging) is a large
+// fraction of every step.  Kernels launched through B2P_LAUNCH_PDL may start while their
+// predecessor in the stream is still draining; they run their prologue and then block in
+// pdl_wait() until the predecessor has completed and its writes are visible.  Everything a
+// kernel does BEFORE pdl_wait() must not touch memory written by earlier kernels of the stream
+// (constant weights are fine).  pdl_trigger() lets the successor be scheduled early.
+// B2P_NO_PDL=1 in the environment, or b2p_set_pdl(0), falls back to plain stream-ordered launches
+// (wanted when two stages share one GPU on two streams: an early-started grid that sits in
+// pdl_wait() holds its SMs' shared memory and keeps the other stream's kernels off them).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline std::atomic<int>& pdl_switch() {
+  static std::atomic<int> on{[] {
+    const char* e = getenv("B2P_NO_PDL");
+    return (e && e[0] && e[0] != '0') ? 0 : 1;
+  }()};
+  return on;
+}
+inline bool pdl_enabled() { return pdl_switch().load(std::memory_order_relaxed) != 0; }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+#define B2P_LAUNCH_PDL(kernel, grid, block, smem, stream, ...)                                  \
+  do {                                                                                          \
+    cudaError_t _e = ::b2p::launch_pdl(kernel, dim3(grid), dim3(block), (smem), (stream), __VA_ARGS__); \
+    ::b2p::launch_counter().fetch_add(1, std::memory_order_relaxed);                            \
+    if (_e != cudaSuccess)                                                                      \
+      return ::b2p::fail(B2P_ECUDA, "launch of %s failed: %s (%s:%d)", #kernel,                 \
+                         cudaGetErrorString(_e), __FILE__, __LINE__);                           \
   } while (0)
 
 // Scoped "make this device current, restore on exit".

@@ -77,6 +77,8 @@ __global__ void __launch_bounds__(256)
 split_tf32(const float* __restrict__ in, float* __restrict__ hi, float* __restrict__ lo, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t stride = (size_t)gridDim.x * blockDim.x;
+  pdl_trigger();
+  pdl_wait();
   for (; i < n; i += stride) {
     const float x = in[i], h = round_tf32(x);
     hi[i] = h;
@@ -89,6 +91,8 @@ __global__ void __launch_bounds__(256)
 layernorm_rows(const float* __restrict__ x, const float* __restrict__ gamma,
                const float* __restrict__ beta, OutT* __restrict__ y, int M, int C) {
   const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  pdl_wait();
   if (row >= M) return;
   const int nvec = C / 128;                       // float4 per lane, <= 16
   const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * C);

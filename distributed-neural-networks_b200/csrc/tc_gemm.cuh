@@ -234,10 +234,12 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     tmem_relinquish();
   }
+  pdl_trigger();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();        // everything above overlapped the previous kernel's tail; its outputs are visible from here
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -526,8 +528,8 @@ int launch_linear_tc(const void* A, const void* A_lo, int64_t lda, const void* W
   splits = ceil_div(total_kb, kb_per_split);            // no empty K slice
   const int items = ceil_div(M, Cfg::BM) * ceil_div(N, BN) * splits;
   const int grid = std::min(items, sms);
-  B2P_LAUNCH((linear_tc<KIND, BN>), grid, Cfg::THREADS, Cfg::SMEM_BYTES, s, ta, tw, ta_lo, tw_lo, ep, M, N, K, splits,
-             kb_per_split);
+  B2P_LAUNCH_PDL((linear_tc<KIND, BN>), grid, Cfg::THREADS, Cfg::SMEM_BYTES, s, ta, tw, ta_lo, tw_lo, ep, M, N, K,
+                 splits, kb_per_split);
   return splits;
 }
 

@@ -62,6 +62,9 @@ class LocalPipeline:
         # CUDA graphs of the whole device-resident schedule, keyed by (input address, batch, seq)
         self._graphs: dict = {}
         self.graph_kernel_launches = 0      # kernels executed through graph replays (for accounting)
+        # stages sharing a GPU run on two streams: early-started dependent grids would squat on
+        # the SMs the other stream needs, so programmatic dependent launch is switched off then
+        self._pdl = len(set(self.devs)) == len(self.devs)
 
     # -- device-resident schedule -------------------------------------------------------
     def run_device(self, x: torch.Tensor, out: torch.Tensor | None = None, seq: int = 0,
@@ -69,10 +72,12 @@ class LocalPipeline:
         """x: [B, *in_shape] on stage 0's GPU.  Enqueues everything; returns the device
         output (valid once ``self.compute[-1]`` has drained).  ``ready[i]`` (optional) is
         an event after which microbatch i of x may be read."""
+        from . import _lib
         b = x.shape[0]
         assert b <= self.max_batch
         out = self.out_dev if out is None else out
         n_st = len(self.stages)
+        prev_pdl = _lib.lib().b2p_set_pdl(1 if self._pdl else 0)
         for i, lo in enumerate(range(0, b, self.mb)):
             n = min(self.mb, b - lo)
             src = x[lo:lo + n]
@@ -97,6 +102,7 @@ class LocalPipeline:
                     prev_done = torch.cuda.Event()
                     prev_done.record(s)
                     src = self.hidden[k][lo:lo + n]
+        _lib.lib().b2p_set_pdl(prev_pdl)
         return out[:b]
 
     # -- the same schedule as one CUDA graph ---------------------------------------------------
@@ -145,12 +151,18 @@ class LocalPipeline:
         if self._x_free[flip] is not None:
             self.copy_in.wait_event(self._x_free[flip])
         with torch.cuda.stream(self.copy_in):
-            for lo in range(0, b, self.mb):
-                n = min(self.mb, b - lo)
-                xd[lo:lo + n].copy_(x_host[lo:lo + n], non_blocking=True)
+            if graph:                          # the graph starts when the whole batch has landed: one large copy
+                xd[:b].copy_(x_host, non_blocking=True)
                 ev = torch.cuda.Event()
                 ev.record(self.copy_in)
                 ready.append(ev)
+            else:
+                for lo in range(0, b, self.mb):
+                    n = min(self.mb, b - lo)
+                    xd[lo:lo + n].copy_(x_host[lo:lo + n], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(self.copy_in)
+                    ready.append(ev)
         if graph:
             self.compute[0].wait_event(ready[-1])
             out = self.run_device_graph(xd[:b], seq=seq)

@@ -96,6 +96,11 @@ B2P_API int         b2p_device_count(int* count);
 /* number of kernels this library has launched in this process (bench's gpu_launches) */
 B2P_API int64_t     b2p_launch_count(void);
 
+/* Programmatic dependent launch (overlap each kernel's prologue with its predecessor's tail).
+ * On by default; switch it off when two stages share one GPU on two streams.  Returns the
+ * previous setting.  Process-wide. */
+B2P_API int b2p_set_pdl(int enabled);
+
 /* ---- stage lifecycle (seam 1; node.py:300-317) ------------------------------- */
 B2P_API int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc);
 B2P_API int b2p_stage_destroy(b2p_stage* st);

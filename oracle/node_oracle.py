@@ -154,6 +154,11 @@ class TwoNodePipeline:
         env = dict(os.environ)
         if self.threads:
             env["OMP_NUM_THREADS"] = env["MKL_NUM_THREADS"] = str(self.threads)
+        else:
+            # torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the reference's nodes
+            # run with torch's default threading (all cores), so do not let that leak in
+            env.pop("OMP_NUM_THREADS", None)
+            env.pop("MKL_NUM_THREADS", None)
         for nid in ("node2", "node1"):
             self.procs.append(subprocess.Popen(
                 [sys.executable, "-m", "oracle.node_oracle", "--node_id", nid, "--config", cpath],
