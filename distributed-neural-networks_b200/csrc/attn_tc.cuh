@@ -7,10 +7,10 @@
 // is transposed or re-laid-out: Q, K and V tiles are fetched by TMA straight out of that
 // buffer (128B-swizzled boxes of 64 columns).
 //
-// One CTA = one (128-query tile, head, batch element); key/value tiles of 64:
+// One CTA = one (128-query tile, head, batch element); key/value tiles of 128:
 //   warp 0      TMA producer: Q once, then K_j / V_j through a 2-stage ring
-//   warp 1      MMA issuer  : S = Q K_j^T   (M128 N64 K64, A and B K-major)      -> TMEM S
-//                             O_j = P_j V_j (M128 N64 K64, A K-major from smem,
+//   warp 1      MMA issuer  : S = Q K_j^T   (M128 N128 K64, A and B K-major)     -> TMEM S
+//                             O_j = P_j V_j (M128 N64 K128, A K-major from smem,
 //                                            B = V tile as MN-major operand)      -> TMEM O
 //   warps 2..5  softmax     : one query row per thread.  Reads S from TMEM, online softmax
 //                             in exp2 domain, writes P (bf16) as a swizzled K-major A tile,
@@ -29,19 +29,21 @@ namespace attn {
 
 using namespace tc;
 
-constexpr int BQ = 128, BKV = 64, HD = 64;
-constexpr int Q_BYTES = BQ * 128, KV_BYTES = BKV * 128, P_BYTES = BQ * 128;
+constexpr int BQ = 128, BKV = 128, HD = 64;
+constexpr int Q_BYTES = BQ * 128, KV_BYTES = BKV * 128, P_ATOM_BYTES = BQ * 128, P_BYTES = (BKV / 64) * P_ATOM_BYTES;
 constexpr int KV_STAGES = 2;
+constexpr int TMEM_COLS = 256;                        // S: cols 0..127, O: cols 128..191
 
 struct Smem {
   unsigned char q[Q_BYTES];
   unsigned char k[KV_STAGES][KV_BYTES];
   unsigned char v[KV_STAGES][KV_BYTES];
-  unsigned char p[P_BYTES];
+  unsigned char p[P_BYTES];                            // two 64-key swizzle atoms of [128 rows x 128 B]
   uint64_t q_full, kv_full[KV_STAGES], kv_empty[KV_STAGES], s_full, p_full, o_full;
   uint32_t tmem_slot;
 };
-constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
+constexpr int SMEM_SLACK = 128;                        // dynamic smem starts 1024-aligned (no static smem here)
+constexpr int SMEM_BYTES = sizeof(Smem) + SMEM_SLACK;  // 2 CTAs per SM must fit: 2 x ~112 KB
 constexpr int THREADS = 192;
 
 // bf16 operands, fp32 accumulate; b_mn_major selects an MN-major B operand (V tile: d contiguous)
@@ -49,13 +51,20 @@ __host__ __device__ constexpr uint32_t idesc_bf16(int m, int n, bool b_mn_major)
   return (1u << 4) | (1u << 7) | (1u << 10) | (b_mn_major ? (1u << 16) : 0u) |
          (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
+__device__ __forceinline__ float ex2_fast(float x) {   // MUFU.EX2; exp2(-inf) = 0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 __global__ void __launch_bounds__(THREADS, 2)
 attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 cols, 128 rows] over qkv
-                    const __grid_constant__ CUtensorMap tmap_kv,    // box [64 cols,  64 rows] over qkv
+                    const __grid_constant__ CUtensorMap tmap_kv,    // box [64 cols, 128 rows] over qkv
                     __nv_bfloat16* __restrict__ y, int T, int C) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  const uint32_t pad = (1024u - (smem_u32(smem_raw) & 1023u)) & 1023u;
+  if (pad > SMEM_SLACK) __trap();
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw + pad);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_qt = gridDim.x;
   const int qt = n_qt - 1 - blockIdx.x;                 // heavy tiles first
@@ -75,7 +84,7 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(&s.tmem_slot, 128);                       // S: cols 0..63, O: cols 64..127
+    tmem_alloc(&s.tmem_slot, TMEM_COLS);
     tmem_relinquish();
   }
   pdl_trigger();
@@ -83,7 +92,7 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s.tmem_slot;
-  const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 64;
+  const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 128;
   pdl_wait();
 
   if (warp == 0) {
@@ -122,10 +131,13 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
       mbar_wait(&s.p_full, j & 1);                       // P_j is in smem (and S, O_{j-1} have been read)
       tc_fence_after();
       if (lane == 0) {
-        const uint64_t dp = make_desc_sw128(smem_u32(s.p)), dv = make_desc_sw128(smem_u32(s.v[stage]));
+        const uint64_t dv = make_desc_sw128(smem_u32(s.v[stage]));
 #pragma unroll
-        for (int k = 0; k < BKV / 16; ++k)               // A: +32 B per 16 keys; B (MN-major): +16 key rows = 2048 B
-          umma<0>(tmem_o, dp + 2 * k, dv + 128 * k, idesc_o, k != 0);
+        for (int k = 0; k < BKV / 16; ++k) {             // 16 keys per MMA
+          // A = P: 64-key atom (k>>2), +32 B per 16 keys inside it; B = V (MN-major): +16 key rows = 2048 B
+          const uint64_t dp = make_desc_sw128(smem_u32(s.p) + (k >> 2) * P_ATOM_BYTES) + 2 * (k & 3);
+          umma<0>(tmem_o, dp, dv + 128 * k, idesc_o, k != 0);
+        }
         umma_commit(&s.o_full);
         umma_commit(&s.kv_empty[stage]);
       }
@@ -143,48 +155,58 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
 #pragma unroll
     for (int d = 0; d < HD; ++d) o[d] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    unsigned char* prow = s.p + r * 128;
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(&s.s_full, j & 1);
       tc_fence_after();
-      uint32_t sr[64];
-      {
-        uint32_t a[32], c[32];
-        tmem_ld32(tmem_s + lane_sel, a);
-        tmem_ld32(tmem_s + lane_sel + 32, c);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) { sr[i] = a[i]; sr[32 + i] = c[i]; }
-      }
       const int k0 = j * BKV;
       const bool diag = k0 + BKV - 1 > q0;               // tile may contain keys beyond some query of the tile
+      // pass 1: row maximum.  S stays in tensor memory and is simply read twice (TMEM reads are
+      // cheap) instead of parking 128 scores per thread in registers.
       float mx = m_run;
+#pragma unroll 1
+      for (int c2 = 0; c2 < BKV / 64; ++c2) {            // two 32-column TMEM loads in flight per wait
+        uint32_t a[32], bq[32];
+        tmem_ld32(tmem_s + lane_sel + c2 * 64, a);
+        tmem_ld32(tmem_s + lane_sel + c2 * 64 + 32, bq);
+        tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        float v = __uint_as_float(sr[i]) * kScale;
-        if (diag && k0 + i > qi) v = -INFINITY;
-        sr[i] = __float_as_uint(v);
-        mx = fmaxf(mx, v);
+        for (int i = 0; i < 32; ++i) {
+          const float v0 = __uint_as_float(a[i]) * kScale, v1 = __uint_as_float(bq[i]) * kScale;
+          if (!(diag && k0 + c2 * 64 + i > qi)) mx = fmaxf(mx, v0);
+          if (!(diag && k0 + c2 * 64 + 32 + i > qi)) mx = fmaxf(mx, v1);
+        }
       }
       // (key 0 is never masked for a real query, so mx is finite whenever it matters)
-      const float corr = exp2f(m_run - mx);
+      const float corr = ex2_fast(m_run - mx);
       float psum = 0.f;
-      uint32_t pk[32];
+      // pass 2: probabilities -> bf16 -> swizzled K-major A tile in shared memory
+#pragma unroll 1
+      for (int c = 0; c < BKV / 32; ++c) {
+        uint32_t a[32];
+        tmem_ld32(tmem_s + lane_sel + c * 32, a);
+        tmem_ld_wait();
+        uint32_t pk[16];
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float p0 = exp2f(__uint_as_float(sr[2 * i]) - mx);
-        const float p1 = exp2f(__uint_as_float(sr[2 * i + 1]) - mx);
-        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
-        // the row sum uses the bf16-rounded probabilities: numerator and denominator match
-        psum += __low2float(pb) + __high2float(pb);
-        pk[i] = *reinterpret_cast<const uint32_t*>(&pb);
+        for (int i = 0; i < 16; ++i) {
+          float p0 = ex2_fast(fmaf(__uint_as_float(a[2 * i]), kScale, -mx));
+          float p1 = ex2_fast(fmaf(__uint_as_float(a[2 * i + 1]), kScale, -mx));
+          if (diag) {
+            if (k0 + c * 32 + 2 * i > qi) p0 = 0.f;
+            if (k0 + c * 32 + 2 * i + 1 > qi) p1 = 0.f;
+          }
+          const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+          psum += __low2float(pb) + __high2float(pb);    // sum of the ROUNDED probabilities: matches the numerator
+          pk[i] = *reinterpret_cast<const uint32_t*>(&pb);
+        }
+        unsigned char* prow = s.p + (c >> 1) * P_ATOM_BYTES + r * 128;
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const int chunk = (c & 1) * 4 + cc;
+          *reinterpret_cast<uint4*>(prow + ((chunk ^ (r & 7)) * 16)) =
+              make_uint4(pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
+        }
       }
       l_run = l_run * corr + psum;
-      // O_{j-1} must have been folded in before P (and, via p_full, the next PV MMA) may
-      // overwrite TMEM O: it was, at the end of the previous iteration.
-#pragma unroll
-      for (int c = 0; c < 8; ++c)
-        *reinterpret_cast<uint4*>(prow + ((c ^ (r & 7)) * 16)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       fence_proxy_async();
       tc_fence_before();
       __syncwarp();
@@ -195,13 +217,13 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
       m_run = mx;
       mbar_wait(&s.o_full, j & 1);
       tc_fence_after();
-      {
-        uint32_t a[32], c[32];
-        tmem_ld32(tmem_o + lane_sel, a);
-        tmem_ld32(tmem_o + lane_sel + 32, c);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t a[32];
+        tmem_ld32(tmem_o + lane_sel + c * 32, a);
         tmem_ld_wait();
 #pragma unroll
-        for (int d = 0; d < 32; ++d) { o[d] += __uint_as_float(a[d]); o[32 + d] += __uint_as_float(c[d]); }
+        for (int d = 0; d < 32; ++d) o[c * 32 + d] += __uint_as_float(a[d]);
       }
     }
     if (qi < T) {
@@ -222,7 +244,7 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 128);
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
 }
 
 // qkv: bf16 [M, 3C]; y: bf16 [M, C]
@@ -243,7 +265,7 @@ inline int launch_attention_tc(const __nv_bfloat16* qkv, __nv_bfloat16* y, int B
     cuuint64_t gdim[2] = {(cuuint64_t)(3 * C), (cuuint64_t)M};
     cuuint64_t gstride[1] = {(cuuint64_t)(3 * C) * 2};
     cuuint32_t estr[2] = {1, 1};
-    cuuint32_t boxq[2] = {64, (cuuint32_t)BQ}, boxkv[2] = {64, (cuuint32_t)BKV};
+    cuuint32_t boxq[2] = {64, (cuuint32_t)BQ}, boxkv[2] = {64, (cuuint32_t)BKV};   // 128-byte rows
     CUresult r1 = enc(&tq, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(qkv), gdim, gstride, boxq, estr,
                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

@@ -128,7 +128,8 @@ int fc1_splits(int64_t) { return FC1_SPLITS; }
 constexpr int FC1_SPLITS_TC = 16;
 
 int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
-                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits = 1, int64_t split_stride = 0);
+                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits = 1, int64_t split_stride = 0,
+                 float* amax_val = nullptr, int* amax_idx = nullptr, int amax_slots = 0);
 
 int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
   const bool tcm = st->d.math != B2P_MATH_FP32;
@@ -185,16 +186,17 @@ int split_activation(b2p_stage* st, const float* A, size_t n, cudaStream_t s) {
 // One nn.Linear call site in the stage's math mode.  A is fp32 except in BF16 mode,
 // where the producer wrote it as bf16; `out` is fp32 unless out_bf16.
 int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
-                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits, int64_t split_stride) {
+                 bool out_bf16, int M, int N, int K, cudaStream_t s, int splits, int64_t split_stride,
+                 float* amax_val, int* amax_idx, int amax_slots) {
   const float* bias = st->dev(bidx);
   const b2p_weight& w = st->w[widx];
-  tc::EpiParams ep{bias, res, out, N, N, out_bf16 ? 1 : 0, act, split_stride};
+  tc::EpiParams ep{bias, res, out, N, N, out_bf16 ? 1 : 0, act, split_stride, amax_val, amax_idx, amax_slots};
   int rc = 0;
   switch (st->d.math) {
     case B2P_MATH_FP32:
       return linear(act, static_cast<const float*>(A), w.dev, bias, res, static_cast<float*>(out), M, N, K, s);
     case B2P_MATH_TF32:
-      rc = tc::linear_tc_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, 0, s);
+      rc = tc::linear_tc_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
       break;
     case B2P_MATH_TF32X3:
       B2P_TRY(split_activation(st, static_cast<const float*>(A), (size_t)M * K, s));
@@ -202,7 +204,7 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
                                   ep, M, N, K, splits, 0, s);
       break;
     case B2P_MATH_BF16:
-      rc = tc::linear_tc_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, 0, s);
+      rc = tc::linear_tc_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
       break;
     default:
       return fail(B2P_EINVAL, "unknown math mode %d", st->d.math);
@@ -289,7 +291,24 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
   }
   B2P_TRY(layernorm(st, hx, st->lnf_w, st->lnf_b, st->ws_ln, M, C, s));
   if (!ids_out) return stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, out, false, M, V, C, s);
-  // greedy ids: logits in row chunks through a bounded scratch buffer, then row arg-max
+  if (st->d.math != B2P_MATH_FP32) {
+    // tensor-core modes: arg-max fused into the LM-head epilogue, logits never materialised
+    const int slots = 2 * ceil_div(V, 128);              // the head runs with 128-wide tiles here
+    const size_t need = (size_t)M * slots;
+    if (st->amax_elems < need) {
+      if (st->amax_val) B2P_CUDA(cudaFree(st->amax_val));
+      if (st->amax_idx) B2P_CUDA(cudaFree(st->amax_idx));
+      st->amax_val = nullptr; st->amax_idx = nullptr; st->amax_elems = 0;
+      B2P_CUDA(cudaMalloc((void**)&st->amax_val, need * sizeof(float)));
+      B2P_CUDA(cudaMalloc((void**)&st->amax_idx, need * sizeof(int)));
+      st->amax_elems = need;
+    }
+    B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, st->amax_val /*unused*/, false, M, V, C, s, 1, 0,
+                         st->amax_val, st->amax_idx, slots));
+    B2P_LAUNCH_PDL(argmax_partials, ceil_div((int64_t)M * 32, 256), 256, 0, s, st->amax_val, st->amax_idx, ids_out, M, slots);
+    return 0;
+  }
+  // fp32 CUDA-core mode: logits in row chunks through a bounded scratch buffer, then row arg-max
   const size_t chunk = std::min<size_t>((size_t)M, 2048);
   if (st->ws_logits_rows < chunk) {
     if (st->ws_logits) B2P_CUDA(cudaFree(st->ws_logits));
@@ -384,7 +403,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   if (!st) return 0;
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
-  cudaFree(st->ws_split);
+  cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
   cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->trace); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
@@ -510,7 +529,7 @@ int b2p_linear(int operand_kind, const void* a_dev, const void* a_lo_dev, int64_
   if (!a_dev || !w_dev || !out_dev) return fail(B2P_EINVAL, "null argument");
   if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) return fail(B2P_ELIMIT, "dimension too large");
   if (act < 0 || act > 2) return fail(B2P_EINVAL, "unknown activation %d", act);
-  tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act, 0};
+  tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act, 0, nullptr, nullptr, 0};
   const int tile_n = (operand_kind >> 8) & 0xfff;       // test hook: force the tile width (0 = pick)
   int rc = tc::linear_tc_dispatch(operand_kind & 0xff, a_dev, a_lo_dev, lda, w_dev, w_lo_dev, ldw, ep, (int)M, (int)N,
                                   (int)K, 1, tile_n, static_cast<cudaStream_t>(stream));

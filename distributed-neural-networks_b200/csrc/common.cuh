@@ -142,4 +142,23 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }
 
+// Branch-free erf GELU for the tensor-core epilogues: erf by Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7, far inside every tolerance in the test-suite) -- 2 MUFU + ~12 FP32 ops per
+// element instead of erff's ~25 with divergent branches.  A GEMM epilogue evaluates one GELU per
+// output element, so with short K (c_fc: K = C) the epilogue, not the MMA loop, was the limiter.
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  poly *= t;
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));
+  const float erf_abs = fmaf(-poly, e, 1.0f);           // erf(|x|/sqrt2)
+  return 0.5f * x + 0.5f * fabsf(x) * erf_abs;          // 0.5 x (1 + sign(x) erf_abs)
+}
+
 }  // namespace b2p

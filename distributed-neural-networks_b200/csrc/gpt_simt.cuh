@@ -333,4 +333,30 @@ argmax_rows(const float* __restrict__ logits, int64_t* __restrict__ ids, int V, 
   }
 }
 
+// Final reduction of the LM-head epilogue partials: [M][slots] (max, first arg-max) -> int64 ids.
+// Slots are in ascending column order, so on equal values the lower slot / lower index wins,
+// which keeps torch.argmax / np.argmax's first-maximum convention.  One warp per row.
+__global__ void __launch_bounds__(256)
+argmax_partials(const float* __restrict__ val, const int* __restrict__ idx, int64_t* __restrict__ ids, int M,
+                int slots) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  pdl_trigger();
+  pdl_wait();
+  if (row >= M) return;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int s = lane; s < slots; s += 32) {
+    const float v = val[(size_t)row * slots + s];
+    const int i = idx[(size_t)row * slots + s];
+    if (v > best || (v == best && i < bi)) { best = v; bi = i; }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, off);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+    if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
+  }
+  if (lane == 0) ids[row] = bi;
+}
+
 }  // namespace b2p

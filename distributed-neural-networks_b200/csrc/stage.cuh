@@ -46,7 +46,10 @@ struct b2p_stage {
   float *ws_x[2] = {nullptr, nullptr};
   float* ws_split = nullptr;        // TF32X3: hi | lo planes of the current GEMM's A operand
   size_t ws_split_elems = 0;        // elements per plane
-  float* ws_logits = nullptr;       // forward_argmax chunk buffer
+  float* amax_val = nullptr;        // forward_argmax: LM-head epilogue partials [M][slots]
+  int* amax_idx = nullptr;
+  size_t amax_elems = 0;
+  float* ws_logits = nullptr;       // forward_argmax chunk buffer (fp32 CUDA-core mode)
   size_t ws_logits_rows = 0;
   int* bad_flag = nullptr;          // device flag: out-of-range token id seen
 

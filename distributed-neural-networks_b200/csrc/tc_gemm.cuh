@@ -176,6 +176,12 @@ struct EpiParams {
   int out_bf16;
   int act;
   int64_t split_stride;  // split-K: elements between the partial outputs of consecutive K slices
+  // Greedy-id mode (LM head): when amax_val is set nothing is stored to `out`; instead every
+  // epilogue warp writes the (max, first arg-max) of its rows over its columns to slot
+  // (tile_n*2 + column_half) of [M][amax_slots] -- the [B,T,V] logits never touch HBM.
+  float* amax_val;
+  int* amax_idx;
+  int amax_slots;
 };
 
 template <int KIND, int BN>
@@ -191,7 +197,8 @@ struct GemmCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = SPLIT ? (BN <= 128 ? 3 : 2) : (BN <= 128 ? 5 : 4);
   static constexpr int EPI_PITCH = 20;       // floats: 16 columns + pad; 16-byte aligned rows, conflict-free float4 stores
-  static constexpr int EPI_BYTES = 8 * 32 * EPI_PITCH * 4;
+  static constexpr int EPI_WARP_FLOATS = 32 * EPI_PITCH + BN / 2;   // transpose buffer + this warp's bias slice
+  static constexpr int EPI_BYTES = 8 * EPI_WARP_FLOATS * 4;
   static constexpr int BAR_BYTES = 256;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
   static constexpr int TMEM_COLS = 2 * BN;     // two accumulator stages (power of two >= 32)
@@ -310,21 +317,59 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     const int q = warp & 3;                         // TMEM lane quarter this warp may read
     const int ew = warp - 2;                        // 0..7
     const int col_half = ew >> 2;                   // which half of the tile's columns
-    float* stg = epi_smem + ew * 32 * P;
+    float* stg = epi_smem + ew * Cfg::EPI_WARP_FLOATS;
+    float* bias_s = stg + 32 * P;                   // [BN/2] bias of this warp's columns for the current tile
     const bool vec_f32 = !ep.out_bf16 && (ep.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 &&
                          (ep.split_stride & 3) == 0 &&
                          (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
     const bool vec_bf16 = ep.out_bf16 && (ep.ldo & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 && !ep.res;
-    const bool bias_vec = ep.bias && (reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0;
     constexpr int CHUNKS = BN / 64;                 // 32-column chunks per warp
     uint32_t acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       const int z = item % splits, tile = item / splits;
       const int m0 = (tile % tiles_m) * Cfg::BM, n0 = (tile / tiles_m) * BN;
+      // This warp's bias slice goes to shared memory BEFORE waiting for the accumulator: the
+      // global-load latency hides behind the MMA wait instead of sitting in front of every chunk.
+      if (ep.bias) {
+        const int cbase = n0 + col_half * (BN / 2);
+#pragma unroll
+        for (int i = lane; i < BN / 2; i += 32) bias_s[i] = (cbase + i < N) ? __ldg(ep.bias + cbase + i) : 0.f;
+        __syncwarp();
+      }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       const int row_base = m0 + q * 32;
       float* out_f32 = static_cast<float*>(ep.out) + static_cast<int64_t>(z) * ep.split_stride;
+      if (ep.amax_val) {
+        float best = -INFINITY;
+        int bidx = 0x7fffffff;
+#pragma unroll 1
+        for (int cc = 0; cc < CHUNKS; ++cc) {
+          const int c = col_half * CHUNKS + cc;
+          const int col0 = n0 + c * 32;
+          if (col0 >= N) break;
+          uint32_t r[32];
+          tmem_ld32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float v = __uint_as_float(r[j]);
+            if (ep.bias) v += bias_s[cc * 32 + j];
+            if (col0 + j < N && v > best) { best = v; bidx = col0 + j; }     // ascending scan: first maximum wins
+          }
+        }
+        const int row = row_base + lane;
+        if (row < M) {
+          const int64_t slot = static_cast<int64_t>(row) * ep.amax_slots + (tile / tiles_m) * 2 + col_half;
+          ep.amax_val[slot] = best;
+          ep.amax_idx[slot] = bidx;
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        continue;
+      }
 #pragma unroll 1
       for (int cc = 0; cc < CHUNKS; ++cc) {
         const int c = col_half * CHUNKS + cc;
@@ -357,14 +402,8 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
 #pragma unroll
           for (int e = 0; e < 4; ++e) v[4 * j4 + e] = __uint_as_float(r[4 * j4 + e]);
           if (ep.bias) {
-            if (bias_vec && full_cols) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.bias + col0) + j4);
-              v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
-            } else {
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                if (col0 + 4 * j4 + e < N) v[4 * j4 + e] += __ldg(ep.bias + col0 + 4 * j4 + e);
-            }
+            const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[cc * 32 + 4 * j4]);     // smem broadcast
+            v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
           }
         }
         if (ep.act == ACT_RELU) {
@@ -372,7 +411,7 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         } else if (ep.act == ACT_GELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
         }
 #pragma unroll
         for (int sub = 0; sub < 2; ++sub) {

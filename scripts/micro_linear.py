@@ -57,3 +57,11 @@ run("fc2", 2048, 768, 3072, res=True)
 run("fc2_nores", 2048, 768, 3072)
 run("head", 2048, 50257, 768, bias=False, reps=5)
 run("big_m", 32768, 768, 768, res=True, reps=5)
+run("fc8k_gelu", 8192, 3072, 768, out_bf16=True, act=2, reps=5)
+run("fc8k_gelu_bn128", 8192, 3072, 768, bn=128, out_bf16=True, act=2, reps=5)
+run("fc8k_noact", 8192, 3072, 768, out_bf16=True, reps=5)
+run("fc8k_f32out", 8192, 3072, 768, reps=5)
+run("qkv8k", 8192, 2304, 768, out_bf16=True, reps=5)
+run("fc2_8k", 8192, 768, 3072, res=True, reps=5)
+run("proj8k", 8192, 768, 768, res=True, reps=5)
+run("sq4k", 4096, 4096, 4096, bias=False, reps=5)
