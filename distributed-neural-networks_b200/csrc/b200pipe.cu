@@ -113,7 +113,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
-    B2P_LAUNCH_PDL(cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
+    B2P_LAUNCH_PDL_BIT(2, cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
                    st->w2img, st->dev(3), out, (int)batch, st->trace);
   return 0;
 }
@@ -345,8 +345,8 @@ int b2p_device_count(int* count) {
 
 int64_t b2p_launch_count(void) { return launch_counter().load(); }
 
-int b2p_set_pdl(int enabled) {
-  const int prev = pdl_switch().exchange(enabled ? 1 : 0);
+int b2p_set_pdl(int mask) {
+  const int prev = pdl_switch().exchange(mask & 3);
   return prev;
 }
 
@@ -549,6 +549,11 @@ int b2p_stage_trace(b2p_stage* st, long long* host_out, int n) {
   B2P_CUDA(cudaDeviceSynchronize());
   B2P_CUDA(cudaMemcpy(host_out, st->trace, 256 * sizeof(long long), cudaMemcpyDeviceToHost));
   return 0;
+}
+
+int b2p_debug_attn_trace(long long* host_out, int n) {
+  if (!host_out) return fail(B2P_EINVAL, "null argument");
+  return attn::read_attn_trace(host_out, n);
 }
 
 int b2p_stage_check(b2p_stage* st, void* stream) {

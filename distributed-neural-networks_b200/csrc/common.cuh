@@ -79,15 +79,17 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 inline std::atomic<int>& pdl_switch() {
   static std::atomic<int> on{[] {
     const char* e = getenv("B2P_NO_PDL");
-    return (e && e[0] && e[0] != '0') ? 0 : 1;
+    return (e && e[0] && e[0] != '0') ? 0 : 3;
   }()};
   return on;
 }
-inline bool pdl_enabled() { return pdl_switch().load(std::memory_order_relaxed) != 0; }
+// bit 0: the light kernel chains (GEMMs, LayerNorm, attention, fc tail, splits); bit 1: the CIFAR part-0
+// kernel, whose CTAs each take a whole SM's shared memory while they wait.
+inline bool pdl_enabled(int bit = 1) { return (pdl_switch().load(std::memory_order_relaxed) & bit) != 0; }
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
-                              Args&&... args) {
+inline cudaError_t launch_pdl_bit(int bit, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                                  Args&&... args) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -95,15 +97,17 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   cfg.stream = s;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  at[0].val.programmaticStreamSerializationAllowed = pdl_enabled(bit) ? 1 : 0;
   cfg.attrs = at;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
-#define B2P_LAUNCH_PDL(kernel, grid, block, smem, stream, ...)                                  \
+#define B2P_LAUNCH_PDL(kernel, grid, block, smem, stream, ...) \
+  B2P_LAUNCH_PDL_BIT(1, kernel, grid, block, smem, stream, __VA_ARGS__)
+#define B2P_LAUNCH_PDL_BIT(bit, kernel, grid, block, smem, stream, ...)                         \
   do {                                                                                          \
-    cudaError_t _e = ::b2p::launch_pdl(kernel, dim3(grid), dim3(block), (smem), (stream), __VA_ARGS__); \
+    cudaError_t _e = ::b2p::launch_pdl_bit(bit, kernel, dim3(grid), dim3(block), (smem), (stream), __VA_ARGS__); \
     ::b2p::launch_counter().fetch_add(1, std::memory_order_relaxed);                            \
     if (_e != cudaSuccess)                                                                      \
       return ::b2p::fail(B2P_ECUDA, "launch of %s failed: %s (%s:%d)", #kernel,                 \

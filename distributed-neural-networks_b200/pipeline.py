@@ -77,7 +77,7 @@ class LocalPipeline:
         assert b <= self.max_batch
         out = self.out_dev if out is None else out
         n_st = len(self.stages)
-        prev_pdl = _lib.lib().b2p_set_pdl(1 if self._pdl else 0)
+        prev_pdl = _lib.lib().b2p_set_pdl(3 if self._pdl else 0)    # shared GPU: no early starts (measured: 0.199 vs 0.238 ms/step)
         for i, lo in enumerate(range(0, b, self.mb)):
             n = min(self.mb, b - lo)
             src = x[lo:lo + n]

@@ -97,9 +97,10 @@ B2P_API int         b2p_device_count(int* count);
 B2P_API int64_t     b2p_launch_count(void);
 
 /* Programmatic dependent launch (overlap each kernel's prologue with its predecessor's tail).
- * On by default; switch it off when two stages share one GPU on two streams.  Returns the
- * previous setting.  Process-wide. */
-B2P_API int b2p_set_pdl(int enabled);
+ * mask bit 0: the light kernel chains (GEMMs, LayerNorm, attention, fc tail); bit 1: the CIFAR
+ * part-0 kernel, whose waiting CTAs each hold a whole SM -- clear it when two stages share one
+ * GPU on two streams.  Default 3.  Returns the previous mask.  Process-wide. */
+B2P_API int b2p_set_pdl(int mask);
 
 /* ---- stage lifecycle (seam 1; node.py:300-317) ------------------------------- */
 B2P_API int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc);
@@ -146,6 +147,10 @@ B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
  * later calls synchronise and copy out 256 clock64 stamps of CTA 0 of the CIFAR part-0
  * tensor-core kernel ([role 0..2][sample 0..7][event 0..7], entry 192 = end of set-up). */
 B2P_API int b2p_stage_trace(b2p_stage* st, long long* host_out, int n);
+
+/* Developer aid (no reference counterpart): clock64 timeline of CTA (0,0,0) of the last tensor-core
+ * attention launch on the current device; 193 entries [role 0..2][key tile 0..7][event 0..7] + start. */
+B2P_API int b2p_debug_attn_trace(long long* host_out, int n);
 
 /* GPT final only: greedy token ids (row arg-max of the logits) without
  * materialising [B,T,V]; out int64 [batch,seq].  (north_star: "greedy token ids") */
