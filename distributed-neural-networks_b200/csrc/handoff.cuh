@@ -11,7 +11,9 @@
 //     transfer rides on the kernel's own epilogue stores: zero extra copies.
 // All waiting is done on the device by one-thread kernels (acquire loads with back-off and a
 // time-out that traps instead of hanging), so the host never blocks and the schedule of a
-// whole batch can be enqueued ahead.  The consumer's waits are on local memory; the
+// whole batch can be enqueued ahead -- or captured once in a CUDA graph and replayed: the message
+// counters live in device memory, so no launch carries a step-dependent argument.  `seq` in the
+// C ABI only selects the slot (seq % slots); messages of one slot must be used in order.  The consumer's waits are on local memory; the
 // producer's back-pressure wait polls the consumer's counter over NVLink.
 #pragma once
 #include <cstring>
@@ -28,6 +30,10 @@ struct b2p_ring {
   bool owner = false, ipc = false;
   int mode = 1;                       // 0: cudaMemcpyAsync (copy engine), 1: SM copy kernel
   void* base = nullptr;               // allocation base (data and flags live in one allocation)
+  // Message counters per slot, in the memory of the GPU that uses them.  Keeping the sequence state
+  // on the device (instead of passing targets as kernel arguments) makes every wait / publish kernel
+  // launch identical from step to step, so a whole step can be captured in a CUDA graph and replayed.
+  unsigned long long* local_count = nullptr;   // producer side: published per slot; consumer side: consumed per slot
 };
 
 namespace b2p {
@@ -50,21 +56,39 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
   asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// stream-ordered "wait until *flag >= target" (one thread; traps after 20 s instead of hanging)
-__global__ void ring_wait_ge(const unsigned long long* flag, unsigned long long target) {
+__device__ __forceinline__ void spin_until_ge(const unsigned long long* flag, unsigned long long target) {
   if (ld_acquire_sys(flag) >= target) return;
   const uint64_t t0 = tc::global_ns();
   unsigned ns = 32;
-  while (ld_acquire_sys(flag) < target) {
+  while (ld_acquire_sys(flag) < target) {           // one thread; traps after 20 s instead of hanging
     __nanosleep(ns);
     if (ns < 1024) ns *= 2;
     if (tc::global_ns() - t0 > 20000000000ull) __trap();
   }
 }
-// stream-ordered "*flag = value" after everything earlier in the stream is visible system-wide
-__global__ void ring_set(unsigned long long* flag, unsigned long long value) {
+// All four are one-thread, stream-ordered kernels whose arguments never change between steps.
+// producer, before writing a slot: the consumer must have released every earlier message of that slot
+__global__ void ring_acquire_k(const unsigned long long* count, const unsigned long long* released_flag) {
+  const unsigned long long k = *count;               // messages already published into this slot
+  if (k > 0) spin_until_ge(released_flag, k);
+}
+// producer, after writing: bump the local count and publish it
+__global__ void ring_publish_k(unsigned long long* count, unsigned long long* published_flag) {
+  const unsigned long long k = *count + 1;
+  *count = k;
+  __threadfence_system();                            // everything earlier in the stream is visible system-wide
+  st_release_sys(published_flag, k);
+}
+// consumer, before reading a slot
+__global__ void ring_recv_k(const unsigned long long* count, const unsigned long long* published_flag) {
+  spin_until_ge(published_flag, *count + 1);
+}
+// consumer, after the last kernel that reads the slot
+__global__ void ring_release_k(unsigned long long* count, unsigned long long* released_flag) {
+  const unsigned long long k = *count + 1;
+  *count = k;
   __threadfence_system();
-  st_release_sys(flag, value);
+  st_release_sys(released_flag, k);
 }
 // SM-driven copy with 128-bit peer stores (dst may be mapped memory of another GPU)
 __global__ void __launch_bounds__(256)
@@ -123,6 +147,14 @@ int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->owner = true;
+  cudaError_t ce = cudaMalloc((void**)&r->local_count, slots * sizeof(unsigned long long));
+  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, slots * sizeof(unsigned long long));
+  if (ce != cudaSuccess) {
+    cudaFree(base);
+    delete r;
+    return fail(B2P_ECUDA, "ring: counter allocation failed: %s", cudaGetErrorString(ce));
+  }
+  B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
   return 0;
 }
@@ -164,6 +196,9 @@ int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->ipc = true;
+  B2P_CUDA(cudaMalloc((void**)&r->local_count, r->slots * sizeof(unsigned long long)));
+  B2P_CUDA(cudaMemset(r->local_count, 0, r->slots * sizeof(unsigned long long)));
+  B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
   return 0;
 }
@@ -185,6 +220,13 @@ int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_de
   r->owner = false;
   r->ipc = false;
   r->producer_dev = producer_device;
+  r->local_count = nullptr;
+  {
+    DeviceGuard g(producer_device);
+    B2P_CUDA(cudaMalloc((void**)&r->local_count, r->slots * sizeof(unsigned long long)));
+    B2P_CUDA(cudaMemset(r->local_count, 0, r->slots * sizeof(unsigned long long)));
+    B2P_CUDA(cudaDeviceSynchronize());
+  }
   *out = r;
   return 0;
 }
@@ -194,9 +236,11 @@ int b2p_ring_destroy(b2p_ring* ring) {
   if (ring->owner) {
     b2p::DeviceGuard g(ring->consumer_dev);
     cudaFree(ring->base);
-  } else if (ring->ipc) {
+    cudaFree(ring->local_count);
+  } else {
     b2p::DeviceGuard g(ring->producer_dev);
-    cudaIpcCloseMemHandle(ring->base);
+    cudaFree(ring->local_count);
+    if (ring->ipc) cudaIpcCloseMemHandle(ring->base);
   }
   delete ring;
   return 0;
@@ -212,8 +256,7 @@ int b2p_ring_acquire(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream
   using namespace b2p;
   if (!ring || !slot_dev) return fail(B2P_EINVAL, "null argument");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const uint64_t k = seq / ring->slots;
-  if (k > 0) B2P_LAUNCH(ring_wait_ge, 1, 1, 0, s, released(ring, seq), (unsigned long long)k);
+  B2P_LAUNCH(ring_acquire_k, 1, 1, 0, s, ring->local_count + (seq % ring->slots), released(ring, seq));
   *slot_dev = ring->data + (seq % ring->slots) * ring->slot_bytes;
   return 0;
 }
@@ -221,8 +264,8 @@ int b2p_ring_acquire(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream
 int b2p_ring_publish(b2p_ring* ring, uint64_t seq, void* stream) {
   using namespace b2p;
   if (!ring) return fail(B2P_EINVAL, "null argument");
-  B2P_LAUNCH(ring_set, 1, 1, 0, static_cast<cudaStream_t>(stream), published(ring, seq),
-             (unsigned long long)(seq / ring->slots + 1));
+  B2P_LAUNCH(ring_publish_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
+             published(ring, seq));
   return 0;
 }
 
@@ -239,8 +282,8 @@ int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uint64_t se
 int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream) {
   using namespace b2p;
   if (!ring || !slot_dev) return fail(B2P_EINVAL, "null argument");
-  B2P_LAUNCH(ring_wait_ge, 1, 1, 0, static_cast<cudaStream_t>(stream), published(ring, seq),
-             (unsigned long long)(seq / ring->slots + 1));
+  B2P_LAUNCH(ring_recv_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
+             published(ring, seq));
   *slot_dev = ring->data + (seq % ring->slots) * ring->slot_bytes;
   return 0;
 }
@@ -248,8 +291,8 @@ int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream) {
 int b2p_ring_release(b2p_ring* ring, uint64_t seq, void* stream) {
   using namespace b2p;
   if (!ring) return fail(B2P_EINVAL, "null argument");
-  B2P_LAUNCH(ring_set, 1, 1, 0, static_cast<cudaStream_t>(stream), released(ring, seq),
-             (unsigned long long)(seq / ring->slots + 1));
+  B2P_LAUNCH(ring_release_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
+             released(ring, seq));
   return 0;
 }
 

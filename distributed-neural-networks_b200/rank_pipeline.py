@@ -47,6 +47,13 @@ def plan(world: int, stages: int) -> list[RankRole]:
     return roles
 
 
+def quiet_nccl():
+    """NCCL_DEBUG=VERSION makes NCCL print a banner on stdout, where bench.py must print exactly one
+    JSON line; keep warnings, drop the banner (an explicit INFO/TRACE setting is left alone)."""
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"
+
+
 def exchange_handles(my_handle: bytes | None, group=None) -> list:
     """Every rank contributes the export handle of the ring it consumes from (or None)."""
     import torch.distributed as dist
@@ -91,6 +98,9 @@ class CifarRankPipeline:
         else:
             self.out_dev = torch.empty((batch, 10), device=device)
             self.out_host = torch.empty((batch, 10)).pin_memory()
+        self.slots = slots
+        self._graphs = {}
+        self.graph_kernel_launches = 0
 
     # ---- one step = one batch through this rank's stage ------------------------------------------
     def step_device(self, x: torch.Tensor | None, ready=None):
@@ -109,8 +119,40 @@ class CifarRankPipeline:
                 self.ring.release(self.seq, s)
             self.seq += 1
 
-    def step_host(self, x_host: torch.Tensor | None):
-        """Stage 0: pinned host batch -> H2D per microbatch -> stage; stage 1: stage -> D2H."""
+    def step_graph(self, x: torch.Tensor | None):
+        """step_device as ONE CUDA-graph launch.  Possible because the ring's sequence counters live in
+        device memory: the wait / publish kernels take no step-dependent argument, so the captured step
+        (microbatches walking the slots in order) is replayed verbatim.  Needs n_mb % slots == 0 or
+        slots % n_mb == 0 so that every step starts on the same slot."""
+        from . import _lib
+        assert self.n_mb % self.slots == 0 or self.slots % self.n_mb == 0
+        if self.seq % self.slots:                      # not at a step boundary the graph was captured for
+            return self.step_device(x)
+        key = x.data_ptr() if x is not None else 0
+        entry = self._graphs.get(key)
+        if entry is None:
+            start = self.seq
+            self.step_device(x)                        # eager once: warm-up and lazy allocations
+            self.stream.synchronize()
+            if self.seq % self.slots:                  # this step does not end on the slot it started on:
+                return                                 # (slots > n_mb) stay eager
+            g = torch.cuda.CUDAGraph()
+            before = _lib.launch_count()
+            seq_before = self.seq
+            with torch.cuda.graph(g, stream=self.stream):
+                self.step_device(x)                    # captured, not executed
+            self.seq = seq_before                      # (host seq only selects slots; nothing ran)
+            self._graphs[key] = (g, _lib.launch_count() - before)
+            return
+        with torch.cuda.stream(self.stream):
+            entry[0].replay()
+        self.seq += self.n_mb
+        self.graph_kernel_launches += entry[1]
+
+    def step_host(self, x_host: torch.Tensor | None, graph: bool = False):
+        """Stage 0: pinned host batch -> H2D -> stage; stage 1: stage -> D2H of the result.
+        graph=True: one large H2D copy, then the captured step (the copy of step s+1 still overlaps
+        the compute of step s through the double-buffered device input)."""
         if self.role.stage == 0:
             flip = self._flip
             self._flip ^= 1
@@ -119,17 +161,30 @@ class CifarRankPipeline:
                 self.copy_stream.wait_event(self._x_free[flip])
             ready = []
             with torch.cuda.stream(self.copy_stream):
-                for lo in range(0, self.batch, self.mb):
-                    xd[lo:lo + self.mb].copy_(x_host[lo:lo + self.mb], non_blocking=True)
+                if graph:
+                    xd.copy_(x_host, non_blocking=True)
                     ev = torch.cuda.Event()
                     ev.record(self.copy_stream)
                     ready.append(ev)
-            self.step_device(xd, ready)
+                else:
+                    for lo in range(0, self.batch, self.mb):
+                        xd[lo:lo + self.mb].copy_(x_host[lo:lo + self.mb], non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(self.copy_stream)
+                        ready.append(ev)
+            if graph:
+                self.stream.wait_event(ready[-1])
+                self.step_graph(xd)
+            else:
+                self.step_device(xd, ready)
             ev = torch.cuda.Event()
             ev.record(self.stream)
             self._x_free[flip] = ev
         else:
-            self.step_device(None)
+            if graph:
+                self.step_graph(None)
+            else:
+                self.step_device(None)
             with torch.cuda.stream(self.stream):
                 self.out_host.copy_(self.out_dev, non_blocking=True)
 
@@ -144,6 +199,7 @@ def bench_main(args) -> int:
     local = int(os.environ.get("LOCAL_RANK", rank))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    quiet_nccl()
     dist.init_process_group("nccl", device_id=dev)
     roles = plan(world, 2)
     role = roles[rank]
@@ -178,15 +234,22 @@ def bench_main(args) -> int:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
         return float(t[0]), float(t[1])
 
-    launches0 = engine.launch_count()
+    use_graph = not getattr(args, "no_graph", False)
+    step = pipe.step_graph if use_graph else pipe.step_device
+    if role.active and use_graph:                      # capture one graph per input buffer (stage 0) / one (stage 1)
+        for i in range(2 * n_pool):
+            step(dev_pool[i % n_pool] if dev_pool else None)
+        torch.cuda.synchronize()
+    dist.barrier()
+    launches0 = engine.launch_count() + pipe.graph_kernel_launches
     sampler.active.set()
     if role.active:
-        ms_dev, _ = timed(lambda i: pipe.step_device(dev_pool[i % n_pool] if dev_pool else None))
+        ms_dev, _ = timed(lambda i: step(dev_pool[i % n_pool] if dev_pool else None))
     else:
         ms_dev, _ = timed(lambda i: None)
-    launches = engine.launch_count() - launches0
+    launches = engine.launch_count() + pipe.graph_kernel_launches - launches0
     if role.active:
-        _, ms_e2e = timed(lambda i: pipe.step_host(host_pool[i % n_pool] if host_pool else None))
+        _, ms_e2e = timed(lambda i: pipe.step_host(host_pool[i % n_pool] if host_pool else None, graph=use_graph))
     else:
         _, ms_e2e = timed(lambda i: None)
     sampler.active.clear()
@@ -231,7 +294,7 @@ def bench_main(args) -> int:
             "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH, "stages": 2,
                        "placement": f"{replicas} pipeline(s) of 2 stages, stage k on GPU 2r+k; activations stored by the "
                                     "stage-0 kernel directly into a peer-memory ring on the stage-1 GPU (NVLink)",
-                       "math": args.math, "launch": "per_kernel",
+                       "math": args.math, "launch": "cuda_graph_per_step_per_rank" if use_graph else "per_kernel",
                        "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
                     "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0])},

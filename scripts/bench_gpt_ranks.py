@@ -30,6 +30,7 @@ rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 local = int(os.environ.get("LOCAL_RANK", rank))
 dev = torch.device("cuda", local)
 torch.cuda.set_device(dev)
+rp.quiet_nccl()
 dist.init_process_group("nccl", device_id=dev)
 dims = dict(engine.GPT2_SMALL if a.model == "small" else engine.GPT2_MEDIUM)
 cfg = engine.GPTConfig(block_size=1024, vocab_size=50257, **dims)

@@ -73,6 +73,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", rank))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    import_module("distributed-neural-networks_b200.rank_pipeline").quiet_nccl()
     dist.init_process_group("nccl", device_id=dev)
     assert world == 2
     results = []
