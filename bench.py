@@ -240,12 +240,42 @@ def engine_arm(args):
     sampler.active.clear()
     clocks = sampler.finish()
 
+    # -- (5) reported comparator, not the target: the reference's own GPU path (node.py:25 DEVICE="cuda"),
+    #        i.e. the same two parts through PyTorch eager (cuDNN / cuBLAS) on this B200
+    eager = None
+    try:
+        from oracle import cifar_oracle as co
+        sd_gpu = {k: v.to(dev) for k, v in sd.items()}
+        def eager_step(x):
+            for lo in range(0, BATCH, MICROBATCH):
+                co.part1(co.part0(x[lo:lo + MICROBATCH], sd_gpu), sd_gpu)
+        for i in range(3):
+            eager_step(dev_pool[i])
+        torch.cuda.synchronize()
+        q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        q0.record()
+        n_eager = min(K, 20)
+        for i in range(n_eager):
+            eager_step(dev_pool[(W + i) % n_pool])
+        q1.record()
+        torch.cuda.synchronize()
+        eager = {"value": BATCH * n_eager / (q0.elapsed_time(q1) * 1e-3), "unit": UNIT,
+                 "what": "reference part classes' arithmetic via torch eager fp32 (cuDNN/cuBLAS) on the same GPU, "
+                         "device-resident inputs, same 8 x 128 microbatching; reported only"}
+    except Exception as e:                                   # never fail the bench on the comparator
+        eager = {"error": f"{type(e).__name__}: {e}"}
+
     tf = FLOP_PART0 * MICROBATCH / (us_k0 * 1e-6) / 1e12
+    traffic = None
+    try:                                                     # dram bytes per launch from the committed ncu capture
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "part0_tc_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
     peak_tf = peaks["bf16_tflops_sustained"]
     roofline = {"kernel": "part0 (conv1+ReLU+pool+conv2+ReLU+pool), one launch per 128-sample microbatch",
                 "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
-                "traffic": None, "peak_source": f"bf16_tflops_sustained of {peaks_kind}",
-                "us_per_launch": us_k0,
+                "traffic": traffic, "peak_source": f"bf16_tflops_sustained of {peaks_kind}",
+                "us_per_launch": us_k0, "algorithmic_bytes_per_launch": BYTES_PART0 * MICROBATCH,
                 "hbm_view": {"achieved_gbs": BYTES_PART0 * MICROBATCH / (us_k0 * 1e-6) / 1e9, "peak_gbs": peaks["hbm_gbs"]}}
 
     cpu = None
@@ -269,6 +299,7 @@ def engine_arm(args):
                 "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
         "p50_request_latency_ms": statistics.median(lats),
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "torch_eager_gpu": eager,
     }
     print(json.dumps(line))
     return 0

@@ -11,7 +11,7 @@ the repository root (``import dnn_b200 as engine``).
 """
 from . import _lib
 from ._lib import EngineError, launch_count
-from .gpt_model import GPT, GPT2_MEDIUM, GPT2_SMALL, GPTConfig
+from .gpt_model import (GPT, GPT2_MEDIUM, GPT2_SMALL, GPTConfig, balanced_ranges, from_hf_gpt2_state_dict)
 from .stages import (MODEL_PARTS_CLASSES, EngineStage, ModelPart0, ModelPart0_2Node,
                      ModelPart1_2Node, ModelPartFinal_GPT, ModelPartIntermediate,
                      NeuralNetwork, gpt_parts_for)
@@ -20,7 +20,8 @@ from . import wire
 from . import handoff, pipeline, service
 
 __all__ = [
-    "EngineError", "launch_count", "GPT", "GPTConfig", "GPT2_SMALL", "GPT2_MEDIUM",
+    "EngineError", "launch_count", "GPT", "GPTConfig", "GPT2_SMALL", "GPT2_MEDIUM", "balanced_ranges",
+    "from_hf_gpt2_state_dict",
     "MODEL_PARTS_CLASSES", "EngineStage", "ModelPart0", "ModelPart0_2Node", "ModelPart1_2Node",
     "ModelPartFinal_GPT", "ModelPartIntermediate", "NeuralNetwork", "gpt_parts_for",
     "NodeConfig", "Topology", "load_config", "wire", "handoff", "pipeline", "service",

@@ -104,3 +104,50 @@ class GPT(nn.Module):
         for p in self._parts[1]:
             x = p(x)
         return x
+
+
+def stage_cost_blocks(cfg: GPTConfig, seq_len: int) -> float:
+    """LM-head cost expressed in transformer blocks (FLOP per token):
+    2*C*V against 24*C^2 + 2*T*C (causal attention counted as executed)."""
+    c = cfg.n_embd
+    return (2.0 * c * cfg.vocab_size) / (24.0 * c * c + 2.0 * seq_len * c)
+
+
+def balanced_ranges(cfg: GPTConfig, num_parts: int, seq_len: int = 1024) -> list[tuple[int, int]]:
+    """Inclusive (start, end) layer ranges for ``num_parts`` stages that equalise FLOP per stage when
+    the final stage also carries ``ln_f`` + ``lm_head`` (2.6x / 2.3x heavier than a 3-block stage for
+    GPT-2 small / medium under an even split).  The reference constructors accept any
+    inclusive range (gpt_model_parts.py:7,27,37); an empty final range is written (n_layer, n_layer-1)."""
+    n = cfg.n_layer
+    if num_parts <= 1:
+        return [(0, n - 1)]
+    head = stage_cost_blocks(cfg, seq_len)
+    per_stage = (n + head) / num_parts
+    last = min(n, max(0, round(per_stage - head)))
+    rest = n - last
+    base, rem = divmod(rest, num_parts - 1)
+    out, s0 = [], 0
+    for k in range(num_parts - 1):
+        cnt = base + (1 if k < rem else 0)
+        out.append((s0, s0 + cnt - 1))
+        s0 += cnt
+    out.append((s0, n - 1))
+    return out
+
+
+def from_hf_gpt2_state_dict(hf_sd: dict, n_layer: int | None = None) -> dict:
+    """Hugging Face ``GPT2LMHeadModel`` checkpoint -> the nanoGPT-named full-model state dict this engine
+    (and the reference's part classes) expect.  HF stores the four per-block projections as ``Conv1D``
+    with weight [in, out]; ``nn.Linear`` wants [out, in], so those are transposed.  Attention-mask
+    buffers (``attn.bias`` / ``attn.masked_bias``) are dropped; a missing ``lm_head.weight`` is tied to
+    ``wte`` (GPT-2 ties them)."""
+    out = {}
+    for k, v in hf_sd.items():
+        if k.endswith((".attn.bias", ".attn.masked_bias")):
+            continue
+        if k.endswith(("attn.c_attn.weight", "attn.c_proj.weight", "mlp.c_fc.weight", "mlp.c_proj.weight")):
+            v = v.t()
+        out[k] = v.contiguous()
+    if "lm_head.weight" not in out and "transformer.wte.weight" in out:
+        out["lm_head.weight"] = out["transformer.wte.weight"]
+    return out

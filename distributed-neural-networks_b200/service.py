@@ -121,3 +121,30 @@ def serve(servicer, port: int, max_message_bytes: int = -1):
     bound = server.add_insecure_port(f"[::]:{port}")
     server.start()
     return server, bound
+
+
+def load_input_image(path: str | None, seed: int | None = None):
+    """node.py:142-154: ``Resize((32,32)) -> ToTensor -> Normalize(0.5, 0.5)`` of an RGB image, or the
+    reference's fallback ``torch.randn(1,3,32,32)`` when the file is missing or unreadable.  Host-side,
+    once per request, not on the hot path (out of scope for optimisation)."""
+    import torch
+    try:
+        from PIL import Image
+        if path is None:
+            raise FileNotFoundError("no input image given")
+        img = Image.open(path).convert("RGB").resize((32, 32), Image.BILINEAR)
+        x = torch.from_numpy(np.asarray(img, dtype=np.float32) / 255.0).permute(2, 0, 1).unsqueeze(0)
+        return ((x - 0.5) / 0.5).contiguous(), True
+    except Exception:
+        g = torch.Generator().manual_seed(seed) if seed is not None else None
+        return torch.randn(1, 3, 32, 32, generator=g), False
+
+
+def initiate_inference(servicer: NodeServiceImpl, input_image_path: str | None = None, seed: int | None = None):
+    """The built-in client of node.py:137-200 for the node that owns part 0: load (or fake) one image,
+    push it through the chain, arg-max the reply.  In the reference part 0 runs in-process and the rest
+    behind a gRPC hop; here the whole chain is one device-resident pipeline, so this is a plain call.
+    Returns (predicted_class_index, probabilities ndarray, used_real_image)."""
+    x, real = load_input_image(input_image_path, seed)
+    probs = servicer.run(x.numpy())
+    return int(np.argmax(probs)), probs, real

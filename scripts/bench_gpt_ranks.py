@@ -35,20 +35,7 @@ dist.init_process_group("nccl", device_id=dev)
 dims = dict(engine.GPT2_SMALL if a.model == "small" else engine.GPT2_MEDIUM)
 cfg = engine.GPTConfig(block_size=1024, vocab_size=50257, **dims)
 model = engine.GPT(cfg, seed=1234)
-ranges = None
-if a.balance and world > 1:
-    # LM head ~ 2*C*V FLOP/token = roughly 4 (small) / 3 (medium) blocks' worth: shorten the final stage
-    L = cfg.n_layer
-    head_blocks = (2 * cfg.n_embd * cfg.vocab_size) / (24 * cfg.n_embd ** 2 + 2 * a.seq * cfg.n_embd)
-    per = (L + head_blocks) / world
-    last = max(0, round(per - head_blocks))
-    rest = L - last
-    base, rem = divmod(rest, world - 1)
-    ranges, s0 = [], 0
-    for k in range(world - 1):
-        n = base + (1 if k < rem else 0)
-        ranges.append((s0, s0 + n - 1)); s0 += n
-    ranges.append((s0, L - 1))
+ranges = engine.balanced_ranges(cfg, world, a.seq) if (a.balance and world > 1) else None
 role = rp.plan(world, world)[rank]
 pipe = rp.GptRankPipeline(role, dev, model, a.math, a.microbatch, a.seq, ranges=ranges)
 n_mb = a.batch // a.microbatch

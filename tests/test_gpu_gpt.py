@@ -194,3 +194,25 @@ def test_bf16_attention_ragged_lengths(cuda_engine):
             got = parts[1](parts[0](idx.cuda()))
         err = (got.cpu() - want).abs().max().item()
         assert err <= 3e-2, f"T={t}: {err}"
+
+
+def test_hf_gpt2_checkpoint_through_the_engine(cuda_engine):
+    """a Hugging Face GPT-2 state dict (Conv1D weights stored [in,out]) is imported and
+    run through the engine's parts; logits must match HF's own forward (exact-erf GELU configured)."""
+    tr = pytest.importorskip("transformers")
+    torch.manual_seed(0)
+    hf_cfg = tr.GPT2Config(vocab_size=512, n_positions=128, n_embd=128, n_layer=2, n_head=2, activation_function="gelu",
+                           resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+    hf = tr.GPT2LMHeadModel(hf_cfg).eval()
+    sd = cuda_engine.from_hf_gpt2_state_dict(hf.state_dict())
+    cfg = cuda_engine.GPTConfig(block_size=128, vocab_size=512, n_layer=2, n_head=2, n_embd=128)
+    model = cuda_engine.GPT(cfg)
+    model.load_state_dict(sd)
+    idx = gpt_oracle.make_tokens(2, 100, 512, seed=1)
+    with torch.no_grad():
+        want = hf(idx).logits
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math="tf32x3")]
+    with torch.no_grad():
+        got = parts[1](parts[0](idx.cuda())).cpu()
+    assert (got - want).abs().max().item() <= 1e-4
+    assert torch.equal(got.argmax(-1), want.argmax(-1)) or ((want.topk(2, -1).values[..., 0] - want.topk(2, -1).values[..., 1]).min() < 2e-4)

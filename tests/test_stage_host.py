@@ -56,3 +56,47 @@ def test_gpt_parts_key_mapping(engine):
         engine.ModelPartIntermediate(g, 2, 4)
     one = engine.gpt_parts_for(g, 1)
     assert [(p.start_layer, p.end_layer) for p in one] == [(0, 3), (4, 3)]
+
+
+def test_balanced_ranges_offset_the_lm_head(engine):
+    small = engine.GPTConfig(vocab_size=50257, **engine.GPT2_SMALL)
+    medium = engine.GPTConfig(vocab_size=50257, **engine.GPT2_MEDIUM)
+    r = engine.balanced_ranges(small, 4)
+    assert r == [(0, 3), (4, 7), (8, 11), (12, 11)]          # head ~ 5 blocks: the final stage keeps none
+    r = engine.balanced_ranges(medium, 8)
+    assert r[0] == (0, 3) and r[-1] == (24, 23) and sum(e - s + 1 for s, e in r) == 24
+    assert all(r[i][1] + 1 == r[i + 1][0] for i in range(7))      # contiguous, inclusive
+    assert engine.balanced_ranges(small, 1) == [(0, 11)]
+    tiny = engine.GPTConfig(block_size=64, vocab_size=256, n_layer=4, n_head=2, n_embd=128)
+    r = engine.balanced_ranges(tiny, 2, seq_len=32)
+    assert sum(e - s + 1 for s, e in r) == 4
+    parts = engine.gpt_parts_for(engine.GPT(tiny, seed=0), 2, ranges=r)
+    assert (parts[0].start_layer, parts[-1].end_layer) == (0, 3)
+
+
+def test_hf_gpt2_checkpoint_import(engine):
+    tr = pytest.importorskip("transformers")
+    hf = tr.GPT2LMHeadModel(tr.GPT2Config(vocab_size=256, n_positions=64, n_embd=128, n_layer=2, n_head=2))
+    sd = engine.from_hf_gpt2_state_dict(hf.state_dict())
+    cfg = engine.GPTConfig(block_size=64, vocab_size=256, n_layer=2, n_head=2, n_embd=128)
+    model = engine.GPT(cfg)
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not missing and not unexpected
+    assert sd["transformer.h.0.attn.c_attn.weight"].shape == (384, 128)          # [out, in] after the transpose
+    assert torch.equal(sd["transformer.h.1.mlp.c_proj.weight"], hf.state_dict()["transformer.h.1.mlp.c_proj.weight"].t())
+    assert torch.equal(sd["lm_head.weight"], sd["transformer.wte.weight"])
+
+
+def test_input_image_fallback_and_preprocessing(engine, tmp_path):
+    svc = engine.service
+    x, real = svc.load_input_image(str(tmp_path / "missing.png"), seed=3)     # node.py:149-151 fallback
+    assert not real and x.shape == (1, 3, 32, 32) and x.dtype == torch.float32
+    from PIL import Image
+    import numpy as np
+    img = Image.fromarray((np.arange(64 * 48 * 3) % 256).astype(np.uint8).reshape(48, 64, 3), "RGB")
+    p = tmp_path / "img.png"
+    img.save(p)
+    x, real = svc.load_input_image(str(p))
+    assert real and x.shape == (1, 3, 32, 32) and float(x.min()) >= -1.0 and float(x.max()) <= 1.0
+    pred, probs, real = svc.initiate_inference(svc.NodeServiceImpl(["n"], lambda a: np.eye(10, dtype=np.float32)[[7] * a.shape[0]]), None, seed=1)
+    assert pred == 7 and probs.shape == (1, 10) and not real
