@@ -308,8 +308,8 @@ def engine_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=1000)      # 1000 x ~0.2 ms: long enough for the clock sampler
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", choices=["engine", "reference"], default="engine")
     ap.add_argument("--math", default="tf32x3", choices=["fp32", "tf32x3", "tf32"],
                     help="tf32x3 (default): tensor-core parity mode, fp32-grade (split-fp16 conv2, 3xTF32 fc1); "

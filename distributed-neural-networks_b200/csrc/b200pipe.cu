@@ -212,14 +212,39 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
   return rc < 0 ? rc : 0;
 }
 
-int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int C, cudaStream_t s) {
-  const int grid = ceil_div((int64_t)M * 32, 256);
-  if (st->d.math == B2P_MATH_BF16)
-    B2P_LAUNCH_PDL(layernorm_rows<__nv_bfloat16>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi),
-                   static_cast<__nv_bfloat16*>(y), M, C);
-  else
-    B2P_LAUNCH_PDL(layernorm_rows<float>, grid, 256, 0, s, x, st->dev(gi), st->dev(bi), static_cast<float*>(y), M, C);
+template <typename OutT, int NVEC>
+int layernorm_launch(const float* x, const float* g, const float* b, OutT* y, int M, int C, cudaStream_t s) {
+  B2P_LAUNCH_PDL((layernorm_rows<OutT, NVEC>), ceil_div((int64_t)M * 32, 256), 256, 0, s, x, g, b, y, M, C);
   return 0;
+}
+
+template <typename OutT>
+int layernorm_typed(const float* x, const float* g, const float* b, OutT* y, int M, int C, cudaStream_t s) {
+  switch (C / 128) {                       // n_embd is a multiple of 128, at most 2048 (checked at stage creation)
+    case 1: return layernorm_launch<OutT, 1>(x, g, b, y, M, C, s);
+    case 2: return layernorm_launch<OutT, 2>(x, g, b, y, M, C, s);
+    case 3: return layernorm_launch<OutT, 3>(x, g, b, y, M, C, s);
+    case 4: return layernorm_launch<OutT, 4>(x, g, b, y, M, C, s);
+    case 5: return layernorm_launch<OutT, 5>(x, g, b, y, M, C, s);
+    case 6: return layernorm_launch<OutT, 6>(x, g, b, y, M, C, s);
+    case 7: return layernorm_launch<OutT, 7>(x, g, b, y, M, C, s);
+    case 8: return layernorm_launch<OutT, 8>(x, g, b, y, M, C, s);
+    case 9: return layernorm_launch<OutT, 9>(x, g, b, y, M, C, s);
+    case 10: return layernorm_launch<OutT, 10>(x, g, b, y, M, C, s);
+    case 11: return layernorm_launch<OutT, 11>(x, g, b, y, M, C, s);
+    case 12: return layernorm_launch<OutT, 12>(x, g, b, y, M, C, s);
+    case 13: return layernorm_launch<OutT, 13>(x, g, b, y, M, C, s);
+    case 14: return layernorm_launch<OutT, 14>(x, g, b, y, M, C, s);
+    case 15: return layernorm_launch<OutT, 15>(x, g, b, y, M, C, s);
+    case 16: return layernorm_launch<OutT, 16>(x, g, b, y, M, C, s);
+    default: return fail(B2P_EINVAL, "layernorm: unsupported width %d", C);
+  }
+}
+
+int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int C, cudaStream_t s) {
+  if (st->d.math == B2P_MATH_BF16)
+    return layernorm_typed<__nv_bfloat16>(x, st->dev(gi), st->dev(bi), static_cast<__nv_bfloat16*>(y), M, C, s);
+  return layernorm_typed<float>(x, st->dev(gi), st->dev(bi), static_cast<float*>(y), M, C, s);
 }
 
 // Runs this stage's blocks.  `x` is the stage input (never written); the result of

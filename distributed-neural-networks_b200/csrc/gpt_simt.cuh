@@ -86,7 +86,7 @@ split_tf32(const float* __restrict__ in, float* __restrict__ hi, float* __restri
   }
 }
 
-template <typename OutT>
+template <typename OutT, int NVEC>          // NVEC = C / 128 float4 per lane (compile-time: row lives in NVEC*4 registers)
 __global__ void __launch_bounds__(256)
 layernorm_rows(const float* __restrict__ x, const float* __restrict__ gamma,
                const float* __restrict__ beta, OutT* __restrict__ y, int M, int C) {
@@ -94,35 +94,30 @@ layernorm_rows(const float* __restrict__ x, const float* __restrict__ gamma,
   pdl_trigger();
   pdl_wait();
   if (row >= M) return;
-  const int nvec = C / 128;                       // float4 per lane, <= 16
   const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * C);
-  float4 v[16];
+  float4 v[NVEC];
   float sum = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (i < nvec) {
-      v[i] = __ldg(xr + lane + 32 * i);
-      sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-    }
+  for (int i = 0; i < NVEC; ++i) {
+    v[i] = __ldg(xr + lane + 32 * i);
+    sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  }
   const float mean = warp_sum(sum) / (float)C;
   float sq = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (i < nvec) {
-      float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
-      sq += (a * a + b * b) + (c * c + d * d);
-    }
+  for (int i = 0; i < NVEC; ++i) {
+    float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+    sq += (a * a + b * b) + (c * c + d * d);
+  }
   const float rstd = rsqrtf(warp_sum(sq) / (float)C + 1e-5f);
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (i < nvec) {
-      float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
-      float4 b = beta ? __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i)
-                      : make_float4(0, 0, 0, 0);
-      store4<OutT>(y + (size_t)row * C + (lane + 32 * i) * 4,
-                   (v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
-                   (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
-    }
+  for (int i = 0; i < NVEC; ++i) {
+    float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + lane + 32 * i);
+    float4 b = beta ? __ldg(reinterpret_cast<const float4*>(beta) + lane + 32 * i) : make_float4(0, 0, 0, 0);
+    store4<OutT>(y + (size_t)row * C + (lane + 32 * i) * 4,
+                 (v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
+                 (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
+  }
 }
 
 // ---------------------------------------------------------------------------------
