@@ -150,8 +150,12 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     dim3 grid(FC1_N / 64, ceil_div(batch, 64), splits);
     B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, in, st->dev(0), st->fc_ws, (int)batch, FC1_K / splits);
   }
-  B2P_LAUNCH_PDL(fc_tail_f32, (int)batch, 128, 0, s, st->fc_ws, splits, (int)batch, st->dev(1), st->dev(2), st->dev(3),
-                 out);
+  if (tcm)
+    B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS_TC>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+                   st->dev(3), out);
+  else
+    B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+                   st->dev(3), out);
   return 0;
 }
 
@@ -674,7 +678,7 @@ extern "C" int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* 
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   dim3 grid(FC1_N / 64, ceil_div(batch, 64), FC1_SPLITS);
   B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, x_dev, fc1_weight_dev, scratch, (int)batch, FC1_K / FC1_SPLITS);
-  B2P_LAUNCH(fc_tail_f32, (int)batch, 128, 0, s, scratch, FC1_SPLITS, (int)batch, fc1_bias_dev, fc2_weight_dev,
+  B2P_LAUNCH(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, scratch, (int)batch, fc1_bias_dev, fc2_weight_dev,
              fc2_bias_dev, out_dev);
   return 0;
 }

@@ -205,8 +205,9 @@ fc1_splitk_f32(const float* __restrict__ x,     // [M,4096]
 //   l = b2 + W2 h                          (10)
 //   out[m] = softmax(l)                    cifar_model_parts.py:55-57
 // ---------------------------------------------------------------------------------
+template <int SPLITS>     // compile-time so the partial-sum loads are all in flight together (they were a serial chain)
 __global__ void __launch_bounds__(128)
-fc_tail_f32(const float* __restrict__ ws, int splits, int M,
+fc_tail_f32(const float* __restrict__ ws, int M,
             const float* __restrict__ b1,
             const float* __restrict__ w2,     // [10,512]
             const float* __restrict__ b2,
@@ -215,17 +216,21 @@ fc_tail_f32(const float* __restrict__ ws, int splits, int M,
   pdl_trigger();
   float4 h = __ldg(reinterpret_cast<const float4*>(b1) + tid);      // constant weight: may precede the wait
   pdl_wait();
-  for (int z = 0; z < splits; ++z) {
-    float4 p = __ldg(reinterpret_cast<const float4*>(ws + ((size_t)z * M + m) * FC1_N) + tid);
-    h.x += p.x; h.y += p.y; h.z += p.z; h.w += p.w;
-  }
+  float4 p[SPLITS];
+#pragma unroll
+  for (int z = 0; z < SPLITS; ++z)      // plain loads, NOT __ldg: ws was written by the previous kernel, and the compiler
+    p[z] = ld_produced(reinterpret_cast<const float4*>(ws + ((size_t)z * M + m) * FC1_N) + tid);   // may hoist ld.global.nc above pdl_wait()
+#pragma unroll
+  for (int z = 0; z < SPLITS; ++z) { h.x += p[z].x; h.y += p[z].y; h.z += p[z].z; h.w += p[z].w; }   // fixed order
   h.x = fmaxf(h.x, 0.f); h.y = fmaxf(h.y, 0.f); h.z = fmaxf(h.z, 0.f); h.w = fmaxf(h.w, 0.f);
   __shared__ float part[4][10];
   float l[10];
+  float4 w[10];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) w[j] = __ldg(reinterpret_cast<const float4*>(w2 + j * FC1_N) + tid);
 #pragma unroll
   for (int j = 0; j < 10; ++j) {
-    float4 w = __ldg(reinterpret_cast<const float4*>(w2 + j * FC1_N) + tid);
-    float v = fmaf(h.x, w.x, fmaf(h.y, w.y, fmaf(h.z, w.z, h.w * w.w)));
+    float v = fmaf(h.x, w[j].x, fmaf(h.y, w[j].y, fmaf(h.z, w[j].z, h.w * w[j].w)));
     v = warp_sum(v);
     if ((tid & 31) == 0) part[tid >> 5][j] = v;
   }

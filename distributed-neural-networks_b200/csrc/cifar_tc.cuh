@@ -54,7 +54,7 @@ struct Smem {
   float w1[27][32];                                  // [c*9+kh*3+kw][oc]
   float b1[32];
   float b2[64];
-  uint64_t bar_w2, bar_act_full, bar_act_empty, bar_tmem_full[2], bar_tmem_empty[2];
+  uint64_t bar_w2, bar_act_full[2], bar_act_empty, bar_tmem_full[2][2], bar_tmem_empty[2];
   uint32_t tmem_slot;
 };
 constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
@@ -133,9 +133,14 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   if (warp == kMmaWarp) {
     if (lane == 0) {
       mbar_init(&s.bar_w2, 1);
-      mbar_init(&s.bar_act_full, kProducerWarps);
+      mbar_init(&s.bar_act_full[0], kProducerWarps);
+      mbar_init(&s.bar_act_full[1], kProducerWarps);
       mbar_init(&s.bar_act_empty, 1);
-      for (int i = 0; i < 2; ++i) { mbar_init(&s.bar_tmem_full[i], 1); mbar_init(&s.bar_tmem_empty[i], 4); }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&s.bar_tmem_full[i][0], 1);
+        mbar_init(&s.bar_tmem_full[i][1], 1);
+        mbar_init(&s.bar_tmem_empty[i], 4);
+      }
       fence_barrier_init();
     }
     __syncwarp();
@@ -158,7 +163,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     if ((int)blockIdx.x < batch) {
       const float4* xin = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 3072);
 #pragma unroll
-      for (int j = 0; j < 3; ++j) pre[j] = __ldg(xin + tid + 256 * j);
+      for (int j = 0; j < 3; ++j) pre[j] = ld_produced(xin + tid + 256 * j);     // the image may come from the previous kernel
     }
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
@@ -175,11 +180,13 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       if (b + (int)gridDim.x < batch) {                     // next image: in flight during the FMAs
         const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
 #pragma unroll
-        for (int j = 0; j < 3; ++j) pre[j] = __ldg(xin + tid + 256 * j);
+        for (int j = 0; j < 3; ++j) pre[j] = ld_produced(xin + tid + 256 * j);
       }
       B2P_TRACE(0, n, 1, tid == 0);
-      // ---- conv1 + ReLU + pool, 32 channels in two passes of 16 (8 packed pairs) --------------
-      uint32_t hi_pk[16], lo_pk[16];                        // fp16x2 words: channels (2i, 2i+1)
+      // ---- conv1 + ReLU + pool, 32 channels in two passes of 16 (8 packed pairs).  Each pass
+      //      publishes its half of the pixel's row (hi chunks 2p,2p+1 and lo chunks 4+2p,5+2p) into
+      //      the three shifted copies right away: the tensor core starts on channels 0..15 (the
+      //      first K=16 MMA of every tap) while the CUDA cores still compute channels 16..31.
 #pragma unroll
       for (int pass = 0; pass < 2; ++pass) {
         unsigned long long acc[8][4];
@@ -218,6 +225,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
               }
             }
         }
+        uint32_t hi_pk[8], lo_pk[8];                          // fp16x2 words: channels pass*16 + (2i, 2i+1)
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
           float a0, a1, b0, b1v, c0, c1, d0, d1;
@@ -229,29 +237,33 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           split_f16(v0, h0, l0);
           split_f16(v1, h1, l1);
           __half2 hh = __halves2half2(h0, h1), ll = __halves2half2(l0, l1);
-          hi_pk[pass * 8 + p] = *reinterpret_cast<uint32_t*>(&hh);
-          lo_pk[pass * 8 + p] = *reinterpret_cast<uint32_t*>(&ll);
+          hi_pk[p] = *reinterpret_cast<uint32_t*>(&hh);
+          lo_pk[p] = *reinterpret_cast<uint32_t*>(&ll);
         }
-      }
-      // ---- publish the pixel's row into the three shifted copies -----------------------------
-      B2P_TRACE(0, n, 2, tid == 0);
-      mbar_wait(&s.bar_act_empty, (n & 1) ^ 1);             // MMAs of the previous sample are done
-      B2P_TRACE(0, n, 3, tid == 0);
-#pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int xc = px - kw + 1;                          // column of this pixel in copy kw
-        if (xc < 0 || xc > 15) continue;
-        const int R = (py + 1) * 16 + xc;
-        unsigned char* row = s.act + kw * ACT_COPY_BYTES + R * 128;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const uint32_t* src = (c < 4) ? &hi_pk[4 * c] : &lo_pk[4 * (c - 4)];
-          *reinterpret_cast<uint4*>(row + ((c ^ (R & 7)) * 16)) = make_uint4(src[0], src[1], src[2], src[3]);
+        if (pass == 0) {
+          B2P_TRACE(0, n, 2, tid == 0);
+          mbar_wait(&s.bar_act_empty, (n & 1) ^ 1);           // MMAs of the previous sample are done
+          B2P_TRACE(0, n, 3, tid == 0);
         }
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+          const int xc = px - kw + 1;                          // column of this pixel in copy kw
+          if (xc < 0 || xc > 15) continue;
+          const int R = (py + 1) * 16 + xc;
+          unsigned char* row = s.act + kw * ACT_COPY_BYTES + R * 128;
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            const int ch = 2 * pass + cc, cl = 4 + 2 * pass + cc;      // hi chunk, lo chunk of this channel group
+            *reinterpret_cast<uint4*>(row + ((ch ^ (R & 7)) * 16)) =
+                make_uint4(hi_pk[4 * cc], hi_pk[4 * cc + 1], hi_pk[4 * cc + 2], hi_pk[4 * cc + 3]);
+            *reinterpret_cast<uint4*>(row + ((cl ^ (R & 7)) * 16)) =
+                make_uint4(lo_pk[4 * cc], lo_pk[4 * cc + 1], lo_pk[4 * cc + 2], lo_pk[4 * cc + 3]);
+          }
+        }
+        fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.bar_act_full[pass]);
       }
-      fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&s.bar_act_full);
       B2P_TRACE(0, n, 4, tid == 0);
     }
   } else if (warp == kMmaWarp) {
@@ -270,7 +282,8 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       B2P_TRACE(1, n, 0, lane == 0);
       mbar_wait(&s.bar_tmem_empty[set], (use & 1) ^ 1);
       B2P_TRACE(1, n, 1, lane == 0);
-      mbar_wait(&s.bar_act_full, n & 1);
+      // channels 0..15 (first K=16 step of every tap) as soon as the first conv1 pass has landed
+      mbar_wait(&s.bar_act_full[0], n & 1);
       tc_fence_after();
       B2P_TRACE(1, n, 2, lane == 0);
       if (lane == 0) {
@@ -282,17 +295,33 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
             const int kh = tap / 3, kw = tap % 3;
             const uint64_t da = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 * t + kh) * 16 * 128);
             const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
-            // K = 32 channels = 2 MMAs of K=16; descriptor units are 16 B: +2 = 32 B, +4 = the lo half
+            // descriptor units are 16 B: +2 = the second K=16 step (channels 16..31), +4 = the lo half
             umma<0>(acc0, da, db, idesc, tap != 0);                 // hi * hi
-            umma<0>(acc0, da + 2, db + 2, idesc, 1u);
             umma<0>(acc1, da, db + 4, idesc, tap != 0);             // hi * lo
-            umma<0>(acc1, da + 2, db + 6, idesc, 1u);
             umma<0>(acc1, da + 4, db, idesc, 1u);                   // lo * hi
-            umma<0>(acc1, da + 6, db + 2, idesc, 1u);
           }
         }
+      }
+      __syncwarp();
+      // channels 16..31, tile by tile, so the epilogue of tile 0 overlaps the MMAs of tile 1
+      mbar_wait(&s.bar_act_full[1], n & 1);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll 1
+        for (int t = 0; t < 2; ++t) {
+          const uint32_t acc0 = tmem_base + set * 256 + t * 128, acc1 = acc0 + 64;
+#pragma unroll 1
+          for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap % 3;
+            const uint64_t da = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 * t + kh) * 16 * 128);
+            const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
+            umma<0>(acc0, da + 2, db + 2, idesc, 1u);
+            umma<0>(acc1, da + 2, db + 6, idesc, 1u);
+            umma<0>(acc1, da + 6, db + 2, idesc, 1u);
+          }
+          umma_commit(&s.bar_tmem_full[set][t]);
+        }
         umma_commit(&s.bar_act_empty);                       // activation copies may be overwritten
-        umma_commit(&s.bar_tmem_full[set]);
       }
       B2P_TRACE(1, n, 3, lane == 0);
       __syncwarp();
@@ -305,12 +334,12 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       const uint32_t set = n & 1, use = n >> 1;
       B2P_TRACE(2, n, 0, et == 0);
-      mbar_wait(&s.bar_tmem_full[set], use & 1);
-      tc_fence_after();
-      B2P_TRACE(2, n, 1, et == 0);
       const bool xo = (lane & 1) != 0, yo = (lane & 16) != 0;
 #pragma unroll 1
       for (int t = 0; t < 2; ++t) {
+        mbar_wait(&s.bar_tmem_full[set][t], use & 1);
+        tc_fence_after();
+        if (t == 0) B2P_TRACE(2, n, 1, et == 0);
 #pragma unroll 1
         for (int ch = 0; ch < 2; ++ch) {                     // 32 output channels at a time
           uint32_t r0[32], r1[32];

@@ -69,11 +69,32 @@ inline std::atomic<int64_t>& launch_counter() {
 // predecessor in the stream is still draining; they run their prologue and then block in
 // pdl_wait() until the predecessor has completed and its writes are visible.  Everything a
 // kernel does BEFORE pdl_wait() must not touch memory written by earlier kernels of the stream
-// (constant weights are fine).  pdl_trigger() lets the successor be scheduled early.
+// (constant weights are fine), and data produced by earlier kernels must be read with PLAIN loads after
+// it: __ldg / ld.global.nc promises immutability, so the compiler may hoist such loads above the wait
+// (observed: the fc tail read split-K partials the GEMM had not finished writing).
+// pdl_trigger() lets the successor be scheduled early.
 // B2P_NO_PDL=1 in the environment, or b2p_set_pdl(0), falls back to plain stream-ordered launches
 // (wanted when two stages share one GPU on two streams: an early-started grid that sits in
 // pdl_wait() holds its SMs' shared memory and keeps the other stream's kernels off them).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Loads of data written by an earlier kernel of the stream.  Volatile asm with a memory clobber keeps
+// them behind pdl_wait(); a C++ load through a `const __restrict__` pointer may be turned into
+// ld.global.nc and scheduled ahead of it.
+__device__ __forceinline__ float4 ld_produced(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int ld_produced(const int* p) {
+  int v;
+  asm volatile("ld.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_produced(const float* p) {
+  float v;
+  asm volatile("ld.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 inline std::atomic<int>& pdl_switch() {

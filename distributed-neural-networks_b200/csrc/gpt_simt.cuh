@@ -80,7 +80,7 @@ split_tf32(const float* __restrict__ in, float* __restrict__ hi, float* __restri
   pdl_trigger();
   pdl_wait();
   for (; i < n; i += stride) {
-    const float x = in[i], h = round_tf32(x);
+    const float x = ld_produced(in + i), h = round_tf32(x);
     hi[i] = h;
     lo[i] = round_tf32(x - h);
   }
@@ -99,7 +99,7 @@ layernorm_rows(const float* __restrict__ x, const float* __restrict__ gamma,
   float sum = 0.f;
 #pragma unroll
   for (int i = 0; i < NVEC; ++i) {
-    v[i] = __ldg(xr + lane + 32 * i);
+    v[i] = ld_produced(xr + lane + 32 * i);      // x comes from the previous kernel (see pdl_wait)
     sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
   }
   const float mean = warp_sum(sum) / (float)C;
@@ -341,8 +341,8 @@ argmax_partials(const float* __restrict__ val, const int* __restrict__ idx, int6
   float best = -INFINITY;
   int bi = 0x7fffffff;
   for (int s = lane; s < slots; s += 32) {
-    const float v = val[(size_t)row * slots + s];
-    const int i = idx[(size_t)row * slots + s];
+    const float v = ld_produced(val + (size_t)row * slots + s);
+    const int i = ld_produced(idx + (size_t)row * slots + s);
     if (v > best || (v == best && i < bi)) { best = v; bi = i; }
   }
 #pragma unroll

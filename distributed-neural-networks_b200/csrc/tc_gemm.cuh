@@ -390,8 +390,8 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
 #pragma unroll
             for (int it = 0; it < 4; ++it) {
               const int row = row_base + it * 8 + (lane >> 2);
-              rv[sub][it] = row < M ? __ldg(reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res +
-                                                                              col0 + sub * 16 + cg))
+              rv[sub][it] = row < M ? ld_produced(reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res +
+                                                                                 col0 + sub * 16 + cg))
                                     : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
