@@ -13,7 +13,7 @@
 #include "common.cuh"
 #include "gpt_simt.cuh"
 #include "stage.cuh"
-#include "tc_gemm.cuh"
+#include "tc_gemm2.cuh"
 
 using namespace b2p;
 
@@ -200,15 +200,15 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
     case B2P_MATH_FP32:
       return linear(act, static_cast<const float*>(A), w.dev, bias, res, static_cast<float*>(out), M, N, K, s);
     case B2P_MATH_TF32:
-      rc = tc::linear_tc_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
+      rc = tc::linear_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
       break;
     case B2P_MATH_TF32X3:
       B2P_TRY(split_activation(st, static_cast<const float*>(A), (size_t)M * K, s));
-      rc = tc::linear_tc_dispatch(2, st->ws_split, st->ws_split + st->ws_split_elems, K, w.packed, w.packed_lo, K,
+      rc = tc::linear_dispatch(2, st->ws_split, st->ws_split + st->ws_split_elems, K, w.packed, w.packed_lo, K,
                                   ep, M, N, K, splits, 0, s);
       break;
     case B2P_MATH_BF16:
-      rc = tc::linear_tc_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
+      rc = tc::linear_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
       break;
     default:
       return fail(B2P_EINVAL, "unknown math mode %d", st->d.math);
@@ -560,7 +560,7 @@ int b2p_linear(int operand_kind, const void* a_dev, const void* a_lo_dev, int64_
   if (act < 0 || act > 2) return fail(B2P_EINVAL, "unknown activation %d", act);
   tc::EpiParams ep{bias_dev, res_dev, out_dev, ldo, ld_res, out_bf16, act, 0, nullptr, nullptr, 0};
   const int tile_n = (operand_kind >> 8) & 0xfff;       // test hook: force the tile width (0 = pick)
-  int rc = tc::linear_tc_dispatch(operand_kind & 0xff, a_dev, a_lo_dev, lda, w_dev, w_lo_dev, ldw, ep, (int)M, (int)N,
+  int rc = tc::linear_dispatch(operand_kind & 0xff, a_dev, a_lo_dev, lda, w_dev, w_lo_dev, ldw, ep, (int)M, (int)N,
                                   (int)K, 1, tile_n, static_cast<cudaStream_t>(stream));
   return rc < 0 ? rc : 0;
 }

@@ -184,6 +184,144 @@ struct EpiParams {
   int amax_slots;
 };
 
+// ------------------------------------------------------------------------------------
+// Epilogue of one output tile for one warp: rows [m0 + 32q, +32), columns of half `col_half` of the
+// BN-wide tile whose accumulator starts at TMEM column `tmem_acc`.  Shared by the 1-CTA and the
+// 2-CTA kernels.  `stg` is the warp's private [32][P] transpose buffer, `bias_s` its bias slice.
+// ------------------------------------------------------------------------------------
+template <int BN, int P>
+__device__ __forceinline__ void epilogue_tile(const EpiParams& ep, float* stg, const float* bias_s, uint32_t tmem_acc,
+                                              int m0, int n0, int M, int N, int q, int col_half, int lane, int z,
+                                              int amax_slot_base, bool vec_f32, bool vec_bf16) {
+  constexpr int CHUNKS = BN / 64;                 // 32-column chunks per warp
+  const int row_base = m0 + q * 32;
+  float* out_f32 = static_cast<float*>(ep.out) + static_cast<int64_t>(z) * ep.split_stride;
+  if (ep.amax_val) {
+    float best = -INFINITY;
+    int bidx = 0x7fffffff;
+#pragma unroll 1
+    for (int cc = 0; cc < CHUNKS; ++cc) {
+      const int c = col_half * CHUNKS + cc;
+      const int col0 = n0 + c * 32;
+      if (col0 >= N) break;
+      uint32_t r[32];
+      tmem_ld32(tmem_acc + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float v = __uint_as_float(r[j]);
+        if (ep.bias) v += bias_s[cc * 32 + j];
+        if (col0 + j < N && v > best) { best = v; bidx = col0 + j; }     // ascending scan: first maximum wins
+      }
+    }
+    const int row = row_base + lane;
+    if (row < M) {
+      const int64_t slot = static_cast<int64_t>(row) * ep.amax_slots + amax_slot_base + col_half;
+      ep.amax_val[slot] = best;
+      ep.amax_idx[slot] = bidx;
+    }
+    return;
+  }
+#pragma unroll 1
+  for (int cc = 0; cc < CHUNKS; ++cc) {
+    const int c = col_half * CHUNKS + cc;
+    const int col0 = n0 + c * 32;
+    if (col0 >= N) break;                        // warp-uniform
+    uint32_t r[32];
+    tmem_ld32(tmem_acc + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
+    const bool full_cols = col0 + 32 <= N;
+    // Residual values are fetched NOW -- while the TMEM load is in flight and before any store
+    // of this chunk.  A load issued after a may-alias store has to wait for it; leaving the
+    // loads inside the store loop serialised eight ~700-cycle round trips per chunk.
+    const bool res_vec = ep.res != nullptr && vec_f32 && full_cols;
+    float4 rv[2][4];
+    if (res_vec) {
+      const int cg = (lane & 3) * 4;
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub)
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int row = row_base + it * 8 + (lane >> 2);
+          rv[sub][it] = row < M ? ld_produced(reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res +
+                                                                             col0 + sub * 16 + cg))
+                                : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    tmem_ld_wait();
+    float v[32];
+#pragma unroll
+    for (int j4 = 0; j4 < 8; ++j4) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) v[4 * j4 + e] = __uint_as_float(r[4 * j4 + e]);
+      if (ep.bias) {
+        const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[cc * 32 + 4 * j4]);     // smem broadcast
+        v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
+      }
+    }
+    if (ep.act == ACT_RELU) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+    } else if (ep.act == ACT_GELU) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
+    }
+#pragma unroll
+    for (int sub = 0; sub < 2; ++sub) {
+      const int cs = col0 + sub * 16;
+#pragma unroll
+      for (int j4 = 0; j4 < 4; ++j4)
+        *reinterpret_cast<float4*>(&stg[lane * P + 4 * j4]) =
+            make_float4(v[sub * 16 + 4 * j4], v[sub * 16 + 4 * j4 + 1], v[sub * 16 + 4 * j4 + 2], v[sub * 16 + 4 * j4 + 3]);
+      __syncwarp();
+      if (vec_f32 && full_cols) {
+        // 4 lanes x 16 B = one 64-byte row segment; 8 rows per instruction
+        const int cg = (lane & 3) * 4;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+          const int rr = it * 8 + (lane >> 2), row = row_base + rr;
+          if (row < M) {
+            float4 o = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+            if (res_vec) { o.x += rv[sub][it].x; o.y += rv[sub][it].y; o.z += rv[sub][it].z; o.w += rv[sub][it].w; }
+            *reinterpret_cast<float4*>(out_f32 + static_cast<int64_t>(row) * ep.ldo + cs + cg) = o;
+          }
+        }
+      } else if (vec_bf16 && full_cols) {
+        // 2 lanes x 16 B (8 bf16) = one 32-byte row segment; 16 rows per instruction
+        __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
+        const int cg = (lane & 1) * 8;
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+          const int rr = it * 16 + (lane >> 1), row = row_base + rr;
+          if (row < M) {
+            const float4 x0 = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
+            const float4 x1 = *reinterpret_cast<const float4*>(&stg[rr * P + cg + 4]);
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(x0.x, x0.y), p1 = __floats2bfloat162_rn(x0.z, x0.w);
+            __nv_bfloat162 p2 = __floats2bfloat162_rn(x1.x, x1.y), p3 = __floats2bfloat162_rn(x1.z, x1.w);
+            uint4 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+            pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+            *reinterpret_cast<uint4*>(out + static_cast<int64_t>(row) * ep.ldo + cs + cg) = pk;
+          }
+        }
+      } else {
+        // generic path (ragged N, unaligned rows, bf16 + residual): one element per lane-iteration
+        const int cj = lane & 15, col = cs + cj;
+#pragma unroll 4
+        for (int it = 0; it < 16; ++it) {
+          const int rr = it * 2 + (lane >> 4), row = row_base + rr;
+          if (row < M && col < N) {
+            float o = stg[rr * P + cj];
+            if (ep.res) o += ep.res[static_cast<int64_t>(row) * ep.ld_res + col];
+            if (ep.out_bf16) static_cast<__nv_bfloat16*>(ep.out)[static_cast<int64_t>(row) * ep.ldo + col] = __float2bfloat16_rn(o);
+            else out_f32[static_cast<int64_t>(row) * ep.ldo + col] = o;
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
 template <int KIND, int BN>
 struct GemmCfg {
   static constexpr int BM = 128;
@@ -323,7 +461,6 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
                          (ep.split_stride & 3) == 0 &&
                          (!ep.res || ((ep.ld_res & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.res) & 15) == 0));
     const bool vec_bf16 = ep.out_bf16 && (ep.ldo & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 15) == 0 && !ep.res;
-    constexpr int CHUNKS = BN / 64;                 // 32-column chunks per warp
     uint32_t acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       const int z = item % splits, tile = item / splits;
@@ -338,136 +475,8 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      const int row_base = m0 + q * 32;
-      float* out_f32 = static_cast<float*>(ep.out) + static_cast<int64_t>(z) * ep.split_stride;
-      if (ep.amax_val) {
-        float best = -INFINITY;
-        int bidx = 0x7fffffff;
-#pragma unroll 1
-        for (int cc = 0; cc < CHUNKS; ++cc) {
-          const int c = col_half * CHUNKS + cc;
-          const int col0 = n0 + c * 32;
-          if (col0 >= N) break;
-          uint32_t r[32];
-          tmem_ld32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float v = __uint_as_float(r[j]);
-            if (ep.bias) v += bias_s[cc * 32 + j];
-            if (col0 + j < N && v > best) { best = v; bidx = col0 + j; }     // ascending scan: first maximum wins
-          }
-        }
-        const int row = row_base + lane;
-        if (row < M) {
-          const int64_t slot = static_cast<int64_t>(row) * ep.amax_slots + (tile / tiles_m) * 2 + col_half;
-          ep.amax_val[slot] = best;
-          ep.amax_idx[slot] = bidx;
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-        continue;
-      }
-#pragma unroll 1
-      for (int cc = 0; cc < CHUNKS; ++cc) {
-        const int c = col_half * CHUNKS + cc;
-        const int col0 = n0 + c * 32;
-        if (col0 >= N) break;                        // warp-uniform
-        uint32_t r[32];
-        tmem_ld32(tmem_base + acc * BN + c * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
-        const bool full_cols = col0 + 32 <= N;
-        // Residual values are fetched NOW -- while the TMEM load is in flight and before any store
-        // of this chunk.  A load issued after a may-alias store has to wait for it; leaving the
-        // loads inside the store loop serialised eight ~700-cycle round trips per chunk.
-        const bool res_vec = ep.res != nullptr && vec_f32 && full_cols;
-        float4 rv[2][4];
-        if (res_vec) {
-          const int cg = (lane & 3) * 4;
-#pragma unroll
-          for (int sub = 0; sub < 2; ++sub)
-#pragma unroll
-            for (int it = 0; it < 4; ++it) {
-              const int row = row_base + it * 8 + (lane >> 2);
-              rv[sub][it] = row < M ? ld_produced(reinterpret_cast<const float4*>(ep.res + static_cast<int64_t>(row) * ep.ld_res +
-                                                                                 col0 + sub * 16 + cg))
-                                    : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
-        tmem_ld_wait();
-        float v[32];
-#pragma unroll
-        for (int j4 = 0; j4 < 8; ++j4) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e) v[4 * j4 + e] = __uint_as_float(r[4 * j4 + e]);
-          if (ep.bias) {
-            const float4 b4 = *reinterpret_cast<const float4*>(&bias_s[cc * 32 + 4 * j4]);     // smem broadcast
-            v[4 * j4] += b4.x; v[4 * j4 + 1] += b4.y; v[4 * j4 + 2] += b4.z; v[4 * j4 + 3] += b4.w;
-          }
-        }
-        if (ep.act == ACT_RELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        } else if (ep.act == ACT_GELU) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);
-        }
-#pragma unroll
-        for (int sub = 0; sub < 2; ++sub) {
-          const int cs = col0 + sub * 16;
-#pragma unroll
-          for (int j4 = 0; j4 < 4; ++j4)
-            *reinterpret_cast<float4*>(&stg[lane * P + 4 * j4]) =
-                make_float4(v[sub * 16 + 4 * j4], v[sub * 16 + 4 * j4 + 1], v[sub * 16 + 4 * j4 + 2], v[sub * 16 + 4 * j4 + 3]);
-          __syncwarp();
-          if (vec_f32 && full_cols) {
-            // 4 lanes x 16 B = one 64-byte row segment; 8 rows per instruction
-            const int cg = (lane & 3) * 4;
-#pragma unroll
-            for (int it = 0; it < 4; ++it) {
-              const int rr = it * 8 + (lane >> 2), row = row_base + rr;
-              if (row < M) {
-                float4 o = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
-                if (res_vec) { o.x += rv[sub][it].x; o.y += rv[sub][it].y; o.z += rv[sub][it].z; o.w += rv[sub][it].w; }
-                *reinterpret_cast<float4*>(out_f32 + static_cast<int64_t>(row) * ep.ldo + cs + cg) = o;
-              }
-            }
-          } else if (vec_bf16 && full_cols) {
-            // 2 lanes x 16 B (8 bf16) = one 32-byte row segment; 16 rows per instruction
-            __nv_bfloat16* out = static_cast<__nv_bfloat16*>(ep.out);
-            const int cg = (lane & 1) * 8;
-#pragma unroll
-            for (int it = 0; it < 2; ++it) {
-              const int rr = it * 16 + (lane >> 1), row = row_base + rr;
-              if (row < M) {
-                const float4 x0 = *reinterpret_cast<const float4*>(&stg[rr * P + cg]);
-                const float4 x1 = *reinterpret_cast<const float4*>(&stg[rr * P + cg + 4]);
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(x0.x, x0.y), p1 = __floats2bfloat162_rn(x0.z, x0.w);
-                __nv_bfloat162 p2 = __floats2bfloat162_rn(x1.x, x1.y), p3 = __floats2bfloat162_rn(x1.z, x1.w);
-                uint4 pk;
-                pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
-                pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
-                *reinterpret_cast<uint4*>(out + static_cast<int64_t>(row) * ep.ldo + cs + cg) = pk;
-              }
-            }
-          } else {
-            // generic path (ragged N, unaligned rows, bf16 + residual): one element per lane-iteration
-            const int cj = lane & 15, col = cs + cj;
-#pragma unroll 4
-            for (int it = 0; it < 16; ++it) {
-              const int rr = it * 2 + (lane >> 4), row = row_base + rr;
-              if (row < M && col < N) {
-                float o = stg[rr * P + cj];
-                if (ep.res) o += ep.res[static_cast<int64_t>(row) * ep.ld_res + col];
-                if (ep.out_bf16) static_cast<__nv_bfloat16*>(ep.out)[static_cast<int64_t>(row) * ep.ldo + col] = __float2bfloat16_rn(o);
-                else out_f32[static_cast<int64_t>(row) * ep.ldo + col] = o;
-              }
-            }
-          }
-          __syncwarp();
-        }
-      }
+      epilogue_tile<BN, P>(ep, stg, bias_s, tmem_base + acc * BN, m0, n0, M, N, q, col_half, lane, z, (tile / tiles_m) * 2,
+                           vec_f32, vec_bf16);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[acc]);

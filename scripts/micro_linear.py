@@ -64,4 +64,13 @@ run("fc8k_f32out", 8192, 3072, 768, reps=5)
 run("qkv8k", 8192, 2304, 768, out_bf16=True, reps=5)
 run("fc2_8k", 8192, 768, 3072, res=True, reps=5)
 run("proj8k", 8192, 768, 768, res=True, reps=5)
-run("sq4k", 4096, 4096, 4096, bias=False, reps=5)
+run("sq4k", 4096, 4096, 4096, bias=False, bn=256, reps=5)
+# the CTA-pair kernel (bn code 2) on the shapes that fill 74 pairs
+run("sq4k_pair", 4096, 4096, 4096, bias=False, bn=2, reps=5)
+run("sq8k_pair", 8192, 8192, 8192, bias=False, bn=2, out_bf16=True, reps=3)
+run("sq8k_bn256", 8192, 8192, 8192, bias=False, bn=256, out_bf16=True, reps=3)
+run("fc8k_gelu_pair", 8192, 3072, 768, bn=2, out_bf16=True, act=2, reps=5)
+run("qkv8k_pair", 8192, 2304, 768, bn=2, out_bf16=True, reps=5)
+run("fc2_8k_pair", 8192, 768, 3072, bn=2, res=True, reps=5)
+run("head_pair", 2048, 50257, 768, bn=2, bias=False, reps=5)
+run("head_bn256", 2048, 50257, 768, bn=256, bias=False, reps=5)

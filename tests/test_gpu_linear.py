@@ -59,8 +59,9 @@ SHAPES = [(128, 128, 64), (128, 128, 512), (256, 384, 256), (200, 136, 72), (1, 
           (2048, 3072, 768), (128, 512, 4096)]
 
 
-@pytest.mark.parametrize("kind,tile_n", [(0, 128), (0, 256), (1, 128), (1, 256), (2, 128)])
-@pytest.mark.parametrize("shape", SHAPES)
+# tile_n 2 = the CTA-pair kernel (tcgen05 cta_group::2, one 256 x 256 tile per pair of SMs)
+@pytest.mark.parametrize("kind,tile_n", [(0, 128), (0, 256), (0, 2), (1, 128), (1, 256), (2, 128)])
+@pytest.mark.parametrize("shape", SHAPES + [(1000, 1300, 200), (4096, 4096, 1024)])
 def test_exact_on_small_integers(cuda_engine, kind, tile_n, shape):
     M, N, K = shape
     g = torch.Generator().manual_seed(M * 7 + N * 3 + K)
@@ -76,7 +77,8 @@ def test_exact_on_small_integers(cuda_engine, kind, tile_n, shape):
 
 @pytest.mark.parametrize("shape", SHAPES)
 @pytest.mark.parametrize("act,use_res,out_bf16", [(0, False, False), (2, False, True), (0, True, False)])
-def test_bf16_random(cuda_engine, shape, act, use_res, out_bf16):
+@pytest.mark.parametrize("tile_n", [0, 2])
+def test_bf16_random(cuda_engine, shape, act, use_res, out_bf16, tile_n):
     M, N, K = shape
     if out_bf16 and N % 2:
         pytest.skip("bf16 output needs even N")
@@ -85,7 +87,7 @@ def test_bf16_random(cuda_engine, shape, act, use_res, out_bf16):
     w = (torch.randn(N, K, generator=g) / K ** 0.5).to(torch.bfloat16).to(DEV)
     bias = torch.randn(N, generator=g).to(DEV)
     res = torch.randn(M, N, generator=g).to(DEV) if use_res else None
-    out = _linear(cuda_engine, 0, a, w, bias, res, act, out_bf16)
+    out = _linear(cuda_engine, 0, a, w, bias, res, act, out_bf16, tile_n=tile_n)
     want = _ref(a, w, bias, res, act)
     tol = 2e-2 if out_bf16 else 1e-4
     assert (out.double() - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
@@ -148,7 +150,7 @@ def test_throughput_report(cuda_engine):
     shapes = [(4096, 4096, 4096), (8192, 8192, 8192), (2048, 3072, 1024), (2048, 1024, 4096), (2048, 50304, 1024),
               (2048, 2304, 768), (32768, 3072, 768)]
     for (M, N, K) in shapes:
-        for kind, tile_n in [(0, 128), (0, 256), (1, 256), (2, 128)]:
+        for kind, tile_n in [(0, 128), (0, 256), (0, 2), (1, 256), (2, 128)]:
             if kind != 0 and M * N * K > 4096 ** 3:
                 continue
             dt = torch.bfloat16 if kind == 0 else torch.float32
