@@ -50,6 +50,7 @@ _PROTOTYPES = {
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_stage_trace": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong), C.c_int]),
     "b2p_debug_attn_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
+    "b2p_debug_fc_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_stage_forward_argmax": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_linear": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
@@ -68,6 +69,8 @@ _PROTOTYPES = {
     "b2p_ring_send": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]),
     "b2p_ring_recv": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p), C.c_void_p]),
     "b2p_ring_release": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
+    "b2p_stage_forward_ring": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                         C.c_void_p, C.c_uint64, C.c_void_p]),
 }
 
 _lib = None

@@ -14,6 +14,7 @@
 #include "gpt_simt.cuh"
 #include "stage.cuh"
 #include "tc_gemm2.cuh"
+#include "fc_stage_tc.cuh"
 
 using namespace b2p;
 
@@ -104,7 +105,10 @@ int alloc_gpt_workspace(b2p_stage* st) {
 
 // ---- forward implementations -------------------------------------------------------
 
-int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
+constexpr RingHook kNoHook{nullptr, nullptr};
+
+int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s,
+                        RingHook acq = kNoHook, RingHook pub = kNoHook, int* ticket = nullptr) {
   const int dev = st->d.device;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -114,7 +118,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH_PDL_BIT(2, cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
-                   st->w2img, st->dev(3), out, (int)batch, st->trace);
+                   st->w2img, st->dev(3), out, (int)batch, st->trace, acq, pub, ticket);
   return 0;
 }
 
@@ -131,8 +135,34 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
                  bool out_bf16, int M, int N, int K, cudaStream_t s, int splits = 1, int64_t split_stride = 0,
                  float* amax_val = nullptr, int* amax_idx = nullptr, int amax_slots = 0);
 
-int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s) {
+// B2P_FC_FUSED=0 keeps the three-kernel path (split, split-K linear, tail) for A/B measurements
+bool fc_fused_enabled() {
+  static const bool on = [] { const char* e = getenv("B2P_FC_FUSED"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s,
+                        RingHook wait = kNoHook, RingHook rel = kNoHook) {
   const bool tcm = st->d.math != B2P_MATH_FP32;
+  if (st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled()) {
+    // fc1 with the activation split inside the kernel (fc_stage_tc.cuh), 32 K slices, then the shared tail
+    const size_t need = fcs::ws_bytes(batch);
+    if (need > st->fc_ws_bytes) {
+      if (st->fc_ws) B2P_CUDA(cudaFree(st->fc_ws));
+      st->fc_ws = nullptr;
+      st->fc_ws_bytes = 0;
+      B2P_CUDA(cudaMalloc((void**)&st->fc_ws, need));
+      st->fc_ws_bytes = need;
+    }
+    const b2p_weight& w = st->w[0];
+    static const int only = [] { const char* e = getenv("B2P_FC_ONLY"); return e ? atoi(e) : 0; }();   // timing aid
+    if (only != 2)
+    B2P_TRY(fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, wait));
+    if (only != 1)
+    B2P_LAUNCH_PDL(fc_tail_f32<fcs::NSLICES>, (int)batch + (rel.flag ? 1 : 0), 128, 0, s, st->fc_ws, (int)batch, st->dev(1),
+                   st->dev(2), st->dev(3), out, rel);
+    return 0;
+  }
   const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);
   const size_t need = (size_t)splits * batch * FC1_N * sizeof(float);
   if (need > st->fc_ws_bytes) {
@@ -152,10 +182,10 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   }
   if (tcm)
     B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS_TC>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
-                   st->dev(3), out);
+                   st->dev(3), out, kNoHook);
   else
     B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
-                   st->dev(3), out);
+                   st->dev(3), out, kNoHook);
   return 0;
 }
 
@@ -585,6 +615,11 @@ int b2p_debug_attn_trace(long long* host_out, int n) {
   return attn::read_attn_trace(host_out, n);
 }
 
+int b2p_debug_fc_trace(long long* host_out, int n) {
+  if (!host_out) return fail(B2P_EINVAL, "null argument");
+  return fcs::read_fc_trace(host_out, n);
+}
+
 int b2p_stage_check(b2p_stage* st, void* stream) {
   if (!st) return fail(B2P_EINVAL, "null stage");
   if (!st->bad_flag) return 0;
@@ -612,6 +647,77 @@ int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev
 }  // extern "C"
 
 #include "handoff.cuh"
+
+// =====================================================================================
+// Stage forward with the handoff-ring handshake folded into the stage's own kernels.
+// Same meaning as  recv -> forward -> release  (ring_in)  and  acquire -> forward -> publish
+// (ring_out); for the CIFAR tensor-core kernels the four one-thread kernels disappear
+// (ring_hooks.cuh), every other stage composes the existing calls.
+// =====================================================================================
+namespace {
+int64_t stage_out_bytes(b2p_stage* st, int64_t batch, int64_t seq) {
+  switch (st->d.kind) {
+    case B2P_CIFAR_PART0: return batch * 4096 * 4;
+    case B2P_CIFAR_PART1: return batch * 10 * 4;
+    case B2P_GPT_FINAL: return batch * seq * (int64_t)st->d.vocab_size * 4;
+    default: return batch * seq * (int64_t)st->d.n_embd * 4;
+  }
+}
+}  // namespace
+
+extern "C" int b2p_stage_forward_ring(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
+                                      b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, void* stream) {
+  using namespace b2p;
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  if (!ring_in && !in_dev) return fail(B2P_EINVAL, "forward_ring: no input (neither a ring nor a device pointer)");
+  if (!ring_out && !out_dev) return fail(B2P_EINVAL, "forward_ring: no output (neither a ring nor a device pointer)");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_forward called before stage_finalize");
+  if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  if (ring_in && !ring_in->owner) return fail(B2P_ESTATE, "forward_ring: ring_in must be the consumer side of a ring");
+  if (ring_out && ring_out->owner) return fail(B2P_ESTATE, "forward_ring: ring_out must be the producer side of a ring");
+  if (ring_out && (uint64_t)stage_out_bytes(st, batch, seq_len) > ring_out->slot_bytes)
+    return fail(B2P_ELIMIT, "forward_ring: output of %lld bytes exceeds the slot size %zu",
+                (long long)stage_out_bytes(st, batch, seq_len), ring_out->slot_bytes);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const void* in = ring_in ? ring_in->data + (seq % ring_in->slots) * ring_in->slot_bytes : in_dev;
+  void* out = ring_out ? ring_out->data + (seq % ring_out->slots) * ring_out->slot_bytes : out_dev;
+  const bool hooked = (st->d.kind == B2P_CIFAR_PART0 && st->d.math != B2P_MATH_FP32) ||
+                      (st->d.kind == B2P_CIFAR_PART1 && st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled());
+  if (hooked) {
+    DeviceGuard g(st->d.device);
+    RingHook h_in = kNoHook, h_out_acq = kNoHook, h_out_pub = kNoHook;
+    if (ring_in) h_in = RingHook{ring_in->local_count + (seq % ring_in->slots), published(ring_in, seq)};
+    RingHook h_rel = ring_in ? RingHook{ring_in->local_count + (seq % ring_in->slots), released(ring_in, seq)} : kNoHook;
+    if (ring_out) {
+      h_out_acq = RingHook{ring_out->local_count + (seq % ring_out->slots), released(ring_out, seq)};
+      h_out_pub = RingHook{ring_out->local_count + (seq % ring_out->slots), published(ring_out, seq)};
+    }
+    if (st->d.kind == B2P_CIFAR_PART0) {
+      if (ring_in) {          // (not a configuration the pipelines use: part 0 takes the request tensor)
+        void* slot = nullptr;
+        B2P_TRY(b2p_ring_recv(ring_in, seq, &slot, stream));
+      }
+      B2P_TRY(cifar_part0_forward(st, static_cast<const float*>(in), static_cast<float*>(out), batch, s, h_out_acq, h_out_pub,
+                                  ring_out ? ring_out->ticket : nullptr));
+      if (ring_in) B2P_TRY(b2p_ring_release(ring_in, seq, stream));
+      return 0;
+    }
+    if (ring_out) {
+      void* slot = nullptr;
+      B2P_TRY(b2p_ring_acquire(ring_out, seq, &slot, stream));
+    }
+    B2P_TRY(cifar_part1_forward(st, static_cast<const float*>(in), static_cast<float*>(out), batch, s, h_in, h_rel));
+    if (ring_out) B2P_TRY(b2p_ring_publish(ring_out, seq, stream));
+    return 0;
+  }
+  void* slot = nullptr;
+  if (ring_in) B2P_TRY(b2p_ring_recv(ring_in, seq, &slot, stream));
+  if (ring_out) B2P_TRY(b2p_ring_acquire(ring_out, seq, &slot, stream));
+  B2P_TRY(b2p_stage_forward(st, in, out, batch, seq_len, stream));
+  if (ring_in) B2P_TRY(b2p_ring_release(ring_in, seq, stream));
+  if (ring_out) B2P_TRY(b2p_ring_publish(ring_out, seq, stream));
+  return 0;
+}
 
 // =====================================================================================
 // Allocation-free variant of the CIFAR part-1 forward (fc1 split-K + tail).
@@ -679,6 +785,6 @@ extern "C" int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* 
   dim3 grid(FC1_N / 64, ceil_div(batch, 64), FC1_SPLITS);
   B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, x_dev, fc1_weight_dev, scratch, (int)batch, FC1_K / FC1_SPLITS);
   B2P_LAUNCH(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, scratch, (int)batch, fc1_bias_dev, fc2_weight_dev,
-             fc2_bias_dev, out_dev);
+             fc2_bias_dev, out_dev, b2p::RingHook{nullptr, nullptr});
   return 0;
 }

@@ -10,6 +10,7 @@
 //   fc_tail_f32       reduce + bias + ReLU + fc2 + softmax   :55-57
 #pragma once
 #include "common.cuh"
+#include "ring_hooks.cuh"
 
 namespace b2p {
 
@@ -211,11 +212,16 @@ fc_tail_f32(const float* __restrict__ ws, int M,
             const float* __restrict__ b1,
             const float* __restrict__ w2,     // [10,512]
             const float* __restrict__ b2,
-            float* __restrict__ out) {        // [M,10]
+            float* __restrict__ out,          // [M,10]
+            RingHook rel) {                   // fc1's input was a handoff-ring slot: release it (ring_hooks.cuh)
   const int m = blockIdx.x, tid = threadIdx.x;
   pdl_trigger();
   float4 h = __ldg(reinterpret_cast<const float4*>(b1) + tid);      // constant weight: may precede the wait
   pdl_wait();
+  if (m >= M) {              // one extra CTA when a ring slot has to be released: the fc1 kernel (the slot's only
+    if (tid == 0) hook_release(rel);      // reader) has completed -- that is what the wait above waited for
+    return;
+  }
   float4 p[SPLITS];
 #pragma unroll
   for (int z = 0; z < SPLITS; ++z)      // plain loads, NOT __ldg: ws was written by the previous kernel, and the compiler

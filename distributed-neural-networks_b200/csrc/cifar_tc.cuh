@@ -30,6 +30,7 @@
 
 #include "common.cuh"
 #include "tc_gemm.cuh"
+#include "ring_hooks.cuh"
 
 namespace b2p {
 namespace cifar_tc {
@@ -113,7 +114,8 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
          const float* __restrict__ w1t,              // [27][32]
          const float* __restrict__ b1, const unsigned char* __restrict__ w2img,
          const float* __restrict__ b2, float* __restrict__ out,   // [B,4096]
-         int batch, long long* __restrict__ dbg) {   // dbg: optional [3 roles][8 samples][8 events] clock64 trace of CTA 0
+         int batch, long long* __restrict__ dbg,     // dbg: optional [3 roles][8 samples][8 events] clock64 trace of CTA 0
+         RingHook acq, RingHook pub, int* ticket) {  // out is a handoff-ring slot: wait for its release, publish it (ring_hooks.cuh)
 #define B2P_TRACE(role, n, ev, cond) \
   do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
   // (offset arithmetic on the __shared__ array itself, not on a uintptr_t: the compiler keeps
@@ -330,6 +332,14 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     // =========================== epilogue =======================================================
     const int q = warp & 3;                                  // TMEM lane quarter: image rows 2q, 2q+1 of the tile
     const int et = tid - kEpiWarp0 * 32;                     // 0..127
+    // The slot may still be in use by the consumer: poll its release counter (on the consumer's GPU, over
+    // NVLink) now, while conv1 and the tensor core are busy, long before this warp's first store.
+    // ONE thread per CTA polls (every poll is a read of the same remote line), the other epilogue threads are
+    // held at a named barrier -- they have nothing to do before the first accumulator is ready anyway.
+    if (acq.flag) {
+      if (et == 0) hook_wait_released(acq);
+      named_bar(2, kEpiThreads);
+    }
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       const uint32_t set = n & 1, use = n >> 1;
@@ -381,6 +391,21 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
       named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
       B2P_TRACE(2, n, 3, et == 0);
+    }
+    if (pub.flag) {
+      // The CTA's peer stores are all issued (barrier); ONE thread fences at gpu scope (cumulative over what the
+      // barrier ordered before it) and takes a ticket.  The last CTA has then observed every arrival, and its
+      // release store of the flag -- the only system-scope fence on this path -- carries all of them.
+      named_bar(2, kEpiThreads);
+      if (et == 0) {
+        __threadfence();
+        const int old = atomicAdd(ticket, 1);
+        if (old == (int)gridDim.x - 1) {
+          *ticket = 0;                                        // ready for the next launch
+          __threadfence();
+          hook_publish(pub);
+        }
+      }
     }
   }
 

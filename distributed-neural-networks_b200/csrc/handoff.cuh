@@ -19,7 +19,7 @@
 #include <cstring>
 
 #include "common.cuh"
-#include "tc_gemm.cuh"     // global_ns()
+#include "ring_hooks.cuh"
 
 struct b2p_ring {
   int consumer_dev = -1, producer_dev = -1;
@@ -34,6 +34,7 @@ struct b2p_ring {
   // on the device (instead of passing targets as kernel arguments) makes every wait / publish kernel
   // launch identical from step to step, so a whole step can be captured in a CUDA graph and replayed.
   unsigned long long* local_count = nullptr;   // producer side: published per slot; consumer side: consumed per slot
+  int* ticket = nullptr;              // producer side: CTA arrival ticket of a stage kernel that publishes by itself (ring_hooks.cuh)
 };
 
 namespace b2p {
@@ -47,25 +48,6 @@ struct RingWire {                      // what travels in the opaque 256-byte ha
 static_assert(sizeof(RingWire) <= B2P_RING_HANDLE_BYTES, "handle too small");
 constexpr uint64_t kRingMagic = 0x62327072696e6731ull;   // "b2pring1"
 
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-__device__ __forceinline__ void spin_until_ge(const unsigned long long* flag, unsigned long long target) {
-  if (ld_acquire_sys(flag) >= target) return;
-  const uint64_t t0 = tc::global_ns();
-  unsigned ns = 32;
-  while (ld_acquire_sys(flag) < target) {           // one thread; traps after 20 s instead of hanging
-    __nanosleep(ns);
-    if (ns < 1024) ns *= 2;
-    if (tc::global_ns() - t0 > 20000000000ull) __trap();
-  }
-}
 // All four are one-thread, stream-ordered kernels whose arguments never change between steps.
 // producer, before writing a slot: the consumer must have released every earlier message of that slot
 __global__ void ring_acquire_k(const unsigned long long* count, const unsigned long long* released_flag) {
@@ -147,8 +129,9 @@ int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->owner = true;
-  cudaError_t ce = cudaMalloc((void**)&r->local_count, slots * sizeof(unsigned long long));
-  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, slots * sizeof(unsigned long long));
+  cudaError_t ce = cudaMalloc((void**)&r->local_count, (slots + 4) * sizeof(unsigned long long));
+  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (slots + 4) * sizeof(unsigned long long));
+  r->ticket = reinterpret_cast<int*>(r->local_count + slots);
   if (ce != cudaSuccess) {
     cudaFree(base);
     delete r;
@@ -196,8 +179,9 @@ int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->ipc = true;
-  B2P_CUDA(cudaMalloc((void**)&r->local_count, r->slots * sizeof(unsigned long long)));
-  B2P_CUDA(cudaMemset(r->local_count, 0, r->slots * sizeof(unsigned long long)));
+  B2P_CUDA(cudaMalloc((void**)&r->local_count, (r->slots + 4) * sizeof(unsigned long long)));
+  B2P_CUDA(cudaMemset(r->local_count, 0, (r->slots + 4) * sizeof(unsigned long long)));
+  r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
   B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
   return 0;
@@ -221,10 +205,12 @@ int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_de
   r->ipc = false;
   r->producer_dev = producer_device;
   r->local_count = nullptr;
+  r->ticket = nullptr;
   {
     DeviceGuard g(producer_device);
-    B2P_CUDA(cudaMalloc((void**)&r->local_count, r->slots * sizeof(unsigned long long)));
-    B2P_CUDA(cudaMemset(r->local_count, 0, r->slots * sizeof(unsigned long long)));
+    B2P_CUDA(cudaMalloc((void**)&r->local_count, (r->slots + 4) * sizeof(unsigned long long)));
+    B2P_CUDA(cudaMemset(r->local_count, 0, (r->slots + 4) * sizeof(unsigned long long)));
+    r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
     B2P_CUDA(cudaDeviceSynchronize());
   }
   *out = r;

@@ -1,0 +1,106 @@
+// ring_hooks.cuh -- one side of a handoff-ring handshake, small enough to live INSIDE a stage kernel.
+//
+// handoff.cuh does the slot handshake with one-thread kernels (wait / publish / recv / release), which keeps the
+// compute kernels unaware of rings but costs a serialised launch (~2.5 us) each: five kernels per 128-sample
+// microbatch on the FC rank of the 2-GPU CIFAR pipeline, more time than the arithmetic.  A RingHook hands the same
+// two pointers to the compute kernel instead:
+//   consumer: the thread that loads the slot waits for `published`; the first kernel that runs after the last
+//             reader stores `released`;
+//   producer: the storing warps wait for `released` while the tensor core is still busy, and the last CTA to
+//             finish (arrival ticket) stores `published` after a system-scope fence.
+// Counters stay in device memory exactly as in handoff.cuh, so launches still carry no step-dependent argument and
+// a captured CUDA graph replays verbatim.  (Replaces node.py:73-89 / :45-48, like handoff.cuh.)
+#pragma once
+#include <cstdint>
+
+namespace b2p {
+
+struct RingHook {                  // all null: no ring on this side
+  unsigned long long* count;       // this GPU's message counter of the slot (local device memory)
+  unsigned long long* flag;        // the slot's published / released counter (consumer GPU's memory)
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_count(const unsigned long long* p) {      // written by an earlier kernel
+  unsigned long long v;
+  asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t hook_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Measured on 2 x B200: a system-scope fence costs ~2.5 us when peer traffic is outstanding, so the hooks use as few
+// as the memory model allows and keep them off the critical path where they can.
+// Flag in LOCAL memory (the consumer waiting for `published`): acquire loads.
+__device__ __forceinline__ void spin_until_ge(const unsigned long long* flag, unsigned long long target) {
+  if (ld_acquire_sys(flag) >= target) return;
+  const uint64_t t0 = hook_ns();
+  unsigned ns = 32;
+  while (ld_acquire_sys(flag) < target) {           // one thread; traps after 20 s instead of hanging
+    __nanosleep(ns);
+    if (ns < 1024) ns *= 2;
+    if (hook_ns() - t0 > 20000000000ull) __trap();
+  }
+}
+// Flag on ANOTHER GPU (the producer waiting for `released`): every poll is an NVLink round trip, so poll relaxed
+// and pay for the acquire once, after the value has been seen.
+__device__ __forceinline__ void spin_until_ge_remote(const unsigned long long* flag, unsigned long long target) {
+  if (ld_relaxed_sys(flag) < target) {
+    const uint64_t t0 = hook_ns();
+    unsigned ns = 64;
+    while (ld_relaxed_sys(flag) < target) {
+      __nanosleep(ns);
+      if (ns < 1024) ns *= 2;
+      if (hook_ns() - t0 > 20000000000ull) __trap();
+    }
+  }
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
+}
+
+// consumer, before reading the slot (one thread)
+__device__ __forceinline__ void hook_wait_published(const RingHook& h) {
+  if (h.flag) spin_until_ge(h.flag, ld_count(h.count) + 1);
+}
+// consumer, after the last read of the slot (one thread of one CTA)
+__device__ __forceinline__ void hook_release(const RingHook& h) {
+  if (h.flag) {
+    const unsigned long long k = ld_count(h.count) + 1;
+    *h.count = k;
+    st_relaxed_sys(h.flag, k);       // nothing to publish but "my reads are over", and they are: their kernel has completed
+  }
+}
+// producer, before the first store into the slot (any number of threads may call it; it only reads)
+__device__ __forceinline__ void hook_wait_released(const RingHook& h) {
+  if (h.flag) {
+    const unsigned long long k = ld_count(h.count);      // messages already published into this slot
+    if (k > 0) spin_until_ge_remote(h.flag, k);
+  }
+}
+// producer, one thread of the last CTA, after it has observed every other CTA's arrival (each behind a gpu-scope
+// fence): the release store's system-scope fence is cumulative over all of them
+__device__ __forceinline__ void hook_publish(const RingHook& h) {
+  if (h.flag) {
+    const unsigned long long k = ld_count(h.count) + 1;
+    *h.count = k;
+    st_release_sys(h.flag, k);
+  }
+}
+
+}  // namespace b2p

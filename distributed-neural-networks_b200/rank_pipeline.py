@@ -48,10 +48,10 @@ def plan(world: int, stages: int) -> list[RankRole]:
 
 
 def quiet_nccl():
-    """NCCL_DEBUG=VERSION makes NCCL print a banner on stdout, where bench.py must print exactly one
-    JSON line; keep warnings, drop the banner (an explicit INFO/TRACE setting is left alone)."""
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    """bench.py must print exactly one JSON line on stdout, and NCCL writes its version banner (any NCCL_DEBUG
+    level from VERSION up, which some images export by default) to stdout too: send NCCL's log to stderr instead,
+    unless the caller already chose a file."""
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 
 def exchange_handles(my_handle: bytes | None, group=None) -> list:
@@ -110,13 +110,10 @@ class CifarRankPipeline:
             if self.role.stage == 0:
                 if ready is not None:
                     self.stream.wait_event(ready[i])
-                slot = self.ring.acquire(self.seq, s)                 # peer memory on the next GPU
-                self.part.forward_ptr(x[lo:].data_ptr(), slot, n, 0, s)   # epilogue stores cross NVLink
-                self.ring.publish(self.seq, s)
+                # epilogue stores cross NVLink into the next GPU's slot; the slot handshake is inside the kernel
+                self.part.forward_ring(x[lo:].data_ptr(), None, n, 0, None, self.ring, self.seq, s)
             else:
-                slot = self.ring.recv(self.seq, s)
-                self.part.forward_ptr(slot, self.out_dev[lo:].data_ptr(), n, 0, s)
-                self.ring.release(self.seq, s)
+                self.part.forward_ring(None, self.out_dev[lo:].data_ptr(), n, 0, self.ring, None, self.seq, s)
             self.seq += 1
 
     def step_graph(self, x: torch.Tensor | None):
@@ -259,6 +256,23 @@ def bench_main(args) -> int:
     checksum = float(pipe.out_host.sum()) if role.active and role.stage == 1 else 0.0
     ct = torch.tensor([checksum], device=dev)
     dist.all_reduce(ct)
+    # Did the ring deliver the right activations?  The FC rank regenerates its producer's last input batch (same
+    # seeded generator), runs BOTH parts locally through the plain two-call path and compares with what came out
+    # of the cross-GPU pipeline in the last end-to-end step: the kernels are deterministic, so it must be bit-exact.
+    mismatch = 0.0
+    if role.active and role.stage == 1:
+        gp = torch.Generator().manual_seed(role.prev_rank)
+        pool = [torch.randn(BATCH, 3, 32, 32, generator=gp) for _ in range(n_pool)]
+        x_last = pool[(W + K - 1) % n_pool].to(dev)
+        torch.manual_seed(1234)
+        full = engine.NeuralNetwork()
+        p0 = engine.MODEL_PARTS_CLASSES[0](full, math=args.math).to(dev)
+        p0.load_state_dict(full.state_dict(), strict=False)
+        with torch.no_grad():
+            want = torch.cat([pipe.part(p0.eval()(x_last[lo:lo + MICROBATCH])) for lo in range(0, BATCH, MICROBATCH)])
+        mismatch = float((want.cpu() - pipe.out_host).abs().max())
+    mt = torch.tensor([mismatch], device=dev)
+    dist.all_reduce(mt, op=dist.ReduceOp.MAX)
 
     # roofline: stage-0 kernel timed alone on rank 0's launch stream
     roofline = None
@@ -297,7 +311,8 @@ def bench_main(args) -> int:
                        "math": args.math, "launch": "cuda_graph_per_step_per_rank" if use_graph else "per_kernel",
                        "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
-                    "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0])},
+                    "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0]),
+                    "max_abs_diff_vs_single_gpu_path": float(mt[0])},
             "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None,
         }
         print(json.dumps(line), flush=True)

@@ -184,6 +184,15 @@ class EngineStage(nn.Module):
         _lib.check(_lib.lib().b2p_stage_forward(
             self._handle, C.c_void_p(in_ptr), C.c_void_p(out_ptr), batch, seq, C.c_void_p(stream)))
 
+    def forward_ring(self, in_ptr: int | None, out_ptr: int | None, batch: int, seq_len: int, ring_in, ring_out,
+                     seq: int, stream: int):
+        """forward_ptr with the handoff handshake inside the stage's kernels (b2p_stage_forward_ring):
+        ring_in (consumer side) replaces in_ptr, ring_out (producer side) replaces out_ptr."""
+        _lib.check(_lib.lib().b2p_stage_forward_ring(
+            self._handle, C.c_void_p(in_ptr), C.c_void_p(out_ptr), batch, seq_len,
+            ring_in._h if ring_in is not None else None, ring_out._h if ring_out is not None else None,
+            seq, C.c_void_p(stream)))
+
 
 # =============================================================================================
 # CIFAR-10 parts (cifar_model_parts.py)

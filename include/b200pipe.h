@@ -152,6 +152,10 @@ B2P_API int b2p_stage_trace(b2p_stage* st, long long* host_out, int n);
  * attention launch on the current device; 193 entries [role 0..2][key tile 0..7][event 0..7] + start. */
 B2P_API int b2p_debug_attn_trace(long long* host_out, int n);
 
+/* Developer aid (no reference counterpart): with B2P_FC_TRACE=1 in the environment, clock64 timeline of the
+ * 128 CTAs of row tile 0 of the last fused CIFAR part-1 launch; 2048 entries [hidden tile 0..3][K slice 0..31][event 0..15]. */
+B2P_API int b2p_debug_fc_trace(long long* host_out, int n);
+
 /* GPT final only: greedy token ids (row arg-max of the logits) without
  * materialising [B,T,V]; out int64 [batch,seq].  (north_star: "greedy token ids") */
 B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
@@ -232,6 +236,19 @@ B2P_API int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uin
 B2P_API int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream);
 /* consumer: mark message seq consumed (enqueue after the last kernel that reads the slot). */
 B2P_API int b2p_ring_release(b2p_ring* ring, uint64_t seq, void* stream);
+
+/* One node's whole SendTensor body (node.py:45-89: receive the tensor, run the part, forward the result) as ONE
+ * call: the stage's forward with the ring handshake folded into its own kernels.
+ *   ring_in  != NULL (consumer side): the input is message `seq` of ring_in (in_dev ignored); same meaning as
+ *             b2p_ring_recv -> forward -> b2p_ring_release.
+ *   ring_out != NULL (producer side): the output is stored straight into slot `seq` of ring_out (out_dev ignored);
+ *             same meaning as b2p_ring_acquire -> forward -> b2p_ring_publish.
+ * The CIFAR tensor-core kernels do the waiting and the flag stores themselves (csrc/ring_hooks.cuh), so the four
+ * one-thread kernels and their launch latencies disappear; every other stage composes the calls above.  Messages of
+ * one slot must be used in order, as with the separate calls.  Errors: B2P_EINVAL (missing input/output),
+ * B2P_ESTATE (stage not finalized, ring used from the wrong side), B2P_ELIMIT (output larger than a slot). */
+B2P_API int b2p_stage_forward_ring(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
+                                   b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, void* stream);
 
 #ifdef __cplusplus
 }

@@ -166,6 +166,31 @@ def test_tensor_core_fc_stage(cuda_engine, mode, tol):
         assert torch.equal(p1(x), torch.cat([p1(x[:128]), p1(x[128:])]))
 
 
+def test_fc1_in_kernel_split_rows_and_back_to_back_launches(cuda_engine):
+    """Part 1 with the activation split inside the fc1 kernel (fc_stage_tc.cuh): ragged batches, rows at any
+    offset inside a 128-row tile, the same answer call after call, and launches queued back to back on one
+    stream (programmatic dependent launch must not let launch i+1 overwrite partial sums launch i still reads)."""
+    sd = co.init_state_dict(1234)
+    p1 = cuda_engine.ModelPart1_2Node(cuda_engine.NeuralNetwork(), math="tf32x3").to("cuda:0")
+    p1.load_state_dict(sd, strict=False)
+    p1.eval()
+    x = co.part0(co.make_input(1000, seed=4242), sd)
+    want = co.part1(x, sd)
+    xd = x.cuda()
+    with torch.no_grad():
+        whole = p1(xd)
+        assert (whole.cpu() - want).abs().max().item() <= PROB_TOL
+        for lo, n in [(0, 1), (0, 5), (3, 127), (64, 129), (500, 257), (999, 1), (0, 1000)]:
+            got = p1(xd[lo:lo + n].contiguous())
+            assert torch.equal(got, whole[lo:lo + n]), f"rows {lo}..{lo + n}"
+        # 64 launches queued without a host sync in between, alternating inputs
+        a, b = xd[:128].contiguous(), xd[128:256].contiguous()
+        outs = [p1(a if i % 2 == 0 else b) for i in range(64)]
+        torch.cuda.synchronize()
+        for i, o in enumerate(outs):
+            assert torch.equal(o, whole[:128] if i % 2 == 0 else whole[128:256]), f"launch {i}"
+
+
 @pytest.fixture(scope="module")
 def tc_parts(cuda_engine):
     """Both parts in the tensor-core parity mode: conv2 as a split-fp16 implicit GEMM

@@ -65,6 +65,47 @@ def test_zero_copy_acquire_publish_with_a_stage(cuda_engine):
     assert (got.cpu() - co.part0(x.cpu(), sd)).abs().max().item() <= 2e-5
 
 
+@pytest.mark.parametrize("math", ["tf32x3", "fp32"])
+def test_forward_ring_handshake_inside_the_stage_kernels(cuda_engine, math):
+    """b2p_stage_forward_ring: part 0 stores into the slot and publishes it, part 1 waits, reads and releases --
+    with the handshake inside the tensor-core kernels (tf32x3) or composed from the one-thread kernels (fp32).
+    Twelve microbatches through a 2-slot ring (every counter wraps six times), ragged sizes, one stream in
+    producer-then-consumer order; results must equal the plain two-call path bit for bit."""
+    Ring = import_module("distributed-neural-networks_b200.handoff").Ring
+    from oracle import cifar_oracle as co
+    sd = co.init_state_dict(1234)
+    parts = []
+    for k in (0, 1):
+        p = cuda_engine.MODEL_PARTS_CLASSES[k](cuda_engine.NeuralNetwork(), math=math).to("cuda:0")
+        p.load_state_dict(sd, strict=False)
+        parts.append(p.eval())
+    p0, p1 = parts
+    ring = Ring.create(0, slots=2, slot_bytes=128 * 4096 * 4)
+    prod = ring.open_local(0)
+    s = torch.cuda.current_stream().cuda_stream
+    sizes = [128, 128, 1, 77, 128, 128, 128, 5, 128, 128, 64, 128]
+    xs = [co.make_input(n, seed=100 + i).cuda() for i, n in enumerate(sizes)]
+    outs = [torch.empty(n, 10, device="cuda:0") for n in sizes]
+    for seq, (x, o) in enumerate(zip(xs, outs)):
+        p0.forward_ring(x.data_ptr(), None, x.shape[0], 0, None, prod, seq, s)
+        p1.forward_ring(None, o.data_ptr(), x.shape[0], 0, ring, None, seq, s)
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        for x, o in zip(xs, outs):
+            assert torch.equal(o, p1(p0(x)))
+    # wrong side / oversize / missing operands are refused before anything is enqueued
+    L = cuda_engine._lib
+    with pytest.raises(L.EngineError, match="consumer side"):
+        p1.forward_ring(None, outs[0].data_ptr(), 1, 0, prod, None, 0, s)
+    with pytest.raises(L.EngineError, match="producer side"):
+        p0.forward_ring(xs[0].data_ptr(), None, 1, 0, None, ring, 0, s)
+    with pytest.raises(L.EngineError, match="exceeds the slot size"):
+        big = torch.zeros(129, 3, 32, 32, device="cuda:0")
+        p0.forward_ring(big.data_ptr(), None, 129, 0, None, prod, 0, s)
+    with pytest.raises(L.EngineError, match="no input"):
+        p1.forward_ring(None, outs[0].data_ptr(), 1, 0, None, None, 0, s)
+
+
 def test_ring_argument_errors(cuda_engine):
     L = cuda_engine._lib
     Ring = import_module("distributed-neural-networks_b200.handoff").Ring
