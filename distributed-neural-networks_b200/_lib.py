@@ -71,6 +71,8 @@ _PROTOTYPES = {
     "b2p_ring_release": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     "b2p_stage_forward_ring": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
                                          C.c_void_p, C.c_uint64, C.c_void_p]),
+    "b2p_stage_forward_ring_span": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p,
+                                              C.c_void_p, C.c_uint64, C.c_int64, C.c_void_p]),
 }
 
 _lib = None

@@ -105,10 +105,10 @@ int alloc_gpt_workspace(b2p_stage* st) {
 
 // ---- forward implementations -------------------------------------------------------
 
-constexpr RingHook kNoHook{nullptr, nullptr};
+const RingSpan kNoSpan{};
 
 int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s,
-                        RingHook acq = kNoHook, RingHook pub = kNoHook, int* ticket = nullptr) {
+                        RingSpan span = kNoSpan) {
   const int dev = st->d.device;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -118,7 +118,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH_PDL_BIT(2, cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
-                   st->w2img, st->dev(3), out, (int)batch, st->trace, acq, pub, ticket);
+                   st->w2img, st->dev(3), out, (int)batch, st->trace, span);
   return 0;
 }
 
@@ -142,7 +142,7 @@ bool fc_fused_enabled() {
 }
 
 int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s,
-                        RingHook wait = kNoHook, RingHook rel = kNoHook) {
+                        RingSpan span = kNoSpan) {
   const bool tcm = st->d.math != B2P_MATH_FP32;
   if (st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled()) {
     // fc1 with the activation split inside the kernel (fc_stage_tc.cuh), 32 K slices, then the shared tail
@@ -157,10 +157,10 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     const b2p_weight& w = st->w[0];
     static const int only = [] { const char* e = getenv("B2P_FC_ONLY"); return e ? atoi(e) : 0; }();   // timing aid
     if (only != 2)
-    B2P_TRY(fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, wait));
+    B2P_TRY(fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, span));
     if (only != 1)
-    B2P_LAUNCH_PDL(fc_tail_f32<fcs::NSLICES>, (int)batch + (rel.flag ? 1 : 0), 128, 0, s, st->fc_ws, (int)batch, st->dev(1),
-                   st->dev(2), st->dev(3), out, rel);
+    B2P_LAUNCH_PDL(fc_tail_f32<fcs::NSLICES>, (int)batch + (span.data ? 1 : 0), 128, 0, s, st->fc_ws, (int)batch, st->dev(1),
+                   st->dev(2), st->dev(3), out, span);
     return 0;
   }
   const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);
@@ -182,10 +182,10 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   }
   if (tcm)
     B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS_TC>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
-                   st->dev(3), out, kNoHook);
+                   st->dev(3), out, kNoSpan);
   else
     B2P_LAUNCH_PDL(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
-                   st->dev(3), out, kNoHook);
+                   st->dev(3), out, kNoSpan);
   return 0;
 }
 
@@ -665,58 +665,91 @@ int64_t stage_out_bytes(b2p_stage* st, int64_t batch, int64_t seq) {
 }
 }  // namespace
 
-extern "C" int b2p_stage_forward_ring(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
-                                      b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, void* stream) {
+namespace {
+b2p::RingSpan span_of(b2p_ring* r, uint64_t seq, int64_t rows_per_msg) {
+  b2p::RingSpan sp{};
+  sp.count = r->local_count;
+  sp.published = r->flags;
+  sp.released = r->flags + r->slots;
+  sp.data = r->data;
+  sp.slot_bytes = r->slot_bytes;
+  sp.slots = r->slots;
+  sp.first_slot = (int)(seq % r->slots);
+  sp.rows_per_msg = (int)rows_per_msg;
+  sp.tickets = r->ticket;
+  return sp;
+}
+int64_t stage_in_bytes(b2p_stage* st, int64_t batch, int64_t seq) {
+  switch (st->d.kind) {
+    case B2P_CIFAR_PART0: return batch * 3 * 32 * 32 * 4;
+    case B2P_CIFAR_PART1: return batch * 4096 * 4;
+    case B2P_GPT_FIRST: return batch * seq * 8;                       // int64 token ids
+    default: return batch * seq * (int64_t)st->d.n_embd * 4;
+  }
+}
+}  // namespace
+
+extern "C" int b2p_stage_forward_ring_span(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
+                                           b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, int64_t rows_per_msg,
+                                           void* stream) {
   using namespace b2p;
   if (!st) return fail(B2P_EINVAL, "null stage");
   if (!ring_in && !in_dev) return fail(B2P_EINVAL, "forward_ring: no input (neither a ring nor a device pointer)");
   if (!ring_out && !out_dev) return fail(B2P_EINVAL, "forward_ring: no output (neither a ring nor a device pointer)");
   if (!st->finalized) return fail(B2P_ESTATE, "stage_forward called before stage_finalize");
   if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  if (rows_per_msg <= 0) return fail(B2P_EINVAL, "forward_ring: rows_per_msg must be positive");
   if (ring_in && !ring_in->owner) return fail(B2P_ESTATE, "forward_ring: ring_in must be the consumer side of a ring");
   if (ring_out && ring_out->owner) return fail(B2P_ESTATE, "forward_ring: ring_out must be the producer side of a ring");
-  if (ring_out && (uint64_t)stage_out_bytes(st, batch, seq_len) > ring_out->slot_bytes)
+  const int64_t msgs = (batch + rows_per_msg - 1) / rows_per_msg;
+  const int64_t msg_rows = std::min(batch, rows_per_msg);
+  if (ring_out && (uint64_t)stage_out_bytes(st, msg_rows, seq_len) > ring_out->slot_bytes)
     return fail(B2P_ELIMIT, "forward_ring: output of %lld bytes exceeds the slot size %zu",
-                (long long)stage_out_bytes(st, batch, seq_len), ring_out->slot_bytes);
+                (long long)stage_out_bytes(st, msg_rows, seq_len), ring_out->slot_bytes);
+  if ((ring_in && msgs > ring_in->slots) || (ring_out && msgs > ring_out->slots))
+    return fail(B2P_ELIMIT, "forward_ring: %lld messages in one call, the ring has fewer slots", (long long)msgs);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const void* in = ring_in ? ring_in->data + (seq % ring_in->slots) * ring_in->slot_bytes : in_dev;
-  void* out = ring_out ? ring_out->data + (seq % ring_out->slots) * ring_out->slot_bytes : out_dev;
-  const bool hooked = (st->d.kind == B2P_CIFAR_PART0 && st->d.math != B2P_MATH_FP32) ||
-                      (st->d.kind == B2P_CIFAR_PART1 && st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled());
-  if (hooked) {
+  const bool hooked_out = ring_out && st->d.kind == B2P_CIFAR_PART0 && st->d.math != B2P_MATH_FP32 && !ring_in;
+  const bool hooked_in = ring_in && st->d.kind == B2P_CIFAR_PART1 && st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled() &&
+                         !ring_out && (rows_per_msg == fcs::BM || (msgs == 1 && batch <= fcs::BM)) &&
+                         ring_in->slot_bytes == (size_t)fcs::BM * fcs::K_IN * 4;
+  if (hooked_out) {
     DeviceGuard g(st->d.device);
-    RingHook h_in = kNoHook, h_out_acq = kNoHook, h_out_pub = kNoHook;
-    if (ring_in) h_in = RingHook{ring_in->local_count + (seq % ring_in->slots), published(ring_in, seq)};
-    RingHook h_rel = ring_in ? RingHook{ring_in->local_count + (seq % ring_in->slots), released(ring_in, seq)} : kNoHook;
-    if (ring_out) {
-      h_out_acq = RingHook{ring_out->local_count + (seq % ring_out->slots), released(ring_out, seq)};
-      h_out_pub = RingHook{ring_out->local_count + (seq % ring_out->slots), published(ring_out, seq)};
-    }
-    if (st->d.kind == B2P_CIFAR_PART0) {
-      if (ring_in) {          // (not a configuration the pipelines use: part 0 takes the request tensor)
-        void* slot = nullptr;
-        B2P_TRY(b2p_ring_recv(ring_in, seq, &slot, stream));
-      }
-      B2P_TRY(cifar_part0_forward(st, static_cast<const float*>(in), static_cast<float*>(out), batch, s, h_out_acq, h_out_pub,
-                                  ring_out ? ring_out->ticket : nullptr));
-      if (ring_in) B2P_TRY(b2p_ring_release(ring_in, seq, stream));
-      return 0;
-    }
-    if (ring_out) {
-      void* slot = nullptr;
-      B2P_TRY(b2p_ring_acquire(ring_out, seq, &slot, stream));
-    }
-    B2P_TRY(cifar_part1_forward(st, static_cast<const float*>(in), static_cast<float*>(out), batch, s, h_in, h_rel));
-    if (ring_out) B2P_TRY(b2p_ring_publish(ring_out, seq, stream));
-    return 0;
+    return cifar_part0_forward(st, static_cast<const float*>(in_dev), static_cast<float*>(out_dev), batch, s,
+                               span_of(ring_out, seq, rows_per_msg));
   }
-  void* slot = nullptr;
-  if (ring_in) B2P_TRY(b2p_ring_recv(ring_in, seq, &slot, stream));
-  if (ring_out) B2P_TRY(b2p_ring_acquire(ring_out, seq, &slot, stream));
-  B2P_TRY(b2p_stage_forward(st, in, out, batch, seq_len, stream));
-  if (ring_in) B2P_TRY(b2p_ring_release(ring_in, seq, stream));
-  if (ring_out) B2P_TRY(b2p_ring_publish(ring_out, seq, stream));
+  if (hooked_in) {
+    DeviceGuard g(st->d.device);
+    return cifar_part1_forward(st, nullptr, static_cast<float*>(out_dev), batch, s, span_of(ring_in, seq, fcs::BM));
+  }
+  // every other stage: one message at a time through the one-thread handshake kernels
+  for (int64_t m = 0; m < msgs; ++m) {
+    const int64_t rows = std::min(rows_per_msg, batch - m * rows_per_msg);
+    void* slot = nullptr;
+    const void* in = nullptr;
+    void* out = nullptr;
+    if (ring_in) {
+      B2P_TRY(b2p_ring_recv(ring_in, seq + m, &slot, stream));
+      in = slot;
+    } else {
+      in = static_cast<const unsigned char*>(in_dev) + m * stage_in_bytes(st, rows_per_msg, seq_len);
+    }
+    if (ring_out) {
+      B2P_TRY(b2p_ring_acquire(ring_out, seq + m, &slot, stream));
+      out = slot;
+    } else {
+      out = static_cast<unsigned char*>(out_dev) + m * stage_out_bytes(st, rows_per_msg, seq_len);
+    }
+    B2P_TRY(b2p_stage_forward(st, in, out, rows, seq_len, stream));
+    if (ring_in) B2P_TRY(b2p_ring_release(ring_in, seq + m, stream));
+    if (ring_out) B2P_TRY(b2p_ring_publish(ring_out, seq + m, stream));
+  }
   return 0;
+}
+
+extern "C" int b2p_stage_forward_ring(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
+                                      b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, void* stream) {
+  return b2p_stage_forward_ring_span(st, in_dev, out_dev, batch, seq_len, ring_in, ring_out, seq, batch > 0 ? batch : 1, stream);
 }
 
 // =====================================================================================
@@ -785,6 +818,6 @@ extern "C" int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* 
   dim3 grid(FC1_N / 64, ceil_div(batch, 64), FC1_SPLITS);
   B2P_LAUNCH(fc1_splitk_f32, grid, 256, 0, s, x_dev, fc1_weight_dev, scratch, (int)batch, FC1_K / FC1_SPLITS);
   B2P_LAUNCH(fc_tail_f32<FC1_SPLITS>, (int)batch, 128, 0, s, scratch, (int)batch, fc1_bias_dev, fc2_weight_dev,
-             fc2_bias_dev, out_dev, b2p::RingHook{nullptr, nullptr});
+             fc2_bias_dev, out_dev, b2p::RingSpan{});
   return 0;
 }

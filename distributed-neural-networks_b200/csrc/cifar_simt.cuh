@@ -213,13 +213,19 @@ fc_tail_f32(const float* __restrict__ ws, int M,
             const float* __restrict__ w2,     // [10,512]
             const float* __restrict__ b2,
             float* __restrict__ out,          // [M,10]
-            RingHook rel) {                   // fc1's input was a handoff-ring slot: release it (ring_hooks.cuh)
+            RingSpan span) {                  // span.data: fc1's input came from handoff-ring slots: release them
   const int m = blockIdx.x, tid = threadIdx.x;
   pdl_trigger();
   float4 h = __ldg(reinterpret_cast<const float4*>(b1) + tid);      // constant weight: may precede the wait
   pdl_wait();
-  if (m >= M) {              // one extra CTA when a ring slot has to be released: the fc1 kernel (the slot's only
-    if (tid == 0) hook_release(rel);      // reader) has completed -- that is what the wait above waited for
+  if (m >= M) {              // one extra CTA when ring slots have to be released: the fc1 kernel (their only reader)
+    const int msgs = (M + span.rows_per_msg - 1) / span.rows_per_msg;      // has completed -- the wait above waited for that
+    if (tid < msgs) {
+      const int slot = span_slot(span, tid);
+      const unsigned long long k = ld_count(span.count + slot) + 1;
+      span.count[slot] = k;
+      st_relaxed_sys(span.released + slot, k);    // nothing to publish but "my reads are over"
+    }
     return;
   }
   float4 p[SPLITS];

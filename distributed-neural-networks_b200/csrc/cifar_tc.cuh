@@ -115,7 +115,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
          const float* __restrict__ b1, const unsigned char* __restrict__ w2img,
          const float* __restrict__ b2, float* __restrict__ out,   // [B,4096]
          int batch, long long* __restrict__ dbg,     // dbg: optional [3 roles][8 samples][8 events] clock64 trace of CTA 0
-         RingHook acq, RingHook pub, int* ticket) {  // out is a handoff-ring slot: wait for its release, publish it (ring_hooks.cuh)
+         RingSpan span) {                            // span.data: rows go into handoff-ring slots instead of out (ring_hooks.cuh)
 #define B2P_TRACE(role, n, ev, cond) \
   do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
   // (offset arithmetic on the __shared__ array itself, not on a uintptr_t: the compiler keeps
@@ -332,18 +332,29 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     // =========================== epilogue =======================================================
     const int q = warp & 3;                                  // TMEM lane quarter: image rows 2q, 2q+1 of the tile
     const int et = tid - kEpiWarp0 * 32;                     // 0..127
-    // The slot may still be in use by the consumer: poll its release counter (on the consumer's GPU, over
-    // NVLink) now, while conv1 and the tensor core are busy, long before this warp's first store.
-    // ONE thread per CTA polls (every poll is a read of the same remote line), the other epilogue threads are
-    // held at a named barrier -- they have nothing to do before the first accumulator is ready anyway.
-    if (acq.flag) {
-      if (et == 0) hook_wait_released(acq);
-      named_bar(2, kEpiThreads);
-    }
+    int acquired = -1;                                       // last message whose slot this CTA has waited for
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       const uint32_t set = n & 1, use = n >> 1;
       B2P_TRACE(2, n, 0, et == 0);
+      float* dst_row = out + (size_t)b * 4096;
+      int msg = 0, slot = 0;
+      if (span.data) {
+        // Row b travels in message b / rows_per_msg.  Its slot may still be in use by the consumer: ONE thread per
+        // CTA polls the release counter (on the consumer's GPU, over NVLink) the first time the CTA meets the
+        // message -- here, before the wait for the accumulator, so the round trip hides behind the tensor core.
+        msg = b / span.rows_per_msg;
+        slot = span_slot(span, msg);
+        if (msg != acquired) {
+          if (et == 0) {
+            const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
+            if (k > 0) spin_until_ge_remote(span.released + slot, k);
+          }
+          named_bar(2, kEpiThreads);
+          acquired = msg;
+        }
+        dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
+      }
       const bool xo = (lane & 1) != 0, yo = (lane & 16) != 0;
 #pragma unroll 1
       for (int t = 0; t < 2; ++t) {
@@ -385,27 +396,27 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       if (lane == 0) mbar_arrive(&s.bar_tmem_empty[set]);
       B2P_TRACE(2, n, 2, et == 0);
       named_bar(2, kEpiThreads);                              // the sample's 4096 outputs are staged
-      float4* dst = reinterpret_cast<float4*>(out + (size_t)b * 4096);
+      float4* dst = reinterpret_cast<float4*>(dst_row);
       const float4* src = reinterpret_cast<const float4*>(s.out);
 #pragma unroll
       for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
       named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
-      B2P_TRACE(2, n, 3, et == 0);
-    }
-    if (pub.flag) {
-      // The CTA's peer stores are all issued (barrier); ONE thread fences at gpu scope (cumulative over what the
-      // barrier ordered before it) and takes a ticket.  The last CTA has then observed every arrival, and its
-      // release store of the flag -- the only system-scope fence on this path -- carries all of them.
-      named_bar(2, kEpiThreads);
-      if (et == 0) {
+      if (span.data && et == 0) {
+        // The row's peer stores are all issued (barrier).  ONE thread fences at gpu scope (cumulative over what the
+        // barrier ordered before it) and counts the row in; whoever stores the message's last row has observed
+        // every other arrival, and its release store of the flag -- the only system-scope fence on this path, paid
+        // once per message -- carries all of them.  The other epilogue threads go on to the next sample meanwhile.
         __threadfence();
-        const int old = atomicAdd(ticket, 1);
-        if (old == (int)gridDim.x - 1) {
-          *ticket = 0;                                        // ready for the next launch
+        const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
+        if (atomicAdd(span.tickets + slot, 1) == rows - 1) {
+          span.tickets[slot] = 0;                             // ready for the slot's next message
           __threadfence();
-          hook_publish(pub);
+          const unsigned long long k = ld_count(span.count + slot) + 1;
+          span.count[slot] = k;
+          st_release_sys(span.published + slot, k);
         }
       }
+      B2P_TRACE(2, n, 3, et == 0);
     }
   }
 

@@ -55,7 +55,7 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
             const __grid_constant__ CUtensorMap tmap_w_lo,    // fc1.weight lo plane
             float* __restrict__ ws,                           // partial sums [32][M][512]
             int M, int trace_on,
-            RingHook wait) {                                  // x is a handoff-ring slot: wait for its publication
+            RingSpan span) {                                  // span.data: tmap_x covers the whole ring, row tile mt is message mt
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* tiles = smem;
@@ -105,9 +105,13 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     }
     __syncwarp();
     pdl_wait();          // x belongs to the previous kernel until here
-    if (wait.flag) {
+    int x_row0 = m0;
+    if (span.data) {
+      // row tile mt is message mt of this launch: wait until the producer GPU has published it
+      const int slot = span_slot(span, mt);
+      x_row0 = slot * BM;                // the ring's slots are 128 rows each, back to back (checked by the host)
       if (lane == 0) {
-        hook_wait_published(wait);       // the producer GPU's stores are visible after this acquire ...
+        spin_until_ge(span.published + slot, ld_count(span.count + slot) + 1);     // acquire: the peer's stores are visible ...
         fence_proxy_async();             // ... also to the TMA unit (async proxy)
       }
       __syncwarp();
@@ -122,7 +126,7 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
           tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[stage], k0 + kb * KB, n0);
           tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[stage], k0 + kb * KB, n0);
         }
-        tma_load_2d(sa, &tmap_x, &full[stage], k0 + kb * KB, m0);                   // raw fp32, becomes the hi plane
+        tma_load_2d(sa, &tmap_x, &full[stage], k0 + kb * KB, x_row0);                   // raw fp32, becomes the hi plane
       }
       __syncwarp();
     }
@@ -210,7 +214,7 @@ inline size_t ws_bytes(int64_t batch) { return (size_t)NSLICES * batch * N_HIDDE
 
 // x [batch,4096] fp32; w_hi / w_lo: the tf32 planes of fc1.weight [512,4096]; ws: ws_bytes(batch).  One launch.
 inline int launch_fc1_x3_splitk(const float* x, const float* w_hi, const float* w_lo, float* ws, int64_t batch,
-                                cudaStream_t s, RingHook wait = RingHook{nullptr, nullptr}) {
+                                cudaStream_t s, RingSpan span = RingSpan{}) {
   static bool configured[64] = {};
   int dev = 0;
   B2P_CUDA(cudaGetDevice(&dev));
@@ -219,12 +223,18 @@ inline int launch_fc1_x3_splitk(const float* x, const float* w_hi, const float* 
     configured[dev] = true;
   }
   CUtensorMap tx, th, tl;
-  B2P_TRY(make_tmap(&tx, 1, x, batch, K_IN, K_IN, BM));
+  if (span.data) {       // every slot of the ring as one [slots*128, 4096] matrix
+    if (span.rows_per_msg != BM || span.slot_bytes != (unsigned long long)BM * K_IN * 4)
+      return fail(B2P_EINVAL, "fc1: a ring feeds this kernel in messages of exactly %d rows in %d-byte slots", BM, BM * K_IN * 4);
+    B2P_TRY(make_tmap(&tx, 1, span.data, (int64_t)span.slots * BM, K_IN, K_IN, BM));
+  } else {
+    B2P_TRY(make_tmap(&tx, 1, x, batch, K_IN, K_IN, BM));
+  }
   B2P_TRY(make_tmap(&th, 1, w_hi, N_HIDDEN, K_IN, K_IN, BN));
   B2P_TRY(make_tmap(&tl, 1, w_lo, N_HIDDEN, K_IN, K_IN, BN));
   dim3 grid(NSLICES, NTILES, ceil_div(batch, BM));
   static const int trace_on = [] { const char* e = getenv("B2P_FC_TRACE"); return (e && e[0] == '1') ? 1 : 0; }();
-  B2P_LAUNCH_PDL(fc1_x3_splitk, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, wait);
+  B2P_LAUNCH_PDL(fc1_x3_splitk, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, span);
   return 0;
 }
 inline int read_fc_trace(long long* host_out, int n) {

@@ -74,6 +74,21 @@ __device__ __forceinline__ void spin_until_ge_remote(const unsigned long long* f
   asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
 
+// A run of consecutive messages of one ring handled by ONE launch: rows [i*rows_per_msg, (i+1)*rows_per_msg) of the
+// launch's batch travel as message i, in slot (first_slot + i) % slots.  The producing kernel publishes each message
+// when its last row has been stored, the consuming kernel waits per message: the stages overlap at microbatch
+// granularity although each of them is a single launch per step.  data == nullptr: no ring.
+struct RingSpan {
+  unsigned long long* count;       // [slots] this GPU's message counters (local)
+  unsigned long long* published;   // [slots] on the consumer GPU
+  unsigned long long* released;    // [slots] on the consumer GPU
+  unsigned char* data;             // slot 0 (consumer GPU's memory)
+  unsigned long long slot_bytes;
+  int slots, first_slot, rows_per_msg;
+  int* tickets;                    // [slots] producer side: rows stored so far into the slot (local)
+};
+__device__ __forceinline__ int span_slot(const RingSpan& r, int msg) { return (r.first_slot + msg) % r.slots; }
+
 // consumer, before reading the slot (one thread)
 __device__ __forceinline__ void hook_wait_published(const RingHook& h) {
   if (h.flag) spin_until_ge(h.flag, ld_count(h.count) + 1);

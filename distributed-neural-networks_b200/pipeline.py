@@ -77,6 +77,21 @@ class LocalPipeline:
         assert b <= self.max_batch
         out = self.out_dev if out is None else out
         n_st = len(self.stages)
+        if ready is None and len(set(self.devs)) == 1 and all(getattr(st, "WHOLE_BATCH_OK", False) for st in self.stages):
+            # Every stage on ONE GPU and the batch already resident: micro-batching has nothing to overlap with (each
+            # stage's kernel fills the GPU), so each stage runs once over the whole batch on one stream -- same rows,
+            # same per-row arithmetic (fixed K slicing), bit-identical results, an eighth of the launches.
+            s = self.compute[0]
+            self._joined = []                  # no other stream took part (run_device_graph joins nothing)
+            prev = _lib.lib().b2p_set_pdl(3)
+            src = x
+            for k, st in enumerate(self.stages):
+                dst = out[:b] if k == n_st - 1 else self.hidden[k][:b]
+                st.forward_ptr(src.data_ptr(), dst.data_ptr(), b, seq, s.cuda_stream)
+                src = dst
+            _lib.lib().b2p_set_pdl(prev)
+            return out[:b]
+        self._joined = self.compute[1:]
         prev_pdl = _lib.lib().b2p_set_pdl(3 if self._pdl else 0)    # shared GPU: no early starts (measured: 0.199 vs 0.238 ms/step)
         for i, lo in enumerate(range(0, b, self.mb)):
             n = min(self.mb, b - lo)
@@ -124,7 +139,7 @@ class LocalPipeline:
             before = _lib.launch_count()
             with torch.cuda.graph(g, stream=main):
                 self.run_device(x, seq=seq)
-                for st in self.compute[1:]:
+                for st in self._joined:
                     main.wait_stream(st)
             entry = (g, _lib.launch_count() - before)
             self._graphs[key] = entry

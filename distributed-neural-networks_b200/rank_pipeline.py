@@ -105,6 +105,15 @@ class CifarRankPipeline:
     # ---- one step = one batch through this rank's stage ------------------------------------------
     def step_device(self, x: torch.Tensor | None, ready=None):
         s = self.stream.cuda_stream
+        if ready is None and self.n_mb <= self.slots:
+            # the whole step as ONE call: microbatch i is message seq+i; the stage-0 kernel publishes each message
+            # when its last row is stored, the stage-1 kernel waits message by message (b2p_stage_forward_ring_span)
+            if self.role.stage == 0:
+                self.part.forward_ring(x.data_ptr(), None, self.batch, 0, None, self.ring, self.seq, s, self.mb)
+            else:
+                self.part.forward_ring(None, self.out_dev.data_ptr(), self.batch, 0, self.ring, None, self.seq, s, self.mb)
+            self.seq += self.n_mb
+            return
         for i, lo in enumerate(range(0, self.batch, self.mb)):
             n = min(self.mb, self.batch - lo)
             if self.role.stage == 0:
@@ -197,6 +206,12 @@ def bench_main(args) -> int:
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     quiet_nccl()
+    # stdout carries exactly one JSON line: park the real stdout and point fd 1 at stderr while NCCL and torch
+    # initialise and run (NCCL prints its version banner with printf, whatever NCCL_DEBUG_FILE says)
+    import sys
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist.init_process_group("nccl", device_id=dev)
     roles = plan(world, 2)
     role = roles[rank]
@@ -315,7 +330,8 @@ def bench_main(args) -> int:
                     "max_abs_diff_vs_single_gpu_path": float(mt[0])},
             "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None,
         }
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     dist.barrier()
     dist.destroy_process_group()
     return 0

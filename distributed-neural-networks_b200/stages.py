@@ -185,13 +185,14 @@ class EngineStage(nn.Module):
             self._handle, C.c_void_p(in_ptr), C.c_void_p(out_ptr), batch, seq, C.c_void_p(stream)))
 
     def forward_ring(self, in_ptr: int | None, out_ptr: int | None, batch: int, seq_len: int, ring_in, ring_out,
-                     seq: int, stream: int):
-        """forward_ptr with the handoff handshake inside the stage's kernels (b2p_stage_forward_ring):
-        ring_in (consumer side) replaces in_ptr, ring_out (producer side) replaces out_ptr."""
-        _lib.check(_lib.lib().b2p_stage_forward_ring(
+                     seq: int, stream: int, rows_per_msg: int | None = None):
+        """forward_ptr with the handoff handshake inside the stage's kernels (b2p_stage_forward_ring[_span]):
+        ring_in (consumer side) replaces in_ptr, ring_out (producer side) replaces out_ptr.  rows_per_msg splits
+        the batch into consecutive messages seq, seq+1, ... handled by one call (one launch where fused)."""
+        _lib.check(_lib.lib().b2p_stage_forward_ring_span(
             self._handle, C.c_void_p(in_ptr), C.c_void_p(out_ptr), batch, seq_len,
             ring_in._h if ring_in is not None else None, ring_out._h if ring_out is not None else None,
-            seq, C.c_void_p(stream)))
+            seq, batch if rows_per_msg is None else rows_per_msg, C.c_void_p(stream)))
 
 
 # =============================================================================================
@@ -207,6 +208,7 @@ _CIFAR_SHAPES = {
 
 class _CifarPart(EngineStage):
     KEYS: tuple = ()
+    WHOLE_BATCH_OK = True       # no per-stage workspace bound: a pipeline on one GPU may run the batch in one call
 
     def __init__(self, original_model=None, math: str = "fp32"):
         super().__init__(math)

@@ -250,6 +250,16 @@ B2P_API int b2p_ring_release(b2p_ring* ring, uint64_t seq, void* stream);
 B2P_API int b2p_stage_forward_ring(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
                                    b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, void* stream);
 
+/* A whole step in one call: rows [i*rows_per_msg, (i+1)*rows_per_msg) of the batch travel as message seq+i (at most
+ * `slots` messages per call).  For the CIFAR tensor-core kernels this is ONE launch per stage per step: the producing
+ * kernel publishes each message as soon as its last row is stored, the consuming kernel waits message by message, so
+ * the two GPUs overlap at microbatch granularity (the micro-batched pipelining of the north star) without paying a
+ * launch per microbatch.  The fused consumer needs rows_per_msg == 128 and 2 MiB slots; anything else, and every other
+ * stage, runs message by message through the calls above with the same results. */
+B2P_API int b2p_stage_forward_ring_span(b2p_stage* st, const void* in_dev, void* out_dev, int64_t batch, int64_t seq_len,
+                                        b2p_ring* ring_in, b2p_ring* ring_out, uint64_t seq, int64_t rows_per_msg,
+                                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -80,6 +80,7 @@ def test_forward_ring_handshake_inside_the_stage_kernels(cuda_engine, math):
         p.load_state_dict(sd, strict=False)
         parts.append(p.eval())
     p0, p1 = parts
+    L = cuda_engine._lib
     ring = Ring.create(0, slots=2, slot_bytes=128 * 4096 * 4)
     prod = ring.open_local(0)
     s = torch.cuda.current_stream().cuda_stream
@@ -93,8 +94,21 @@ def test_forward_ring_handshake_inside_the_stage_kernels(cuda_engine, math):
     with torch.no_grad():
         for x, o in zip(xs, outs):
             assert torch.equal(o, p1(p0(x)))
+    # a whole step per call: 1000 rows as 8 messages of 128 (the last one ragged), one launch per stage where fused
+    ring8 = Ring.create(0, slots=8, slot_bytes=128 * 4096 * 4)
+    prod8 = ring8.open_local(0)
+    xb = co.make_input(1000, seed=77).cuda()
+    ob = torch.empty(1000, 10, device="cuda:0")
+    for step in range(3):                                    # slots are reused from step to step
+        p0.forward_ring(xb.data_ptr(), None, 1000, 0, None, prod8, 8 * step, s, 128)
+        p1.forward_ring(None, ob.data_ptr(), 1000, 0, ring8, None, 8 * step, s, 128)
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            assert torch.equal(ob, p1(p0(xb))), f"step {step}"
+        ob.zero_()
+    with pytest.raises(L.EngineError, match="fewer slots"):
+        p0.forward_ring(xb.data_ptr(), None, 1000, 0, None, prod8, 0, s, 64)
     # wrong side / oversize / missing operands are refused before anything is enqueued
-    L = cuda_engine._lib
     with pytest.raises(L.EngineError, match="consumer side"):
         p1.forward_ring(None, outs[0].data_ptr(), 1, 0, prod, None, 0, s)
     with pytest.raises(L.EngineError, match="producer side"):
