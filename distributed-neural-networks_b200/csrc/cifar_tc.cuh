@@ -40,7 +40,8 @@ using namespace tc;
 constexpr int kProducerWarps = 8, kProducerThreads = 256;
 constexpr int kMmaWarp = 8;
 constexpr int kEpiWarp0 = 9, kEpiThreads = 128;
-constexpr int kThreads = (kEpiWarp0 + 4) * 32;       // 416
+constexpr int kAcqWarp = kEpiWarp0 + 4, kPubWarp = kAcqWarp + 1;   // handoff-ring handshake, off the epilogue's critical path
+constexpr int kThreads = (kPubWarp + 1) * 32;        // 480
 
 constexpr int W2_TAP_BYTES = 64 * 128;               // [64 oc rows][128 B]
 constexpr int W2_BYTES = 9 * W2_TAP_BYTES;           // 73 728
@@ -57,6 +58,8 @@ struct Smem {
   float b2[64];
   uint64_t bar_w2, bar_act_full[2], bar_act_empty, bar_tmem_full[2][2], bar_tmem_empty[2];
   uint32_t tmem_slot;
+  int acq_upto;                                      // ring: samples of this CTA whose slot may be written (acquirer -> epilogue)
+  int stored;                                        // ring: epilogue warps that have issued a sample's peer stores (-> publisher)
 };
 constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
 
@@ -132,6 +135,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = w1t[i];
   if (tid < 32) s.b1[tid] = b1[tid];
   if (tid < 64) s.b2[tid] = b2[tid];
+  if (tid == 0) { s.acq_upto = 0; s.stored = 0; }
   if (warp == kMmaWarp) {
     if (lane == 0) {
       mbar_init(&s.bar_w2, 1);
@@ -328,7 +332,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       B2P_TRACE(1, n, 3, lane == 0);
       __syncwarp();
     }
-  } else {
+  } else if (warp < kAcqWarp) {
     // =========================== epilogue =======================================================
     const int q = warp & 3;                                  // TMEM lane quarter: image rows 2q, 2q+1 of the tile
     const int et = tid - kEpiWarp0 * 32;                     // 0..127
@@ -338,22 +342,10 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       const uint32_t set = n & 1, use = n >> 1;
       B2P_TRACE(2, n, 0, et == 0);
       float* dst_row = out + (size_t)b * 4096;
-      int msg = 0, slot = 0;
-      if (span.data) {
-        // Row b travels in message b / rows_per_msg.  Its slot may still be in use by the consumer: ONE thread per
-        // CTA polls the release counter (on the consumer's GPU, over NVLink) the first time the CTA meets the
-        // message -- here, before the wait for the accumulator, so the round trip hides behind the tensor core.
-        msg = b / span.rows_per_msg;
-        slot = span_slot(span, msg);
-        if (msg != acquired) {
-          if (et == 0) {
-            const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
-            if (k > 0) spin_until_ge_remote(span.released + slot, k);
-          }
-          named_bar(2, kEpiThreads);
-          acquired = msg;
-        }
-        dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
+      if (span.data) {           // row b travels in message b / rows_per_msg, in that message's ring slot
+        const int msg = b / span.rows_per_msg;
+        dst_row = reinterpret_cast<float*>(span.data + (size_t)span_slot(span, msg) * span.slot_bytes) +
+                  (size_t)(b - msg * span.rows_per_msg) * 4096;
       }
       const bool xo = (lane & 1) != 0, yo = (lane & 16) != 0;
 #pragma unroll 1
@@ -396,16 +388,46 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       if (lane == 0) mbar_arrive(&s.bar_tmem_empty[set]);
       B2P_TRACE(2, n, 2, et == 0);
       named_bar(2, kEpiThreads);                              // the sample's 4096 outputs are staged
+      if (span.data) {                                        // the slot must have been released by the consumer:
+        while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the acquirer warp polled for it long ago
+      }
       float4* dst = reinterpret_cast<float4*>(dst_row);
       const float4* src = reinterpret_cast<const float4*>(s.out);
 #pragma unroll
       for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
+      if (span.data) {                                        // hand the sample to the publisher warp
+        __syncwarp();
+        if (lane == 0) red_release_cta_add(&s.stored, 1);
+      }
       named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
-      if (span.data && et == 0) {
-        // The row's peer stores are all issued (barrier).  ONE thread fences at gpu scope (cumulative over what the
-        // barrier ordered before it) and counts the row in; whoever stores the message's last row has observed
-        // every other arrival, and its release store of the flag -- the only system-scope fence on this path, paid
-        // once per message -- carries all of them.  The other epilogue threads go on to the next sample meanwhile.
+      B2P_TRACE(2, n, 3, et == 0);
+    }
+  } else if (span.data && lane == 0) {
+    // =========================== handoff-ring handshake (ring_hooks.cuh) ========================
+    // Two single-thread roles kept OFF the epilogue warps: with one sample per CTA per message, every sample
+    // needs a poll of the consumer's release counter (an NVLink round trip) and an arrival ticket (fence + L2
+    // atomic); done by the epilogue they added ~40 us to a 64 us step.
+    uint32_t n = 0;
+    if (warp == kAcqWarp) {
+      // acquirer: runs ahead of the pipeline, one poll per message this CTA contributes to
+      int acquired = -1;
+      for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+        const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
+        if (msg != acquired) {
+          const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
+          if (k > 0) spin_until_ge_remote(span.released + slot, k);
+          acquired = msg;
+        }
+        st_release_cta(&s.acq_upto, (int)n + 1);
+      }
+    } else {
+      // publisher: once the four epilogue warps have issued sample n's peer stores (release/acquire at CTA scope),
+      // fence at gpu scope -- cumulative over those stores -- and count the row in.  Whoever counts a message's
+      // last row has observed every other arrival; its release store of the flag, the only system-scope fence
+      // on this path, carries all of them.
+      for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+        const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
+        while (ld_acquire_cta(&s.stored) < 4 * ((int)n + 1)) __nanosleep(64);
         __threadfence();
         const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
         if (atomicAdd(span.tickets + slot, 1) == rows - 1) {
@@ -416,7 +438,6 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           st_release_sys(span.published + slot, k);
         }
       }
-      B2P_TRACE(2, n, 3, et == 0);
     }
   }
 

@@ -89,6 +89,19 @@ struct RingSpan {
 };
 __device__ __forceinline__ int span_slot(const RingSpan& r, int msg) { return (r.first_slot + msg) % r.slots; }
 
+// CTA-scope hand-offs between warp roles of one kernel (shared-memory words)
+__device__ __forceinline__ int ld_acquire_cta(const int* p) {
+  int v;
+  asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_cta(int* p, int v) {
+  asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_cta_add(int* p, int v) {
+  asm volatile("red.release.cta.shared.add.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
 // consumer, before reading the slot (one thread)
 __device__ __forceinline__ void hook_wait_published(const RingHook& h) {
   if (h.flag) spin_until_ge(h.flag, ld_count(h.count) + 1);

@@ -12,6 +12,7 @@ from importlib import import_module
 Ring = import_module("distributed-neural-networks_b200.handoff").Ring
 
 MB, NMB, SLOTS = 128, 8, 8
+SPAN = True      # one call per step (b2p_stage_forward_ring_span) instead of one per microbatch
 d0, d1 = torch.device("cuda:0"), torch.device("cuda:1")
 torch.manual_seed(1234)
 full = engine.NeuralNetwork()
@@ -61,12 +62,17 @@ for name, act in (("local", act_local), ("peer", act_peer)):
 # b) producer alone (consumer = release kernels only)
 ring = Ring.create(1, SLOTS, MB * 4096 * 4); prod = ring.open_local(0)
 seq = [0]
-def prod_step(s):
+phase = {"p": 0, "c": 0, "fp": 0, "fc": 0}
+def prod_step(s, k="p"):
+    base = phase[k]; phase[k] = (base + NMB) % SLOTS
+    if SPAN:
+        return p0.forward_ring(x.data_ptr(), None, NMB * MB, 0, None, prod, base, s, MB)
     for i in range(NMB):
-        p0.forward_ring(x[i * MB:].data_ptr(), None, MB, 0, None, prod, i, s)
+        p0.forward_ring(x[i * MB:].data_ptr(), None, MB, 0, None, prod, base + i, s)
 def fake_cons_step(s):
+    base = phase["fc"]; phase["fc"] = (base + NMB) % SLOTS
     for i in range(NMB):
-        ring.recv(i, s); ring.release(i, s)
+        ring.recv(base + i, s); ring.release(base + i, s)
 gp, sp = graph_of(d0, prod_step, 1)
 with torch.cuda.device(d1):
     sc = torch.cuda.Stream(device=d1)
@@ -92,8 +98,11 @@ print(f"b) producer alone (fake consumer): producer {tp:6.2f} us/microbatch (fak
 
 # d) real pipeline: consumer graph
 def cons_step(s):
+    base = phase["c"]; phase["c"] = (base + NMB) % SLOTS
+    if SPAN:
+        return p1.forward_ring(None, out1.data_ptr(), NMB * MB, 0, ring, None, base, s, MB)
     for i in range(NMB):
-        p1.forward_ring(None, out1[i * MB:].data_ptr(), MB, 0, ring, None, i, s)
+        p1.forward_ring(None, out1[i * MB:].data_ptr(), MB, 0, ring, None, base + i, s)
 # warm-up pair eagerly (producer first)
 with torch.cuda.device(d0):
     prod_step(sp.cuda_stream)
@@ -112,8 +121,9 @@ print(f"d) real pipeline: producer {tp:6.2f}, consumer {tc:6.2f} us/microbatch")
 
 # c) consumer alone: fake producer publishes without writing
 def fake_prod_step(s):
+    base = phase["fp"]; phase["fp"] = (base + NMB) % SLOTS
     for i in range(NMB):
-        prod.acquire(i, s); prod.publish(i, s)
+        prod.acquire(base + i, s); prod.publish(base + i, s)
 with torch.cuda.device(d0):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(20):
