@@ -40,46 +40,54 @@ constexpr int NTILES = N_HIDDEN / BN;       // 4
 constexpr int PLANE = BM * 128;             // 16 KB: 128 rows x 32 fp32
 constexpr int STAGE_BYTES = 4 * PLANE;      // x hi | x lo | W hi | W lo
 constexpr int STAGES = 3;
+constexpr int EPI_PITCH = 36;               // floats: 32 columns + pad, 16-byte aligned rows
+constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;      // one [32][36] transpose buffer per epilogue warp
 constexpr int BAR_BYTES = 256;
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;
-constexpr int THREADS = 192;                // TMA warp, MMA warp, 4 convert/epilogue warps
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;
+constexpr int THREADS = 320;                // TMA warp, MMA warp, 4 converter warps, 4 epilogue warps
 
-// optional per-CTA timeline of row tile 0 (clock64 at 14 points, thread 64), read back by b2p_debug_fc_trace
+// optional timeline of the first work item of each CTA (clock64 at a few points), read back by b2p_debug_fc_trace
 __device__ long long g_fc_trace[NSLICES * NTILES * 16];
-#define FC_TRACE(ev) do { if (trace_on && threadIdx.x == 64 && blockIdx.z == 0) \
-    g_fc_trace[(blockIdx.y * NSLICES + blockIdx.x) * 16 + (ev)] = clock64(); } while (0)
+#define FC_TRACE(ev) do { if (trace_on && lane == 0 && blockIdx.x < NSLICES * NTILES) \
+    g_fc_trace[blockIdx.x * 16 + (ev)] = clock64(); } while (0)
 
+// Persistent: CTA c takes work items c, c + gridDim.x, ...; item = (K slice z, hidden tile j, row tile mt) with z
+// fastest, so the 128 items of a row tile (= one ring message) are adjacent.  The smem stage ring and the two
+// accumulator stages in tensor memory run on across items: the loads and MMAs of item i+1 overlap the epilogue of
+// item i, and only the first item of a CTA sees the ~1.2 us TMA start-up latency.
 __global__ void __launch_bounds__(THREADS, 1)
 fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp32, box [32 k][128 rows]
-            const __grid_constant__ CUtensorMap tmap_w_hi,    // fc1.weight hi plane [512,4096], box [32 k][128 rows]
-            const __grid_constant__ CUtensorMap tmap_w_lo,    // fc1.weight lo plane
-            float* __restrict__ ws,                           // partial sums [32][M][512]
-            int M, int trace_on,
-            RingSpan span) {                                  // span.data: tmap_x covers the whole ring, row tile mt is message mt
+              const __grid_constant__ CUtensorMap tmap_w_hi,    // fc1.weight hi plane [512,4096], box [32 k][128 rows]
+              const __grid_constant__ CUtensorMap tmap_w_lo,    // fc1.weight lo plane
+              float* __restrict__ ws,                           // partial sums [32][M][512]
+              int M, int trace_on,
+              RingSpan span) {                                  // span.data: tmap_x covers the whole ring, row tile mt is message mt
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* tiles = smem;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  float* epi_smem = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + EPI_BYTES);
   uint64_t* full = bars;                  // [STAGES] TMA -> converters, MMA
   uint64_t* conv = bars + STAGES;         // [STAGES] converters -> MMA
   uint64_t* empty = bars + 2 * STAGES;    // [STAGES] MMA -> TMA
-  uint64_t* tmem_full = bars + 3 * STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* tmem_full = bars + 3 * STAGES;   // [2] MMA -> epilogue
+  uint64_t* tmem_empty = tmem_full + 2;      // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int z = blockIdx.x, j = blockIdx.y, mt = blockIdx.z;
-  const int m0 = mt * BM, n0 = j * BN, k0 = z * KSLICE;
+  const int m_tiles = (M + BM - 1) / BM;
+  const int num_items = NSLICES * NTILES * m_tiles;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w_hi)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w_lo)) : "memory");
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&conv[i], 4); mbar_init(&empty[i], 1); }
-    mbar_init(tmem_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, BN);
+    tmem_alloc(tmem_slot, 2 * BN);
     tmem_relinquish();
   }
   FC_TRACE(0);
@@ -88,126 +96,161 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  FC_TRACE(1);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    // fc1.weight is constant: its first STAGES k-blocks are requested BEFORE griddepcontrol.wait, so two thirds of
-    // this CTA's bytes are already on their way while the previous kernel in the stream drains.
-    if (lane == 0) {
+    // fc1.weight is constant: the first item's first STAGES k-blocks are requested BEFORE griddepcontrol.wait, so
+    // most of that item's bytes are on their way while the previous kernel in the stream drains.
+    const int first = blockIdx.x;
+    if (lane == 0 && first < num_items) {
+      const int z = first % NSLICES, j = (first / NSLICES) % NTILES;
 #pragma unroll
       for (int kb = 0; kb < (KBLOCKS < STAGES ? KBLOCKS : STAGES); ++kb) {
         unsigned char* sa = tiles + kb * STAGE_BYTES;
         mbar_expect_tx(&full[kb], 3 * PLANE);
-        tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[kb], k0 + kb * KB, n0);
-        tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[kb], k0 + kb * KB, n0);
+        tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[kb], z * KSLICE + kb * KB, j * BN);
+        tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[kb], z * KSLICE + kb * KB, j * BN);
       }
     }
     __syncwarp();
     pdl_wait();          // x belongs to the previous kernel until here
-    int x_row0 = m0;
-    if (span.data) {
-      // row tile mt is message mt of this launch: wait until the producer GPU has published it
-      const int slot = span_slot(span, mt);
-      x_row0 = slot * BM;                // the ring's slots are 128 rows each, back to back (checked by the host)
-      if (lane == 0) {
-        spin_until_ge(span.published + slot, ld_count(span.count + slot) + 1);     // acquire: the peer's stores are visible ...
-        fence_proxy_async();             // ... also to the TMA unit (async proxy)
-      }
-      __syncwarp();
-    }
-    for (int kb = 0; kb < KBLOCKS; ++kb) {
-      const int stage = kb % STAGES, round = kb / STAGES;
-      mbar_wait(&empty[stage], (round & 1) ^ 1);
-      if (lane == 0) {
-        unsigned char* sa = tiles + stage * STAGE_BYTES;
-        if (kb >= STAGES) {
-          mbar_expect_tx(&full[stage], 3 * PLANE);
-          tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[stage], k0 + kb * KB, n0);
-          tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[stage], k0 + kb * KB, n0);
+    uint32_t stage = 0, phase = 0;
+    int waited_mt = -1, x_row0 = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int z = item % NSLICES, j = (item / NSLICES) % NTILES, mt = item / (NSLICES * NTILES);
+      if (mt != waited_mt) {
+        x_row0 = mt * BM;
+        if (span.data) {
+          // row tile mt is message mt of this launch: wait until the producer GPU has published it
+          const int slot = span_slot(span, mt);
+          x_row0 = slot * BM;              // the ring's slots are 128 rows each, back to back (checked by the host)
+          if (lane == 0) {
+            spin_until_ge(span.published + slot, ld_count(span.count + slot) + 1);     // acquire: the peer's stores are visible ...
+            fence_proxy_async();           // ... also to the TMA unit (async proxy)
+          }
+          __syncwarp();
         }
-        tma_load_2d(sa, &tmap_x, &full[stage], k0 + kb * KB, x_row0);                   // raw fp32, becomes the hi plane
+        waited_mt = mt;
       }
-      __syncwarp();
+      for (int kb = 0; kb < KBLOCKS; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        if (lane == 0) {
+          unsigned char* sa = tiles + stage * STAGE_BYTES;
+          if (item != first || kb >= STAGES) {
+            mbar_expect_tx(&full[stage], 3 * PLANE);
+            tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[stage], z * KSLICE + kb * KB, j * BN);
+            tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[stage], z * KSLICE + kb * KB, j * BN);
+          }
+          tma_load_2d(sa, &tmap_x, &full[stage], z * KSLICE + kb * KB, x_row0);      // raw fp32, becomes the hi plane
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = make_idesc(1, BM, BN);
-    for (int kb = 0; kb < KBLOCKS; ++kb) {
-      const int stage = kb % STAGES, round = kb / STAGES;
-      mbar_wait(&full[stage], round & 1);
-      mbar_wait(&conv[stage], round & 1);
+    uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
-      if (lane == 0) {
-        const uint32_t base = smem_u32(tiles + stage * STAGE_BYTES);
-        const uint64_t xa = make_desc_sw128(base), xl = make_desc_sw128(base + PLANE);
-        const uint64_t wh = make_desc_sw128(base + 2 * PLANE), wl = make_desc_sw128(base + 3 * PLANE);
+      const uint32_t tmem_d = tmem_base + acc * BN;
+      for (int kb = 0; kb < KBLOCKS; ++kb) {
+        mbar_wait(&full[stage], phase);
+        mbar_wait(&conv[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t base = smem_u32(tiles + stage * STAGE_BYTES);
+          const uint64_t xa = make_desc_sw128(base), xl = make_desc_sw128(base + PLANE);
+          const uint64_t wh = make_desc_sw128(base + 2 * PLANE), wl = make_desc_sw128(base + 3 * PLANE);
 #pragma unroll
-        for (int k = 0; k < KB / 8; ++k) {              // tf32 k-step = 8 elements = 32 B = +2 in the descriptor
-          umma<1>(tmem_base, xl + 2 * k, wh + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);      // small terms first
-          umma<1>(tmem_base, xa + 2 * k, wl + 2 * k, idesc, 1u);
-          umma<1>(tmem_base, xa + 2 * k, wh + 2 * k, idesc, 1u);
+          for (int k = 0; k < KB / 8; ++k) {              // tf32 k-step = 8 elements = 32 B = +2 in the descriptor
+            umma<1>(tmem_d, xl + 2 * k, wh + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);      // small terms first
+            umma<1>(tmem_d, xa + 2 * k, wl + 2 * k, idesc, 1u);
+            umma<1>(tmem_d, xa + 2 * k, wh + 2 * k, idesc, 1u);
+          }
+          umma_commit(&empty[stage]);
+          if (kb == KBLOCKS - 1) umma_commit(&tmem_full[acc]);
         }
-        umma_commit(&empty[stage]);
-        if (kb == KBLOCKS - 1) umma_commit(tmem_full);
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp < 6) {
+    // ===================== converters (warps 2..5) =====================
+    const int ct = threadIdx.x - 64;                  // 0..127
+    uint32_t stage = 0, phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      for (int kb = 0; kb < KBLOCKS; ++kb) {
+        mbar_wait(&full[stage], phase);
+        if (item == (int)blockIdx.x && kb == 0 && warp == 2) FC_TRACE(1);
+        float4* xs = reinterpret_cast<float4*>(tiles + stage * STAGE_BYTES);
+        float4 v[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = xs[ct + 128 * i];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float4 h, l;
+          h.x = round_tf32(v[i].x); l.x = round_tf32(v[i].x - h.x);
+          h.y = round_tf32(v[i].y); l.y = round_tf32(v[i].y - h.y);
+          h.z = round_tf32(v[i].z); l.z = round_tf32(v[i].z - h.z);
+          h.w = round_tf32(v[i].w); l.w = round_tf32(v[i].w - h.w);
+          xs[ct + 128 * i] = h;
+          xs[ct + 128 * i + PLANE / 16] = l;
+        }
+        fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core's smem reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&conv[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (item == (int)blockIdx.x && warp == 2) FC_TRACE(2);
     }
   } else {
-    // ===================== converters, then epilogue (warps 2..5) =====================
-    const int et = threadIdx.x - 64;                  // 0..127
+    // ===================== epilogue (warps 6..9) =====================
+    // accumulator -> partial sums of K slice z.  tcgen05.ld gives a thread one ROW (32 consecutive columns); a
+    // per-warp [32][36] shared-memory transpose turns that into stores where 8 lanes write one row's 128 bytes.
     pdl_wait();          // ws is still being read by the previous microbatch's tail until here
-    FC_TRACE(2);
-    for (int kb = 0; kb < KBLOCKS; ++kb) {
-      const int stage = kb % STAGES, round = kb / STAGES;
-      mbar_wait(&full[stage], round & 1);
-      if (kb == 0) FC_TRACE(3);
-      float4* xs = reinterpret_cast<float4*>(tiles + stage * STAGE_BYTES);
-      float4 v[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = xs[et + 128 * i];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float4 h, l;
-        h.x = round_tf32(v[i].x); l.x = round_tf32(v[i].x - h.x);
-        h.y = round_tf32(v[i].y); l.y = round_tf32(v[i].y - h.y);
-        h.z = round_tf32(v[i].z); l.z = round_tf32(v[i].z - h.z);
-        h.w = round_tf32(v[i].w); l.w = round_tf32(v[i].w - h.w);
-        xs[et + 128 * i] = h;
-        xs[et + 128 * i + PLANE / 16] = l;
-      }
-      fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core's smem reads
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&conv[stage]);
-    }
-    // accumulator -> partial sums of K slice z (thread = row; 128 contiguous bytes per 32-column chunk)
-    const int q = warp & 3;
-    FC_TRACE(4);
-    mbar_wait(tmem_full, 0);
-    FC_TRACE(5);
-    tc_fence_after();
-    const int row = m0 + q * 32 + lane;
-    float* dst = ws + ((size_t)z * M + row) * N_HIDDEN + n0;
+    const int q = warp & 3;                           // TMEM lane quarter this warp may read
+    float* stg = epi_smem + (warp - 6) * (32 * EPI_PITCH);
+    uint32_t acc = 0, acc_phase = 0;
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+      const int z = item % NSLICES, j = (item / NSLICES) % NTILES, mt = item / (NSLICES * NTILES);
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      if (item == (int)blockIdx.x && warp == 6) FC_TRACE(3);
+      const int row0 = mt * BM + q * 32;
+      float* dst = ws + ((size_t)z * M + row0) * N_HIDDEN + j * BN;
 #pragma unroll 1
-    for (int ch = 0; ch < BN / 32; ++ch) {
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ch * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
-      tmem_ld_wait();
-      if (row < M) {
+      for (int ch = 0; ch < BN / 32; ++ch) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + acc * BN + ch * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
+        tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          *reinterpret_cast<float4*>(dst + ch * 32 + 4 * i) =
+          *reinterpret_cast<float4*>(stg + lane * EPI_PITCH + 4 * i) =
               make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
                           __uint_as_float(r[4 * i + 3]));
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = 4 * i + (lane >> 3), c4 = (lane & 7) * 4;
+          const float4 v = *reinterpret_cast<const float4*>(stg + rr * EPI_PITCH + c4);
+          if (row0 + rr < M) *reinterpret_cast<float4*>(dst + (size_t)rr * N_HIDDEN + ch * 32 + c4) = v;
+        }
+        __syncwarp();
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (item == (int)blockIdx.x && warp == 6) FC_TRACE(4);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
-    tc_fence_before();
-    FC_TRACE(6);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, BN);
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
 }
 
 inline size_t ws_bytes(int64_t batch) { return (size_t)NSLICES * batch * N_HIDDEN * sizeof(float); }
@@ -232,7 +275,9 @@ inline int launch_fc1_x3_splitk(const float* x, const float* w_hi, const float* 
   }
   B2P_TRY(make_tmap(&th, 1, w_hi, N_HIDDEN, K_IN, K_IN, BN));
   B2P_TRY(make_tmap(&tl, 1, w_lo, N_HIDDEN, K_IN, K_IN, BN));
-  dim3 grid(NSLICES, NTILES, ceil_div(batch, BM));
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = std::min(NSLICES * NTILES * ceil_div(batch, BM), sms);
   static const int trace_on = [] { const char* e = getenv("B2P_FC_TRACE"); return (e && e[0] == '1') ? 1 : 0; }();
   B2P_LAUNCH_PDL(fc1_x3_splitk, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, span);
   return 0;

@@ -19,7 +19,7 @@ print("single launch (events):", e0.elapsed_time(e1) * 1e3, "us")
 buf = (C.c_longlong * 2048)()
 L.check(L.lib().b2p_debug_fc_trace(buf, 2048))
 t = np.array(list(buf), dtype=np.int64).reshape(128, 16)
-names = ["start", "setup_done", "pdl_wait_done", "first_tile_landed", "converted_all", "acc_ready", "partials_stored"]
+names = ["start", "first_tile_landed", "first_item_converted", "first_acc_ready", "first_item_stored"]
 rel = t - t[:, :1]
 for e, n in enumerate(names):
     col = rel[:, e][t[:, e] != 0]
