@@ -155,12 +155,15 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
       st->fc_ws_bytes = need;
     }
     const b2p_weight& w = st->w[0];
-    static const int only = [] { const char* e = getenv("B2P_FC_ONLY"); return e ? atoi(e) : 0; }();   // timing aid
-    if (only != 2)
-    B2P_TRY(fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, span));
-    if (only != 1)
-    B2P_LAUNCH_PDL(fc_tail_f32<fcs::NSLICES>, (int)batch + (span.data ? 1 : 0), 128, 0, s, st->fc_ws, (int)batch, st->dev(1),
-                   st->dev(2), st->dev(3), out, span);
+    const int parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, span);
+    if (parts < 0) return parts;
+    const int tail_grid = (int)batch + (span.data ? 1 : 0);
+    if (parts == fcs::NSLICES)
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, true>), tail_grid, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+                     st->dev(3), out, span);
+    else
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 2, false>), tail_grid, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+                     st->dev(3), out, span);
     return 0;
   }
   const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);

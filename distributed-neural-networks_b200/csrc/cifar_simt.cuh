@@ -206,7 +206,10 @@ fc1_splitk_f32(const float* __restrict__ x,     // [M,4096]
 //   l = b2 + W2 h                          (10)
 //   out[m] = softmax(l)                    cifar_model_parts.py:55-57
 // ---------------------------------------------------------------------------------
-template <int SPLITS>     // compile-time so the partial-sum loads are all in flight together (they were a serial chain)
+// SPLITS is compile-time so the partial-sum loads are all in flight together (they were a serial chain).
+// PAIRS: the partials are added two by two first ((p0+p1), (p2+p3), ...), the association the fc1 kernel of
+// fc_stage_tc.cuh uses when it sums pairs of K slices itself -- so 32 unpaired and 16 paired partials give the same bits.
+template <int SPLITS, bool PAIRS = false>
 __global__ void __launch_bounds__(128)
 fc_tail_f32(const float* __restrict__ ws, int M,
             const float* __restrict__ b1,
@@ -232,8 +235,15 @@ fc_tail_f32(const float* __restrict__ ws, int M,
 #pragma unroll
   for (int z = 0; z < SPLITS; ++z)      // plain loads, NOT __ldg: ws was written by the previous kernel, and the compiler
     p[z] = ld_produced(reinterpret_cast<const float4*>(ws + ((size_t)z * M + m) * FC1_N) + tid);   // may hoist ld.global.nc above pdl_wait()
+  if (PAIRS) {
 #pragma unroll
-  for (int z = 0; z < SPLITS; ++z) { h.x += p[z].x; h.y += p[z].y; h.z += p[z].z; h.w += p[z].w; }   // fixed order
+    for (int z = 0; z < SPLITS; z += 2) {
+      h.x += p[z].x + p[z + 1].x; h.y += p[z].y + p[z + 1].y; h.z += p[z].z + p[z + 1].z; h.w += p[z].w + p[z + 1].w;
+    }
+  } else {
+#pragma unroll
+    for (int z = 0; z < SPLITS; ++z) { h.x += p[z].x; h.y += p[z].y; h.z += p[z].z; h.w += p[z].w; }   // fixed order
+  }
   h.x = fmaxf(h.x, 0.f); h.y = fmaxf(h.y, 0.f); h.z = fmaxf(h.z, 0.f); h.w = fmaxf(h.w, 0.f);
   __shared__ float part[4][10];
   float l[10];

@@ -55,11 +55,17 @@ __device__ long long g_fc_trace[NSLICES * NTILES * 16];
 // fastest, so the 128 items of a row tile (= one ring message) are adjacent.  The smem stage ring and the two
 // accumulator stages in tensor memory run on across items: the loads and MMAs of item i+1 overlap the epilogue of
 // item i, and only the first item of a CTA sees the ~1.2 us TMA start-up latency.
+// GROUP = 1: one K slice per item, 32 partial sums per output element (fills the GPU from a single 128-row tile).
+// GROUP = 2: an item covers two consecutive K slices, each into its own accumulator stage; the epilogue adds the pair
+//            (slice 2g first) and writes 16 partial sums -- half the partial-sum traffic once there are enough row
+//            tiles to fill the GPU anyway.  fc_tail adds unpaired partials pairwise in the same order, so both
+//            groupings give bit-identical results.
+template <int GROUP>
 __global__ void __launch_bounds__(THREADS, 1)
 fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp32, box [32 k][128 rows]
               const __grid_constant__ CUtensorMap tmap_w_hi,    // fc1.weight hi plane [512,4096], box [32 k][128 rows]
               const __grid_constant__ CUtensorMap tmap_w_lo,    // fc1.weight lo plane
-              float* __restrict__ ws,                           // partial sums [32][M][512]
+              float* __restrict__ ws,                           // partial sums [32 / GROUP][M][512]
               int M, int trace_on,
               RingSpan span) {                                  // span.data: tmap_x covers the whole ring, row tile mt is message mt
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -70,24 +76,26 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
   uint64_t* full = bars;                  // [STAGES] TMA -> converters, MMA
   uint64_t* conv = bars + STAGES;         // [STAGES] converters -> MMA
   uint64_t* empty = bars + 2 * STAGES;    // [STAGES] MMA -> TMA
-  uint64_t* tmem_full = bars + 3 * STAGES;   // [2] MMA -> epilogue
-  uint64_t* tmem_empty = tmem_full + 2;      // [2] epilogue -> MMA
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  constexpr int ACC = 2 * GROUP;             // accumulator stages in tensor memory (an item uses GROUP of them)
+  constexpr int ZI = NSLICES / GROUP;        // items along K
+  uint64_t* tmem_full = bars + 3 * STAGES;   // [ACC] MMA -> epilogue
+  uint64_t* tmem_empty = tmem_full + ACC;    // [ACC] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + ACC);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (M + BM - 1) / BM;
-  const int num_items = NSLICES * NTILES * m_tiles;
+  const int num_items = ZI * NTILES * m_tiles;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_x)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w_hi)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmap_w_lo)) : "memory");
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&conv[i], 4); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
+    for (int i = 0; i < ACC; ++i) { mbar_init(&tmem_full[i], 1); mbar_init(&tmem_empty[i], 4); }
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 2 * BN);
+    tmem_alloc(tmem_slot, ACC * BN);
     tmem_relinquish();
   }
   FC_TRACE(0);
@@ -103,13 +111,13 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     // most of that item's bytes are on their way while the previous kernel in the stream drains.
     const int first = blockIdx.x;
     if (lane == 0 && first < num_items) {
-      const int z = first % NSLICES, j = (first / NSLICES) % NTILES;
+      const int zi = first % ZI, j = (first / ZI) % NTILES;
 #pragma unroll
-      for (int kb = 0; kb < (KBLOCKS < STAGES ? KBLOCKS : STAGES); ++kb) {
+      for (int kb = 0; kb < STAGES; ++kb) {          // (KBLOCKS * GROUP >= STAGES)
         unsigned char* sa = tiles + kb * STAGE_BYTES;
         mbar_expect_tx(&full[kb], 3 * PLANE);
-        tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[kb], z * KSLICE + kb * KB, j * BN);
-        tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[kb], z * KSLICE + kb * KB, j * BN);
+        tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[kb], zi * GROUP * KSLICE + kb * KB, j * BN);
+        tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[kb], zi * GROUP * KSLICE + kb * KB, j * BN);
       }
     }
     __syncwarp();
@@ -117,7 +125,7 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     uint32_t stage = 0, phase = 0;
     int waited_mt = -1, x_row0 = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-      const int z = item % NSLICES, j = (item / NSLICES) % NTILES, mt = item / (NSLICES * NTILES);
+      const int zi = item % ZI, j = (item / ZI) % NTILES, mt = item / (ZI * NTILES);
       if (mt != waited_mt) {
         x_row0 = mt * BM;
         if (span.data) {
@@ -132,16 +140,17 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
         }
         waited_mt = mt;
       }
-      for (int kb = 0; kb < KBLOCKS; ++kb) {
+      for (int kb = 0; kb < KBLOCKS * GROUP; ++kb) {          // the item's K range is contiguous: GROUP slices back to back
         mbar_wait(&empty[stage], phase ^ 1);
         if (lane == 0) {
           unsigned char* sa = tiles + stage * STAGE_BYTES;
+          const int kx = zi * GROUP * KSLICE + kb * KB;
           if (item != first || kb >= STAGES) {
             mbar_expect_tx(&full[stage], 3 * PLANE);
-            tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[stage], z * KSLICE + kb * KB, j * BN);
-            tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[stage], z * KSLICE + kb * KB, j * BN);
+            tma_load_2d(sa + 2 * PLANE, &tmap_w_hi, &full[stage], kx, j * BN);
+            tma_load_2d(sa + 3 * PLANE, &tmap_w_lo, &full[stage], kx, j * BN);
           }
-          tma_load_2d(sa, &tmap_x, &full[stage], z * KSLICE + kb * KB, x_row0);      // raw fp32, becomes the hi plane
+          tma_load_2d(sa, &tmap_x, &full[stage], kx, x_row0);      // raw fp32, becomes the hi plane
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -151,7 +160,8 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = make_idesc(1, BM, BN);
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-    for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+    for (int item = blockIdx.x; item < num_items; item += gridDim.x)
+    for (int sl = 0; sl < GROUP; ++sl) {             // one accumulator stage per K slice of the item
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + acc * BN;
@@ -175,14 +185,14 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
     }
   } else if (warp < 6) {
     // ===================== converters (warps 2..5) =====================
     const int ct = threadIdx.x - 64;                  // 0..127
     uint32_t stage = 0, phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-      for (int kb = 0; kb < KBLOCKS; ++kb) {
+      for (int kb = 0; kb < KBLOCKS * GROUP; ++kb) {
         mbar_wait(&full[stage], phase);
         if (item == (int)blockIdx.x && kb == 0 && warp == 2) FC_TRACE(1);
         float4* xs = reinterpret_cast<float4*>(tiles + stage * STAGE_BYTES);
@@ -215,17 +225,26 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     float* stg = epi_smem + (warp - 6) * (32 * EPI_PITCH);
     uint32_t acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-      const int z = item % NSLICES, j = (item / NSLICES) % NTILES, mt = item / (NSLICES * NTILES);
+      const int zi = item % ZI, j = (item / ZI) % NTILES, mt = item / (ZI * NTILES);
       mbar_wait(&tmem_full[acc], acc_phase);
+      if (GROUP == 2) mbar_wait(&tmem_full[acc + 1], acc_phase);      // (ACC is a multiple of GROUP: same phase)
       tc_fence_after();
       if (item == (int)blockIdx.x && warp == 6) FC_TRACE(3);
       const int row0 = mt * BM + q * 32;
-      float* dst = ws + ((size_t)z * M + row0) * N_HIDDEN + j * BN;
+      float* dst = ws + ((size_t)zi * M + row0) * N_HIDDEN + j * BN;
 #pragma unroll 1
       for (int ch = 0; ch < BN / 32; ++ch) {
         uint32_t r[32];
         tmem_ld32(tmem_base + acc * BN + ch * 32 + (static_cast<uint32_t>(q * 32) << 16), r);
-        tmem_ld_wait();
+        if (GROUP == 2) {
+          uint32_t r2[32];
+          tmem_ld32(tmem_base + (acc + 1) * BN + ch * 32 + (static_cast<uint32_t>(q * 32) << 16), r2);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) + __uint_as_float(r2[i]));   // slice 2g + slice 2g+1
+        } else {
+          tmem_ld_wait();
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           *reinterpret_cast<float4*>(stg + lane * EPI_PITCH + 4 * i) =
@@ -242,27 +261,35 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) {
+        mbar_arrive(&tmem_empty[acc]);
+        if (GROUP == 2) mbar_arrive(&tmem_empty[acc + 1]);
+      }
       if (item == (int)blockIdx.x && warp == 6) FC_TRACE(4);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      acc += GROUP;
+      if (acc == ACC) { acc = 0; acc_phase ^= 1; }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, 2 * BN);
+  if (warp == 1) tmem_dealloc(tmem_base, ACC * BN);
 }
 
 inline size_t ws_bytes(int64_t batch) { return (size_t)NSLICES * batch * N_HIDDEN * sizeof(float); }
+// rows from which pairs of K slices still give every SM an item (16 x 4 items per 128-row tile)
+inline int fc1_group_for(int64_t batch) { return ceil_div(batch, BM) >= 3 ? 2 : 1; }
 
-// x [batch,4096] fp32; w_hi / w_lo: the tf32 planes of fc1.weight [512,4096]; ws: ws_bytes(batch).  One launch.
+// x [batch,4096] fp32; w_hi / w_lo: the tf32 planes of fc1.weight [512,4096]; ws: ws_bytes(batch).  One launch;
+// returns the number of partial sums per output element it wrote (32 or 16) or a negative error.
 inline int launch_fc1_x3_splitk(const float* x, const float* w_hi, const float* w_lo, float* ws, int64_t batch,
                                 cudaStream_t s, RingSpan span = RingSpan{}) {
   static bool configured[64] = {};
   int dev = 0;
   B2P_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !configured[dev]) {
-    B2P_CUDA(cudaFuncSetAttribute(fc1_x3_splitk, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    B2P_CUDA(cudaFuncSetAttribute(fc1_x3_splitk<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    B2P_CUDA(cudaFuncSetAttribute(fc1_x3_splitk<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     configured[dev] = true;
   }
   CUtensorMap tx, th, tl;
@@ -277,10 +304,14 @@ inline int launch_fc1_x3_splitk(const float* x, const float* w_hi, const float* 
   B2P_TRY(make_tmap(&tl, 1, w_lo, N_HIDDEN, K_IN, K_IN, BN));
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int grid = std::min(NSLICES * NTILES * ceil_div(batch, BM), sms);
+  const int group = fc1_group_for(batch);
+  const int grid = std::min((NSLICES / group) * NTILES * ceil_div(batch, BM), sms);
   static const int trace_on = [] { const char* e = getenv("B2P_FC_TRACE"); return (e && e[0] == '1') ? 1 : 0; }();
-  B2P_LAUNCH_PDL(fc1_x3_splitk, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, span);
-  return 0;
+  if (group == 2)
+    B2P_LAUNCH_PDL(fc1_x3_splitk<2>, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, span);
+  else
+    B2P_LAUNCH_PDL(fc1_x3_splitk<1>, grid, THREADS, SMEM_BYTES, s, tx, th, tl, ws, (int)batch, trace_on, span);
+  return NSLICES / group;
 }
 inline int read_fc_trace(long long* host_out, int n) {
   if (n != NSLICES * NTILES * 16) return fail(B2P_EINVAL, "fc trace: expected %d slots", NSLICES * NTILES * 16);
