@@ -31,6 +31,8 @@ namespace fcs {
 
 using namespace tc;
 
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+
 constexpr int BM = 128, BN = 128;           // rows x hidden units per CTA
 constexpr int N_HIDDEN = 512, K_IN = 4096;
 constexpr int KB = 32;                      // fp32 per 128-byte swizzle row
@@ -201,12 +203,13 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
         for (int i = 0; i < 8; ++i) v[i] = xs[ct + 128 * i];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float4 h, l;
-          h.x = round_tf32(v[i].x); l.x = round_tf32(v[i].x - h.x);
-          h.y = round_tf32(v[i].y); l.y = round_tf32(v[i].y - h.y);
-          h.z = round_tf32(v[i].z); l.z = round_tf32(v[i].z - h.z);
-          h.w = round_tf32(v[i].w); l.w = round_tf32(v[i].w - h.w);
-          xs[ct + 128 * i] = h;
+          // kind::tf32 reads the top 19 bits of each fp32 word, so the raw tile already IS the hi plane
+          // (hi = x with the low 13 mantissa bits dropped); only lo = rna_tf32(x - hi) has to be written.
+          float4 l;
+          l.x = round_tf32(v[i].x - trunc_tf32(v[i].x));
+          l.y = round_tf32(v[i].y - trunc_tf32(v[i].y));
+          l.z = round_tf32(v[i].z - trunc_tf32(v[i].z));
+          l.w = round_tf32(v[i].w - trunc_tf32(v[i].w));
           xs[ct + 128 * i + PLANE / 16] = l;
         }
         fence_proxy_async();                            // generic-proxy stores -> visible to the tensor core's smem reads
