@@ -222,6 +222,41 @@ def engine_arm(args):
         if i >= 20:
             lats.append(1e3 * (time.perf_counter() - q0))
 
+    # -- (3b) the same requests through the reference-facing client seam: a node_service.proto client over a real
+    #         localhost gRPC channel into the NodeService front door (what an unmodified reference client calls)
+    front = None
+    try:
+        import grpc
+        import numpy as np
+        svc = import_module("distributed-neural-networks_b200.service")
+        wire = import_module("distributed-neural-networks_b200.wire")
+        servicer = svc.NodeServiceImpl(["node1", "node2"], svc.ChainRunner(pipe))
+        server, port = svc.serve(servicer, 0)
+        unlimited = [("grpc.max_send_message_length", -1), ("grpc.max_receive_message_length", -1)]
+        with grpc.insecure_channel(f"127.0.0.1:{port}", options=unlimited) as ch:
+            stub = wire.NodeServiceStub(ch)
+            front = {}
+            for nb, reps in ((1, 300), (MICROBATCH, 200)):
+                xq = host_pool[1][:nb].numpy()
+                req = wire.TensorRequest(request_id="bench", tensor=wire.ndarray_to_tensor(xq))
+                fl = []
+                t_all = time.perf_counter()
+                for i in range(20 + reps):
+                    if i == 20:
+                        t_all = time.perf_counter()
+                    q0 = time.perf_counter()
+                    resp = stub.SendTensor(req)
+                    if i >= 20:
+                        fl.append(1e3 * (time.perf_counter() - q0))
+                assert resp.HasField("result_tensor"), resp.status
+                front[f"p50_ms_b{nb}"] = statistics.median(fl)
+                front[f"samples_per_s_b{nb}"] = nb * reps / (time.perf_counter() - t_all)
+        server.stop(0)
+        front["what"] = ("TensorRequest -> gRPC (localhost) -> NodeService front door -> both stages on the GPU -> TensorResponse; "
+                         "one request at a time, like the reference's client (node.py:170-189)")
+    except Exception as e:                                   # never fail the bench on this extra
+        front = {"error": f"{type(e).__name__}: {e}"}
+
     # -- (4) roofline of the dominant kernel (stage 0), timed alone on its launch stream ------------------
     s0 = pipe.compute[0]
     act = pipe.hidden[0]
@@ -310,6 +345,7 @@ def engine_arm(args):
         "e2e": {"value": BATCH * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4,
                 "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
         "p50_request_latency_ms": statistics.median(lats),
+        "front_door_grpc": front,
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "torch_eager_gpu": eager,
     }

@@ -18,6 +18,7 @@ and one process serves the whole chain (stage k on GPU k) instead of one process
 """
 from __future__ import annotations
 
+import warnings
 from concurrent import futures
 from typing import Callable, Sequence
 
@@ -75,7 +76,10 @@ class ChainRunner:
         outs = []
         for lo in range(0, x.shape[0], p.max_batch):
             n = min(p.max_batch, x.shape[0] - lo)
-            self.stage_in[:n].copy_(torch.from_numpy(x[lo:lo + n]))        # the one host copy (node.py:48 makes two)
+            with warnings.catch_warnings():                    # np.frombuffer views are read-only; they are only read here
+                warnings.simplefilter("ignore", UserWarning)
+                src = torch.from_numpy(x[lo:lo + n])
+            self.stage_in[:n].copy_(src)                       # the one host copy (node.py:48 makes two)
             outs.append(p.run_host(self.stage_in[:n], sync=True).numpy().copy())
         return np.concatenate(outs) if len(outs) != 1 else outs[0]
 
