@@ -117,8 +117,13 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
                st->dev(3), out, (int)batch);
   else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
-    B2P_LAUNCH_PDL_BIT(2, cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, st->w1t, st->dev(1),
-                   st->w2img, st->dev(3), out, (int)batch, st->trace, span);
+  {
+    cifar_tc::Conv1Const c1;
+    static_assert(sizeof(c1) == sizeof(st->w1_host), "host copy layout");
+    memcpy(&c1, st->w1_host, sizeof(c1));
+    B2P_LAUNCH_PDL_BIT(2, cifar_tc::part0_tc, grid, cifar_tc::kThreads, cifar_tc::SMEM_BYTES, s, in, c1,
+                       st->w2img, st->dev(3), out, (int)batch, st->trace, span);
+  }
   return 0;
 }
 
@@ -525,6 +530,9 @@ int b2p_stage_finalize(b2p_stage* st) {
     if (st->d.math != B2P_MATH_FP32) {
       if (!st->w2img) B2P_CUDA(cudaMalloc((void**)&st->w2img, cifar_tc::W2_BYTES));
       B2P_LAUNCH(cifar_tc::pack_conv2_f16x2, ceil_div(9 * 64 * 8, 256), 256, 0, 0, st->dev(2), st->w2img);
+      // host copy of the transposed conv1 weights + bias: they travel as a kernel parameter (cifar_tc::Conv1Const)
+      B2P_CUDA(cudaMemcpy(st->w1_host, st->w1t, 27 * 32 * sizeof(float), cudaMemcpyDeviceToHost));
+      B2P_CUDA(cudaMemcpy(st->w1_host + 27 * 32, st->dev(1), 32 * sizeof(float), cudaMemcpyDeviceToHost));
     }
   }
   // math-mode copies of the matrices that feed the tensor cores

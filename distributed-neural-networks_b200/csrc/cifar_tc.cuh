@@ -37,24 +37,33 @@ namespace cifar_tc {
 
 using namespace tc;
 
-constexpr int kProducerWarps = 8, kProducerThreads = 256;
-constexpr int kMmaWarp = 8;
-constexpr int kEpiWarp0 = 9, kEpiThreads = 128;
+// 16 producer warps: thread = (pooled pixel, half of the channel group).  Eight warps (2 per SM sub-partition) left
+// the FP32 pipe 49 % busy -- ncu: the FFMA2s stall on shared-memory loads (short scoreboard) and fixed latencies with
+// nobody else to issue; twice the warps at half the accumulators per thread hide that.
+constexpr int kProducerWarps = 16, kProducerThreads = 512;
+constexpr int kMmaWarp = 16;
+constexpr int kEpiWarp0 = 17, kEpiThreads = 128;
 constexpr int kAcqWarp = kEpiWarp0 + 4, kPubWarp = kAcqWarp + 1;   // handoff-ring handshake, off the epilogue's critical path
-constexpr int kThreads = (kPubWarp + 1) * 32;        // 480
+constexpr int kThreads = (kPubWarp + 1) * 32;        // 736
 
 constexpr int W2_TAP_BYTES = 64 * 128;               // [64 oc rows][128 B]
 constexpr int W2_BYTES = 9 * W2_TAP_BYTES;           // 73 728
 constexpr int ACT_COPY_BYTES = 18 * 16 * 128;        // 36 864: 18 rows (y halo) x 16 px x 128 B
 constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;        // 110 592
 
+// conv1 weights [c*9+kh*3+kw][oc] and bias travel in the kernel's PARAMETER bank: the producers read them through the
+// constant cache (warp-uniform addresses) instead of shared memory, whose bandwidth the tensor core's operand reads,
+// the window loads and the activation stores already fill (~80 % at 16 producer warps, measured).
+struct Conv1Const {
+  float w[27][32];
+  float b[32];
+};
+
 struct Smem {
   unsigned char w2[W2_BYTES];                        // pre-swizzled image from global
   unsigned char act[ACT_BYTES];                      // 3 shifted copies, swizzled rows
   float out[64 * 64];                                // one sample, flatten order
   float in[3][34][34];                               // zero-padded input image
-  float w1[27][32];                                  // [c*9+kh*3+kw][oc]
-  float b1[32];
   float b2[64];
   uint64_t bar_w2, bar_act_full[2], bar_act_empty, bar_tmem_full[2][2], bar_tmem_empty[2];
   uint32_t tmem_slot;
@@ -65,6 +74,16 @@ constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
 
 __device__ __forceinline__ void named_bar(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+// 32 lanes x 16 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
 }
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -114,8 +133,8 @@ __global__ void pack_conv2_f16x2(const float* __restrict__ w2, unsigned char* __
 
 __global__ void __launch_bounds__(kThreads, 1)
 part0_tc(const float* __restrict__ x,                // [B,3,32,32]
-         const float* __restrict__ w1t,              // [27][32]
-         const float* __restrict__ b1, const unsigned char* __restrict__ w2img,
+         const __grid_constant__ Conv1Const c1,      // conv1.weight (transposed) and conv1.bias
+         const unsigned char* __restrict__ w2img,
          const float* __restrict__ b2, float* __restrict__ out,   // [B,4096]
          int batch, long long* __restrict__ dbg,     // dbg: optional [3 roles][8 samples][8 events] clock64 trace of CTA 0
          RingSpan span) {                            // span.data: rows go into handoff-ring slots instead of out (ring_hooks.cuh)
@@ -132,8 +151,6 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   pdl_trigger();
   for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
-  for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = w1t[i];
-  if (tid < 32) s.b1[tid] = b1[tid];
   if (tid < 64) s.b2[tid] = b2[tid];
   if (tid == 0) { s.acq_upto = 0; s.stored = 0; }
   if (warp == kMmaWarp) {
@@ -164,20 +181,22 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
 
   if (warp < kProducerWarps) {
     // =========================== conv1 producers ===========================================
-    const int py = tid >> 4, px = tid & 15;
-    float4 pre[3];
+    const int pix = tid & 255, half = tid >> 8;              // pooled pixel; which 8 of the pass's 16 channels
+    const int py = pix >> 4, px = pix & 15;
+    float4 pre[2];
     if ((int)blockIdx.x < batch) {
       const float4* xin = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 3072);
-#pragma unroll
-      for (int j = 0; j < 3; ++j) pre[j] = ld_produced(xin + tid + 256 * j);     // the image may come from the previous kernel
+      pre[0] = ld_produced(xin + tid);                      // the image may come from the previous kernel
+      if (tid < 256) pre[1] = ld_produced(xin + tid + 512);
     }
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       B2P_TRACE(0, n, 0, tid == 0);
       named_bar(1, kProducerThreads);                       // previous sample's window reads are done
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const int e = (tid + 256 * j) * 4;
+      for (int j = 0; j < 2; ++j) {
+        if (j == 1 && tid >= 256) break;
+        const int e = (tid + 512 * j) * 4;
         const int c = e >> 10, r = (e >> 5) & 31, col = e & 31;
         float* d = &s.in[c][r + 1][col + 1];
         d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
@@ -185,24 +204,25 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       named_bar(1, kProducerThreads);
       if (b + (int)gridDim.x < batch) {                     // next image: in flight during the FMAs
         const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
-#pragma unroll
-        for (int j = 0; j < 3; ++j) pre[j] = ld_produced(xin + tid + 256 * j);
+        pre[0] = ld_produced(xin + tid);
+        if (tid < 256) pre[1] = ld_produced(xin + tid + 512);
       }
       B2P_TRACE(0, n, 1, tid == 0);
-      // ---- conv1 + ReLU + pool, 32 channels in two passes of 16 (8 packed pairs).  Each pass
-      //      publishes its half of the pixel's row (hi chunks 2p,2p+1 and lo chunks 4+2p,5+2p) into
-      //      the three shifted copies right away: the tensor core starts on channels 0..15 (the
-      //      first K=16 MMA of every tap) while the CUDA cores still compute channels 16..31.
+      // ---- conv1 + ReLU + pool, 32 channels in two passes of 16; within a pass this thread owns 8 channels
+      //      (4 packed pairs) of its pixel.  Each pass publishes its part of the pixel's row (one hi and one lo
+      //      16-byte chunk) into the three shifted copies right away: the tensor core starts on channels 0..15
+      //      (the first K=16 MMA of every tap) while the CUDA cores still compute channels 16..31.
 #pragma unroll
       for (int pass = 0; pass < 2; ++pass) {
-        unsigned long long acc[8][4];
+        const int ch0 = pass * 16 + half * 8;                // first channel of this thread's group
+        unsigned long long acc[4][4];
 #pragma unroll
-        for (int p = 0; p < 8; ++p) {
-          const float2 bb = *reinterpret_cast<const float2*>(&s.b1[pass * 16 + 2 * p]);
+        for (int p = 0; p < 4; ++p) {
+          const float2 bb = *reinterpret_cast<const float2*>(&c1.b[ch0 + 2 * p]);
           const unsigned long long bv = pack2(bb.x, bb.y);
           acc[p][0] = bv; acc[p][1] = bv; acc[p][2] = bv; acc[p][3] = bv;
         }
-#pragma unroll 1
+#pragma unroll
         for (int c = 0; c < 3; ++c) {
           float win[4][4];
 #pragma unroll
@@ -220,9 +240,9 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
               const unsigned long long x10 = pack2(win[kh + 1][kw], win[kh + 1][kw]);
               const unsigned long long x11 = pack2(win[kh + 1][kw + 1], win[kh + 1][kw + 1]);
               const unsigned long long* wrow =
-                  reinterpret_cast<const unsigned long long*>(&s.w1[c * 9 + kh * 3 + kw][pass * 16]);
+                  reinterpret_cast<const unsigned long long*>(&c1.w[c * 9 + kh * 3 + kw][ch0]);
 #pragma unroll
-              for (int p = 0; p < 8; ++p) {
+              for (int p = 0; p < 4; ++p) {
                 const unsigned long long w = wrow[p];
                 ffma2(acc[p][0], x00, w);
                 ffma2(acc[p][1], x01, w);
@@ -231,9 +251,9 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
               }
             }
         }
-        uint32_t hi_pk[8], lo_pk[8];                          // fp16x2 words: channels pass*16 + (2i, 2i+1)
+        uint32_t hi_pk[4], lo_pk[4];                          // fp16x2 words: channels ch0 + (2i, 2i+1)
 #pragma unroll
-        for (int p = 0; p < 8; ++p) {
+        for (int p = 0; p < 4; ++p) {
           float a0, a1, b0, b1v, c0, c1, d0, d1;
           unpack2(acc[p][0], a0, a1); unpack2(acc[p][1], b0, b1v);
           unpack2(acc[p][2], c0, c1); unpack2(acc[p][3], d0, d1);
@@ -251,20 +271,15 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           mbar_wait(&s.bar_act_empty, (n & 1) ^ 1);           // MMAs of the previous sample are done
           B2P_TRACE(0, n, 3, tid == 0);
         }
+        const int ch = 2 * pass + half, cl = 4 + 2 * pass + half;      // hi chunk, lo chunk of this channel group
 #pragma unroll
         for (int kw = 0; kw < 3; ++kw) {
           const int xc = px - kw + 1;                          // column of this pixel in copy kw
           if (xc < 0 || xc > 15) continue;
           const int R = (py + 1) * 16 + xc;
           unsigned char* row = s.act + kw * ACT_COPY_BYTES + R * 128;
-#pragma unroll
-          for (int cc = 0; cc < 2; ++cc) {
-            const int ch = 2 * pass + cc, cl = 4 + 2 * pass + cc;      // hi chunk, lo chunk of this channel group
-            *reinterpret_cast<uint4*>(row + ((ch ^ (R & 7)) * 16)) =
-                make_uint4(hi_pk[4 * cc], hi_pk[4 * cc + 1], hi_pk[4 * cc + 2], hi_pk[4 * cc + 3]);
-            *reinterpret_cast<uint4*>(row + ((cl ^ (R & 7)) * 16)) =
-                make_uint4(lo_pk[4 * cc], lo_pk[4 * cc + 1], lo_pk[4 * cc + 2], lo_pk[4 * cc + 3]);
-          }
+          *reinterpret_cast<uint4*>(row + ((ch ^ (R & 7)) * 16)) = make_uint4(hi_pk[0], hi_pk[1], hi_pk[2], hi_pk[3]);
+          *reinterpret_cast<uint4*>(row + ((cl ^ (R & 7)) * 16)) = make_uint4(lo_pk[0], lo_pk[1], lo_pk[2], lo_pk[3]);
         }
         fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
         __syncwarp();
@@ -293,19 +308,22 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       tc_fence_after();
       B2P_TRACE(1, n, 2, lane == 0);
       if (lane == 0) {
+        // Consecutive MMAs go to DIFFERENT accumulators (tile 0 / tile 1 alternate): a 128x64x16 MMA is ~32 cycles of
+        // tensor work, far less than the pipeline latency of a dependent accumulate into the same TMEM tile.
+        const uint32_t a0 = tmem_base + set * 256, a1 = a0 + 128;            // tile 0 / tile 1: acc0 at +0, acc1 at +64
 #pragma unroll 1
-        for (int t = 0; t < 2; ++t) {
-          const uint32_t acc0 = tmem_base + set * 256 + t * 128, acc1 = acc0 + 64;
-#pragma unroll 1
-          for (int tap = 0; tap < 9; ++tap) {
-            const int kh = tap / 3, kw = tap % 3;
-            const uint64_t da = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 * t + kh) * 16 * 128);
-            const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
-            // descriptor units are 16 B: +2 = the second K=16 step (channels 16..31), +4 = the lo half
-            umma<0>(acc0, da, db, idesc, tap != 0);                 // hi * hi
-            umma<0>(acc1, da, db + 4, idesc, tap != 0);             // hi * lo
-            umma<0>(acc1, da + 4, db, idesc, 1u);                   // lo * hi
-          }
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap % 3;
+          const uint64_t da0 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + kh * 16 * 128);
+          const uint64_t da1 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 + kh) * 16 * 128);
+          const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
+          // descriptor units are 16 B: +2 = the second K=16 step (channels 16..31), +4 = the lo half
+          umma<0>(a0, da0, db, idesc, tap != 0);                  // hi * hi
+          umma<0>(a1, da1, db, idesc, tap != 0);
+          umma<0>(a0 + 64, da0, db + 4, idesc, tap != 0);         // hi * lo
+          umma<0>(a1 + 64, da1, db + 4, idesc, tap != 0);
+          umma<0>(a0 + 64, da0 + 4, db, idesc, 1u);               // lo * hi
+          umma<0>(a1 + 64, da1 + 4, db, idesc, 1u);
         }
       }
       __syncwarp();
@@ -313,20 +331,22 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       mbar_wait(&s.bar_act_full[1], n & 1);
       tc_fence_after();
       if (lane == 0) {
+        const uint32_t a0 = tmem_base + set * 256, a1 = a0 + 128;
 #pragma unroll 1
-        for (int t = 0; t < 2; ++t) {
-          const uint32_t acc0 = tmem_base + set * 256 + t * 128, acc1 = acc0 + 64;
-#pragma unroll 1
-          for (int tap = 0; tap < 9; ++tap) {
-            const int kh = tap / 3, kw = tap % 3;
-            const uint64_t da = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 * t + kh) * 16 * 128);
-            const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
-            umma<0>(acc0, da + 2, db + 2, idesc, 1u);
-            umma<0>(acc1, da + 2, db + 6, idesc, 1u);
-            umma<0>(acc1, da + 6, db + 2, idesc, 1u);
-          }
-          umma_commit(&s.bar_tmem_full[set][t]);
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap % 3;
+          const uint64_t da0 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + kh * 16 * 128);
+          const uint64_t da1 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 + kh) * 16 * 128);
+          const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
+          umma<0>(a0, da0 + 2, db + 2, idesc, 1u);
+          umma<0>(a1, da1 + 2, db + 2, idesc, 1u);
+          umma<0>(a0 + 64, da0 + 2, db + 6, idesc, 1u);
+          umma<0>(a1 + 64, da1 + 2, db + 6, idesc, 1u);
+          umma<0>(a0 + 64, da0 + 6, db + 2, idesc, 1u);
+          umma<0>(a1 + 64, da1 + 6, db + 2, idesc, 1u);
         }
+        umma_commit(&s.bar_tmem_full[set][0]);
+        umma_commit(&s.bar_tmem_full[set][1]);
         umma_commit(&s.bar_act_empty);                       // activation copies may be overwritten
       }
       B2P_TRACE(1, n, 3, lane == 0);
@@ -354,20 +374,20 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
         tc_fence_after();
         if (t == 0) B2P_TRACE(2, n, 1, et == 0);
 #pragma unroll 1
-        for (int ch = 0; ch < 2; ++ch) {                     // 32 output channels at a time
-          uint32_t r0[32], r1[32];
-          const uint32_t ta = tmem_base + set * 256 + t * 128 + ch * 32 + (static_cast<uint32_t>(q * 32) << 16);
-          tmem_ld32(ta, r0);
-          tmem_ld32(ta + 64, r1);
+        for (int ch = 0; ch < 4; ++ch) {                     // 16 output channels at a time (register budget: 88 per thread)
+          uint32_t r0[16], r1[16];
+          const uint32_t ta = tmem_base + set * 256 + t * 128 + ch * 16 + (static_cast<uint32_t>(q * 32) << 16);
+          tmem_ld16(ta, r0);
+          tmem_ld16(ta + 64, r1);
           tmem_ld_wait();
           // 2x2 max-pool across lanes.  A lane owns one conv2 pixel (x = lane&15, row = lane>>4);
           // pool partners are lane^1 (x) and lane^16 (y).  Instead of two shuffles per channel
           // with 3/4 of the lanes ending up redundant, partners SWAP channels: after the x step
           // the even-x lane keeps channel 2p and the odd-x lane channel 2p+1, after the y step
-          // likewise -- 24 shuffles per 32 channels and every lane ends with 8 distinct results.
-          float u[16];
+          // likewise -- 12 shuffles per 16 channels and every lane ends with 4 distinct results.
+          float u[8];
 #pragma unroll
-          for (int p = 0; p < 16; ++p) {
+          for (int p = 0; p < 8; ++p) {
             const float a = fmaf(__uint_as_float(r1[2 * p]), 1.0f / 2048.0f, __uint_as_float(r0[2 * p]));
             const float b = fmaf(__uint_as_float(r1[2 * p + 1]), 1.0f / 2048.0f, __uint_as_float(r0[2 * p + 1]));
             const float recv = __shfl_xor_sync(0xffffffffu, xo ? a : b, 1);
@@ -375,10 +395,10 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           }
           const int pooled = (t * 4 + q) * 8 + ((lane & 15) >> 1);    // h*8 + w of the pooled pixel
 #pragma unroll
-          for (int g = 0; g < 8; ++g) {
+          for (int g = 0; g < 4; ++g) {
             const float recv = __shfl_xor_sync(0xffffffffu, yo ? u[2 * g] : u[2 * g + 1], 16);
             const float m = fmaxf(yo ? u[2 * g + 1] : u[2 * g], recv);
-            const int c = ch * 32 + 4 * g + (yo ? 2 : 0) + (xo ? 1 : 0);
+            const int c = ch * 16 + 4 * g + (yo ? 2 : 0) + (xo ? 1 : 0);
             s.out[c * 64 + pooled] = fmaxf(m + s.b2[c], 0.f);         // max(a)+b == max(a+b)
           }
         }

@@ -32,6 +32,7 @@ struct b2p_stage {
 
   // ---- CIFAR part 0 ----
   float* w1t = nullptr;             // [27][32]
+  float w1_host[27 * 32 + 32] = {};  // host copy of w1t and conv1.bias: kernel-parameter operand of part0_tc
   float* w2t = nullptr;             // [288][64]
   unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's B tiles (split fp16)
   long long* trace = nullptr;       // optional kernel timeline buffer (b2p_stage_trace)
