@@ -529,7 +529,7 @@ int b2p_stage_finalize(b2p_stage* st) {
     B2P_LAUNCH(transpose2d_f32, ceil_div(64 * 288, 256), 256, 0, 0, st->dev(2), st->w2t, 64, 288);
     if (st->d.math != B2P_MATH_FP32) {
       if (!st->w2img) B2P_CUDA(cudaMalloc((void**)&st->w2img, cifar_tc::W2_BYTES));
-      B2P_LAUNCH(cifar_tc::pack_conv2_f16x2, ceil_div(9 * 64 * 8, 256), 256, 0, 0, st->dev(2), st->w2img);
+      B2P_LAUNCH(cifar_tc::pack_conv2_f16x2, ceil_div(9 * 128 * 4, 256), 256, 0, 0, st->dev(2), st->w2img);
       // host copy of the transposed conv1 weights + bias: they travel as a kernel parameter (cifar_tc::Conv1Const)
       B2P_CUDA(cudaMemcpy(st->w1_host, st->w1t, 27 * 32 * sizeof(float), cudaMemcpyDeviceToHost));
       B2P_CUDA(cudaMemcpy(st->w1_host + 27 * 32, st->dev(1), 32 * sizeof(float), cudaMemcpyDeviceToHost));

@@ -46,7 +46,7 @@ constexpr int kEpiWarp0 = 17, kEpiThreads = 128;
 constexpr int kAcqWarp = kEpiWarp0 + 4, kPubWarp = kAcqWarp + 1;   // handoff-ring handshake, off the epilogue's critical path
 constexpr int kThreads = (kPubWarp + 1) * 32;        // 736
 
-constexpr int W2_TAP_BYTES = 64 * 128;               // [64 oc rows][128 B]
+constexpr int W2_TAP_BYTES = 128 * 64;               // [64 oc hi rows ; 64 oc lo rows][64 B]
 constexpr int W2_BYTES = 9 * W2_TAP_BYTES;           // 73 728
 constexpr int ACT_COPY_BYTES = 18 * 16 * 128;        // 36 864: 18 rows (y halo) x 16 px x 128 B
 constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;        // 110 592
@@ -111,23 +111,38 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {   // kind:
   return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
-// One-off weight repack (b2p_stage_finalize): conv2.weight [64,32,3,3] fp32 -> the exact
-// byte image of the B-operand tiles in shared memory: per tap a [64 oc][128 B] K-major tile,
-// row = [hi ic0..31 | lo ic0..31] fp16, 16-byte chunk c of row n stored at chunk c^(n&7).
+// K-major operand tile with 64-byte rows in the 64B-swizzle layout: 8-row groups 512 B apart (SBO), 16-byte chunk c
+// of row r stored at chunk c ^ ((r >> 1) & 3)  (address bits [4,6) ^= bits [7,9): cute Swizzle<2,4,3>).
+__device__ __forceinline__ uint64_t make_desc_sw64(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(512 >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(4) << 61;                        // SWIZZLE_64B
+  return d;
+}
+
+// One-off weight repack (b2p_stage_finalize): conv2.weight [64,32,3,3] fp32 -> the exact byte image of the
+// B-operand tiles in shared memory: per tap a [128 rows][64 B] K-major tile, rows 0..63 = fp16 hi part of oc's 32
+// input channels, rows 64..127 = the lo part (x ~= hi + lo * 2^-11), 64B-swizzled.  One descriptor over all 128
+// rows makes  act_hi x [W_hi ; W_lo]  a single N=128 MMA (hi*hi and hi*lo together): an MMA this small costs
+// ~130 cycles for its operand fetch whatever N is, so two instructions per tap and K-step instead of three.
 __global__ void pack_conv2_f16x2(const float* __restrict__ w2, unsigned char* __restrict__ img) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;       // one 16-byte chunk each
-  if (i >= 9 * 64 * 8) return;
-  const int tap = i / 512, n = (i / 8) % 64, c = i % 8;
+  if (i >= 9 * 128 * 4) return;
+  const int tap = i / 512, r = (i / 4) % 128, c = i % 4;
+  const int n = r & 63;
   const int kh = tap / 3, kw = tap % 3;
   __half v[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
-    const int ic = 8 * (c & 3) + e;
+    const int ic = 8 * c + e;
     __half hi, lo;
     split_f16(w2[((n * 32 + ic) * 3 + kh) * 3 + kw], hi, lo);
-    v[e] = c < 4 ? hi : lo;
+    v[e] = r < 64 ? hi : lo;
   }
-  *reinterpret_cast<uint4*>(img + tap * W2_TAP_BYTES + n * 128 + ((c ^ (n & 7)) * 16)) =
+  *reinterpret_cast<uint4*>(img + tap * W2_TAP_BYTES + r * 64 + ((c ^ ((r >> 1) & 3)) * 16)) =
       *reinterpret_cast<const uint4*>(v);
 }
 
@@ -295,7 +310,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     }
     __syncwarp();
     mbar_wait(&s.bar_w2, 0);
-    constexpr uint32_t idesc = make_idesc_f16(128, 64);
+    constexpr uint32_t idesc = make_idesc_f16(128, 64), idesc128 = make_idesc_f16(128, 128);
     const uint32_t act_addr = smem_u32(s.act), w2_addr = smem_u32(s.w2);
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
@@ -316,13 +331,11 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           const int kh = tap / 3, kw = tap % 3;
           const uint64_t da0 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + kh * 16 * 128);
           const uint64_t da1 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 + kh) * 16 * 128);
-          const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
-          // descriptor units are 16 B: +2 = the second K=16 step (channels 16..31), +4 = the lo half
-          umma<0>(a0, da0, db, idesc, tap != 0);                  // hi * hi
-          umma<0>(a1, da1, db, idesc, tap != 0);
-          umma<0>(a0 + 64, da0, db + 4, idesc, tap != 0);         // hi * lo
-          umma<0>(a1 + 64, da1, db + 4, idesc, tap != 0);
-          umma<0>(a0 + 64, da0 + 4, db, idesc, 1u);               // lo * hi
+          const uint64_t db = make_desc_sw64(w2_addr + tap * W2_TAP_BYTES);
+          // descriptor units are 16 B: +2 = the second K=16 step (channels 16..31); act rows: +4 = the lo half
+          umma<0>(a0, da0, db, idesc128, tap != 0);               // hi * [W_hi ; W_lo] -> acc0 | acc1
+          umma<0>(a1, da1, db, idesc128, tap != 0);
+          umma<0>(a0 + 64, da0 + 4, db, idesc, 1u);               // lo * W_hi -> acc1
           umma<0>(a1 + 64, da1 + 4, db, idesc, 1u);
         }
       }
@@ -337,13 +350,11 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
           const int kh = tap / 3, kw = tap % 3;
           const uint64_t da0 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + kh * 16 * 128);
           const uint64_t da1 = make_desc_sw128(act_addr + kw * ACT_COPY_BYTES + (8 + kh) * 16 * 128);
-          const uint64_t db = make_desc_sw128(w2_addr + tap * W2_TAP_BYTES);
-          umma<0>(a0, da0 + 2, db + 2, idesc, 1u);
-          umma<0>(a1, da1 + 2, db + 2, idesc, 1u);
-          umma<0>(a0 + 64, da0 + 2, db + 6, idesc, 1u);
-          umma<0>(a1 + 64, da1 + 2, db + 6, idesc, 1u);
-          umma<0>(a0 + 64, da0 + 6, db + 2, idesc, 1u);
-          umma<0>(a1 + 64, da1 + 6, db + 2, idesc, 1u);
+          const uint64_t db = make_desc_sw64(w2_addr + tap * W2_TAP_BYTES) + 2;
+          umma<0>(a0, da0 + 2, db, idesc128, 1u);
+          umma<0>(a1, da1 + 2, db, idesc128, 1u);
+          umma<0>(a0 + 64, da0 + 6, db, idesc, 1u);
+          umma<0>(a1 + 64, da1 + 6, db, idesc, 1u);
         }
         umma_commit(&s.bar_tmem_full[set][0]);
         umma_commit(&s.bar_tmem_full[set][1]);
