@@ -51,9 +51,9 @@ constexpr int W2_BYTES = 9 * W2_TAP_BYTES;           // 73 728
 constexpr int ACT_COPY_BYTES = 18 * 16 * 128;        // 36 864: 18 rows (y halo) x 16 px x 128 B
 constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;        // 110 592
 
-// conv1 weights [c*9+kh*3+kw][oc] and bias travel in the kernel's PARAMETER bank: the producers read them through the
-// constant cache (warp-uniform addresses) instead of shared memory, whose bandwidth the tensor core's operand reads,
-// the window loads and the activation stores already fill (~80 % at 16 producer warps, measured).
+// conv1 weights [c*9+kh*3+kw][oc] and bias travel as a kernel parameter (3.5 KB) and are copied to shared memory in
+// the prologue.  Reading them straight from the parameter bank in the FMA loop (LDC, warp-uniform addresses) was
+// measured slower: 55.9 vs 52.7 us per 1024 samples -- ncu showed the FFMA2s waiting on the constant loads.
 struct Conv1Const {
   float w[27][32];
   float b[32];
@@ -65,6 +65,7 @@ struct Smem {
   float out[64 * 64];                                // one sample, flatten order
   float in[3][34][34];                               // zero-padded input image
   float b2[64];
+  float w1[27][32];                                  // [c*9+kh*3+kw][oc]
   uint64_t bar_w2, bar_act_full[2], bar_act_empty, bar_tmem_full[2][2], bar_tmem_empty[2];
   uint32_t tmem_slot;
   int acq_upto;                                      // ring: samples of this CTA whose slot may be written (acquirer -> epilogue)
@@ -92,7 +93,17 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
 }
 // packed fp32 FMA (two independent fp32 FMAs per lane per instruction, sm_100)
 __device__ __forceinline__ void ffma2(unsigned long long& acc, unsigned long long a, unsigned long long b) {
+#ifdef B2P_SCALAR_FMA   // measured: same producer time as FFMA2 (6.0 k vs 6.1 k cycles per pass), slower overall
+  float a0, a1, b0, b1, c0, c1;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a0), "=f"(a1) : "l"(a));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(b0), "=f"(b1) : "l"(b));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(c0), "=f"(c1) : "l"(acc));
+  c0 = fmaf(a0, b0, c0);
+  c1 = fmaf(a1, b1, c1);
+  asm("mov.b64 %0, {%1, %2};" : "=l"(acc) : "f"(c0), "f"(c1));
+#else
   asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+#endif
 }
 __device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
   unsigned long long r;
@@ -167,6 +178,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
   if (tid < 64) s.b2[tid] = b2[tid];
+  for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = (&c1.w[0][0])[i];
   if (tid == 0) { s.acq_upto = 0; s.stored = 0; }
   if (warp == kMmaWarp) {
     if (lane == 0) {
@@ -255,7 +267,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
               const unsigned long long x10 = pack2(win[kh + 1][kw], win[kh + 1][kw]);
               const unsigned long long x11 = pack2(win[kh + 1][kw + 1], win[kh + 1][kw + 1]);
               const unsigned long long* wrow =
-                  reinterpret_cast<const unsigned long long*>(&c1.w[c * 9 + kh * 3 + kw][ch0]);
+                  reinterpret_cast<const unsigned long long*>(&s.w1[c * 9 + kh * 3 + kw][ch0]);
 #pragma unroll
               for (int p = 0; p < 4; ++p) {
                 const unsigned long long w = wrow[p];
