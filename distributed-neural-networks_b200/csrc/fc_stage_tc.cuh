@@ -6,14 +6,15 @@
 // Part 1 used to be three launches per microbatch: split_tf32 (x -> hi/lo planes in HBM), the generic
 // linear_tc<tf32x3> with 16 K slices (64 CTAs, each pulling 512 KB through one SM), and fc_tail.  This kernel
 // replaces the first two:
-//   * 128 CTAs per 128 rows -- CTA (z, j, mt): K slice z (128 of 4096), hidden-unit tile j (128 of 512), row tile
-//     mt -- so the 16.8 MB of weight planes and the activation are spread over 128 SMs (192 KB each);
-//   * x is loaded ONCE as raw fp32 by TMA and split in shared memory by four converter warps: hi = rna_tf32(x)
-//     in place, lo = rna_tf32(x - hi) beside it (elementwise, so TMA's 128-byte swizzle is preserved);
-//   * the weight planes of the first three k-blocks are requested before griddepcontrol.wait (they are constants),
-//     so most of the CTA's bytes are in flight while the previous kernel of the stream drains;
-//   * tcgen05.mma kind::tf32, three products per k-step (lo*hi, hi*lo, hi*hi) into one 128 x 128 accumulator,
-//     written as partial sums ws[z][row][512]; fc_tail_f32<32> adds the 32 slices in ascending order.
+//   * persistent CTAs over work items (K slice(s), 128 hidden units, 128 rows): a single 128-row tile already gives
+//     128 items, so the 16.8 MB of weight planes and the activation are spread over 128 SMs;
+//   * x is loaded ONCE as raw fp32 by TMA.  kind::tf32 reads only the top 19 bits of a word, so the raw tile IS the
+//     hi plane; four converter warps write lo = rna_tf32(x - trunc_tf32(x)) beside it (elementwise, so TMA's
+//     128-byte swizzle is preserved) -- no split kernel, no hi/lo planes in HBM;
+//   * the weight planes of the first item's first three k-blocks are requested before griddepcontrol.wait (they are
+//     constants), so most of its bytes are in flight while the previous kernel of the stream drains;
+//   * tcgen05.mma kind::tf32, three products per k-step (lo*hi, hi*lo, hi*hi) into a 128 x 128 accumulator stage;
+//     partial sums leave as ws[slice or pair][row][512]; fc_tail_f32 adds them pairwise in ascending order.
 // A row's result depends only on that row (fixed K slicing, fixed summation order): micro-batching is bit-exact.
 //
 // Measured dead end, kept as a note: a fully fused variant (clusters of 8 K slices reducing over distributed
