@@ -688,6 +688,7 @@ b2p::RingSpan span_of(b2p_ring* r, uint64_t seq, int64_t rows_per_msg) {
   sp.first_slot = (int)(seq % r->slots);
   sp.rows_per_msg = (int)rows_per_msg;
   sp.tickets = r->ticket;
+  sp.acq_seen = r->local_count + 2 * r->slots;
   return sp;
 }
 int64_t stage_in_bytes(b2p_stage* st, int64_t batch, int64_t seq) {

@@ -69,7 +69,8 @@ struct Smem {
   uint64_t bar_w2, bar_act_full[2], bar_act_empty, bar_tmem_full[2][2], bar_tmem_empty[2];
   uint32_t tmem_slot;
   int acq_upto;                                      // ring: samples of this CTA whose slot may be written (acquirer -> epilogue)
-  int stored;                                        // ring: epilogue warps that have issued a sample's peer stores (-> publisher)
+  int staged;                                        // ring: samples whose 16 KB sit complete in `out` (epilogue -> publisher)
+  int out_free;                                      // ring: samples whose bulk copy has finished READING `out` (publisher -> epilogue)
 };
 constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
 
@@ -86,6 +87,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
       : "r"(taddr)
       : "memory");
 }
+// shared -> global bulk copy (TMA store path); the destination may be another GPU's memory
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
@@ -179,7 +187,7 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
   if (tid < 64) s.b2[tid] = b2[tid];
   for (int i = tid; i < 27 * 32; i += kThreads) (&s.w1[0][0])[i] = (&c1.w[0][0])[i];
-  if (tid == 0) { s.acq_upto = 0; s.stored = 0; }
+  if (tid == 0) { s.acq_upto = 0; s.staged = 0; s.out_free = 0; }
   if (warp == kMmaWarp) {
     if (lane == 0) {
       mbar_init(&s.bar_w2, 1);
@@ -395,7 +403,12 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       for (int t = 0; t < 2; ++t) {
         mbar_wait(&s.bar_tmem_full[set][t], use & 1);
         tc_fence_after();
-        if (t == 0) B2P_TRACE(2, n, 1, et == 0);
+        if (t == 0) {
+          B2P_TRACE(2, n, 1, et == 0);
+          if (span.data) {                                  // the previous sample's bulk copy must be done reading `out`
+            while (ld_acquire_cta(&s.out_free) < (int)n) { }
+          }
+        }
 #pragma unroll 1
         for (int ch = 0; ch < 4; ++ch) {                     // 16 output channels at a time (register budget: 88 per thread)
           uint32_t r0[16], r1[16];
@@ -430,19 +443,21 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_tmem_empty[set]);
       B2P_TRACE(2, n, 2, et == 0);
-      named_bar(2, kEpiThreads);                              // the sample's 4096 outputs are staged
-      if (span.data) {                                        // the slot must have been released by the consumer:
-        while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the acquirer warp polled for it long ago
-      }
-      float4* dst = reinterpret_cast<float4*>(dst_row);
-      const float4* src = reinterpret_cast<const float4*>(s.out);
+      if (span.data) {
+        // Ring mode: the 16 KB leave through ONE bulk copy issued by the publisher warp.  With per-thread peer stores
+        // the four epilogue warps sat in the LSU queue while all 148 CTAs pushed their samples over NVLink at the same
+        // moment (2.4 MB bursts): +19 us on a 53 us step.
+        fence_proxy_async();                                  // this thread's writes to `out` -> visible to the copy engine
+        named_bar(2, kEpiThreads);                            // the sample's 4096 outputs are staged
+        if (et == 0) st_release_cta(&s.staged, (int)n + 1);
+      } else {
+        named_bar(2, kEpiThreads);                            // the sample's 4096 outputs are staged
+        float4* dst = reinterpret_cast<float4*>(dst_row);
+        const float4* src = reinterpret_cast<const float4*>(s.out);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
-      if (span.data) {                                        // hand the sample to the publisher warp
-        __syncwarp();
-        if (lane == 0) red_release_cta_add(&s.stored, 1);
+        for (int i = 0; i < 8; ++i) dst[et + 128 * i] = src[et + 128 * i];
+        named_bar(2, kEpiThreads);                            // staging buffer free for the next sample
       }
-      named_bar(2, kEpiThreads);                              // staging buffer free for the next sample
       B2P_TRACE(2, n, 3, et == 0);
     }
   } else if (span.data && lane == 0) {
@@ -452,25 +467,44 @@ part0_tc(const float* __restrict__ x,                // [B,3,32,32]
     // atomic); done by the epilogue they added ~40 us to a 64 us step.
     uint32_t n = 0;
     if (warp == kAcqWarp) {
-      // acquirer: runs ahead of the pipeline, one poll per message this CTA contributes to
+      // acquirer: runs ahead of the pipeline.  The consumer's release counter lives on the consumer's GPU, and
+      // sys-scope reads of one remote line serialise: with every CTA polling for every message (1036 polls per
+      // step) the acquirers fell behind the epilogue (+19 us per 53 us step).  So ONE CTA per message -- the one
+      // that holds the message's first row -- polls over NVLink and posts what it saw in local memory; the others
+      // wait on that local word.  (Acyclic: the poller of message m only ever waits for messages < m.)
       int acquired = -1;
       for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
         const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
         if (msg != acquired) {
           const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
-          if (k > 0) spin_until_ge_remote(span.released + slot, k);
+          if (k > 0) {
+            if (b == msg * span.rows_per_msg) {
+              spin_until_ge_remote(span.released + slot, k);
+              st_release_gpu(span.acq_seen + slot, k);
+            } else {
+              while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
+            }
+          }
           acquired = msg;
         }
         st_release_cta(&s.acq_upto, (int)n + 1);
       }
     } else {
-      // publisher: once the four epilogue warps have issued sample n's peer stores (release/acquire at CTA scope),
-      // fence at gpu scope -- cumulative over those stores -- and count the row in.  Whoever counts a message's
-      // last row has observed every other arrival; its release store of the flag, the only system-scope fence
-      // on this path, carries all of them.
+      // publisher: when sample n is staged and its slot acquired, one bulk copy (shared -> the consumer GPU's slot);
+      // as soon as the copy engine has READ the staging buffer the epilogue may refill it; when the copy has
+      // completed, fence at gpu scope and count the row in.  Whoever counts a message's last row has observed every
+      // other arrival; its release store of the flag, the only system-scope fence on this path, carries all of them.
+      // (Awaiting copy n-1 only after issuing copy n was measured slower: 68.5 vs 62.9 us per step.)
       for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
         const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
-        while (ld_acquire_cta(&s.stored) < 4 * ((int)n + 1)) __nanosleep(64);
+        float* dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) +
+                         (size_t)(b - msg * span.rows_per_msg) * 4096;
+        while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
+        while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the slot must have been released by the consumer
+        bulk_s2g(dst_row, s.out, 64 * 64 * 4);
+        bulk_wait_read();
+        st_release_cta(&s.out_free, (int)n + 1);
+        bulk_wait_all();
         __threadfence();
         const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
         if (atomicAdd(span.tickets + slot, 1) == rows - 1) {

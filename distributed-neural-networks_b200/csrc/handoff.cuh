@@ -129,8 +129,8 @@ int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->owner = true;
-  cudaError_t ce = cudaMalloc((void**)&r->local_count, (2 * slots + 4) * sizeof(unsigned long long));
-  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (2 * slots + 4) * sizeof(unsigned long long));
+  cudaError_t ce = cudaMalloc((void**)&r->local_count, (3 * slots + 4) * sizeof(unsigned long long));
+  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (3 * slots + 4) * sizeof(unsigned long long));
   r->ticket = reinterpret_cast<int*>(r->local_count + slots);
   if (ce != cudaSuccess) {
     cudaFree(base);
@@ -179,8 +179,8 @@ int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->ipc = true;
-  B2P_CUDA(cudaMalloc((void**)&r->local_count, (2 * r->slots + 4) * sizeof(unsigned long long)));
-  B2P_CUDA(cudaMemset(r->local_count, 0, (2 * r->slots + 4) * sizeof(unsigned long long)));
+  B2P_CUDA(cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long)));
+  B2P_CUDA(cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long)));
   r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
   B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
@@ -208,8 +208,8 @@ int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_de
   r->ticket = nullptr;
   {
     DeviceGuard g(producer_device);
-    B2P_CUDA(cudaMalloc((void**)&r->local_count, (2 * r->slots + 4) * sizeof(unsigned long long)));
-    B2P_CUDA(cudaMemset(r->local_count, 0, (2 * r->slots + 4) * sizeof(unsigned long long)));
+    B2P_CUDA(cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long)));
+    B2P_CUDA(cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long)));
     r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
     B2P_CUDA(cudaDeviceSynchronize());
   }

@@ -86,6 +86,7 @@ struct RingSpan {
   unsigned long long slot_bytes;
   int slots, first_slot, rows_per_msg;
   int* tickets;                    // [slots] producer side: rows stored so far into the slot (local)
+  unsigned long long* acq_seen;    // [slots] producer side: highest `released` value some CTA has observed (local)
 };
 __device__ __forceinline__ int span_slot(const RingSpan& r, int msg) { return (r.first_slot + msg) % r.slots; }
 
@@ -100,6 +101,15 @@ __device__ __forceinline__ void st_release_cta(int* p, int v) {
 }
 __device__ __forceinline__ void red_release_cta_add(int* p, int v) {
   asm volatile("red.release.cta.shared.add.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
 // consumer, before reading the slot (one thread)
