@@ -252,6 +252,28 @@ def engine_arm(args):
                 front[f"p50_ms_b{nb}"] = statistics.median(fl)
                 front[f"samples_per_s_b{nb}"] = nb * reps / (time.perf_counter() - t_all)
         server.stop(0)
+        # the same B=1 requests from 32 concurrent clients into the batching front door
+        import threading
+        runner = svc.BatchingRunner(svc.ChainRunner(pipe), max_rows=MICROBATCH, max_wait_ms=0.2)
+        server, port = svc.serve(svc.NodeServiceImpl(["node1", "node2"], runner), 0, workers=32)
+        n_clients, per_client = 32, 150
+        def client(k):
+            with grpc.insecure_channel(f"127.0.0.1:{port}", options=unlimited) as c2:
+                st2 = wire.NodeServiceStub(c2)
+                rq = wire.TensorRequest(request_id=f"c{k}", tensor=wire.ndarray_to_tensor(host_pool[2][k:k + 1].numpy()))
+                for _ in range(per_client):
+                    assert st2.SendTensor(rq).HasField("result_tensor")
+        ths = [threading.Thread(target=client, args=(k,)) for k in range(n_clients)]
+        t_all = time.perf_counter()
+        for t in ths:
+            t.start()
+        for t in ths:
+            t.join()
+        dt = time.perf_counter() - t_all
+        server.stop(0)
+        runner.close()
+        front["concurrent_b1"] = {"clients": n_clients, "requests_per_s": n_clients * per_client / dt,
+                                  "mean_rows_per_batch": sum(runner.batches) / max(len(runner.batches), 1)}
         front["what"] = ("TensorRequest -> gRPC (localhost) -> NodeService front door -> both stages on the GPU -> TensorResponse; "
                          "one request at a time, like the reference's client (node.py:170-189)")
     except Exception as e:                                   # never fail the bench on this extra

@@ -84,6 +84,96 @@ class ChainRunner:
         return np.concatenate(outs) if len(outs) != 1 else outs[0]
 
 
+class BatchingRunner:
+    """Dynamic micro-batching of concurrent requests.
+
+    The reference handles one request at a time: its forward blocks the asyncio loop (node.py:53) and every hop
+    opens a fresh channel (node.py:73), so B=1 clients pay the whole pipeline latency each.  Here gRPC worker
+    threads enqueue their tensors; ONE dispatcher thread collects what has arrived -- up to ``max_rows`` rows, waiting
+    at most ``max_wait_ms`` after the first arrival -- concatenates along the batch dimension, runs the chain once
+    and hands every caller its own rows.  No op on the path mixes samples and the K slicing is fixed, so a request's
+    result does not depend on what it was batched with (bit-exact; tests/test_gpu_cifar.py).  A failing batch is
+    re-run request by request so that one malformed request cannot poison its neighbours; shape / dtype mismatches
+    never enter a batch (only requests with the first request's row shape and dtype are merged)."""
+
+    def __init__(self, run: Callable[[np.ndarray], np.ndarray], max_rows: int = 128, max_wait_ms: float = 0.2):
+        import queue
+        import threading
+        self.run, self.max_rows, self.max_wait = run, int(max_rows), max_wait_ms * 1e-3
+        self._q: "queue.Queue" = queue.Queue()
+        self._queue_mod = queue
+        self.batches: list[int] = []            # rows per executed batch (for tests / accounting)
+        self._stop = False
+        self._t = threading.Thread(target=self._loop, name="b2p-batcher", daemon=True)
+        self._t.start()
+
+    def __call__(self, x: np.ndarray) -> np.ndarray:
+        import threading
+        item = {"x": x, "done": threading.Event(), "y": None, "err": None}
+        self._q.put(item)
+        item["done"].wait()
+        if item["err"] is not None:
+            raise item["err"]
+        return item["y"]
+
+    def close(self):
+        self._stop = True
+        self._q.put(None)
+        self._t.join(timeout=5)
+
+    def _run_alone(self, it):
+        try:
+            it["y"] = self.run(it["x"])
+        except Exception as e:                  # folded into the status string by the servicer
+            it["err"] = e
+        it["done"].set()
+
+    def _loop(self):
+        import time
+        pending = None
+        while not self._stop:
+            first = pending if pending is not None else self._q.get()
+            pending = None
+            if first is None:
+                break
+            group, rows = [first], first["x"].shape[0] if first["x"].ndim else 1
+            key = (first["x"].shape[1:], first["x"].dtype)
+            deadline = time.perf_counter() + self.max_wait
+            while rows < self.max_rows:
+                left = deadline - time.perf_counter()
+                try:
+                    nxt = self._q.get(timeout=left) if left > 0 else self._q.get_nowait()
+                except self._queue_mod.Empty:
+                    break
+                if nxt is None:
+                    self._stop = True
+                    break
+                ok = nxt["x"].ndim >= 1 and (nxt["x"].shape[1:], nxt["x"].dtype) == key
+                if not ok or rows + nxt["x"].shape[0] > self.max_rows:
+                    pending = nxt               # starts the next batch
+                    break
+                group.append(nxt)
+                rows += nxt["x"].shape[0]
+            if len(group) == 1 or first["x"].ndim < 1:
+                for it in group:
+                    self._run_alone(it)
+                self.batches.append(rows)
+                continue
+            try:
+                y = self.run(np.concatenate([it["x"] for it in group]))
+                lo = 0
+                for it in group:
+                    n = it["x"].shape[0]
+                    it["y"] = y[lo:lo + n]
+                    lo += n
+                    it["done"].set()
+                self.batches.append(rows)
+            except Exception:                   # find the culprit: everyone gets an individual run
+                for it in group:
+                    self._run_alone(it)
+                    self.batches.append(it["x"].shape[0])
+
+
 def build_cifar_chain(topology, node_id: str, math: str = "tf32x3", microbatch: int = 128, max_batch: int = 1024,
                       state_dict=None):
     """What node.py:294-318 does for every node from ``node_id`` to the end of the chain, in one
@@ -115,12 +205,13 @@ def build_cifar_chain(topology, node_id: str, math: str = "tf32x3", microbatch: 
     return NodeServiceImpl([n["id"] for n in chain], ChainRunner(pipe)), pipe
 
 
-def serve(servicer, port: int, max_message_bytes: int = -1):
+def serve(servicer, port: int, max_message_bytes: int = -1, workers: int = 1):
     """node.py:114-133 with a blocking server; one worker keeps the reference's
-    one-request-at-a-time behaviour (node.py:53 blocks its event loop)."""
+    one-request-at-a-time behaviour (node.py:53 blocks its event loop).  ``workers > 1`` admits concurrent
+    requests: give the servicer a ``BatchingRunner`` then, the chain itself runs one batch at a time."""
     import grpc
     opts = [("grpc.max_send_message_length", max_message_bytes), ("grpc.max_receive_message_length", max_message_bytes)]
-    server = grpc.server(futures.ThreadPoolExecutor(max_workers=1), options=opts)
+    server = grpc.server(futures.ThreadPoolExecutor(max_workers=workers), options=opts)
     wire.add_NodeServiceServicer_to_server(servicer, server)
     bound = server.add_insecure_port(f"[::]:{port}")
     server.start()

@@ -51,6 +51,58 @@ def test_status_strings_and_error_folding(engine):
     assert single._status(4) == "[only] Processing complete. Prediction: 4"
 
 
+def test_dynamic_batching_of_concurrent_requests(engine):
+    """concurrent B=1 clients are merged into one chain call; every caller gets its own rows back,
+    a malformed request neither joins a batch nor poisons its neighbours, and status strings stay per request."""
+    import threading
+    import time
+    svc = _svc()
+    w = engine.wire
+    calls = []
+
+    def chain(x):                                    # row i -> one-hot at int(x[i,0,0,0]) % 10; slow enough for a queue to form
+        calls.append(x.shape[0])
+        if x.ndim != 4:
+            raise ValueError("expected [B,3,32,32]")
+        if (x[:, 0, 0, 0] < 0).any():
+            raise ValueError("negative tag")
+        time.sleep(0.01)
+        y = np.zeros((x.shape[0], 10), np.float32)
+        y[np.arange(x.shape[0]), x[:, 0, 0, 0].astype(int) % 10] = 1.0
+        return y
+
+    runner = svc.BatchingRunner(chain, max_rows=16, max_wait_ms=20.0)
+    servicer = svc.NodeServiceImpl(["node1", "node2"], runner)
+    server, port = svc.serve(servicer, 0, workers=32)
+    results = {}
+    try:
+        def client(tag):
+            ch, stub = _client(engine, port)
+            x = np.full((1, 3, 32, 32), float(tag), np.float32)
+            results[tag] = stub.SendTensor(w.TensorRequest(request_id=str(tag), tensor=w.ndarray_to_tensor(x)))
+            ch.close()
+        tags = list(range(24)) + [-1]                # -1 makes its batch fail: neighbours must still succeed
+        threads = [threading.Thread(target=client, args=(t,)) for t in tags]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=30)
+        odd = _client(engine, port)
+        rep = odd[1].SendTensor(w.TensorRequest(request_id="odd", tensor=w.ndarray_to_tensor(np.zeros((2, 5), np.float32))))
+        assert rep.status == "[node1] Error: expected [B,3,32,32]" and not rep.HasField("result_tensor")
+        odd[0].close()
+    finally:
+        server.stop(0)
+        runner.close()
+    for tag in range(24):
+        rep = results[tag]
+        assert rep.status.endswith(f"Prediction: {tag % 10}"), rep.status
+        y = w.tensor_to_ndarray(rep.result_tensor)
+        assert y.shape == (1, 10) and y[0, tag % 10] == 1.0
+    assert results[-1].status == "[node1] Error: negative tag" and not results[-1].HasField("result_tensor")
+    assert max(runner.batches) > 1 and max(runner.batches) <= 16, runner.batches      # requests really were merged
+
+
 def test_messages_beyond_the_reference_cap(engine):
     """The reference cannot carry > 4 MiB; the front door can."""
     svc = _svc()
