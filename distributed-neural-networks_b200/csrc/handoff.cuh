@@ -9,7 +9,8 @@
 //   - lets the producing stage kernel store its output STRAIGHT into the mapped slot
 //     (b2p_ring_acquire -> stage forward with out = slot -> b2p_ring_publish), so the
 //     transfer rides on the kernel's own epilogue stores: zero extra copies.
-// All waiting is done on the device by one-thread kernels (acquire loads with back-off and a
+// (The CIFAR tensor-core kernels do the same handshake themselves: ring_hooks.cuh, b2p_stage_forward_ring_span.)
+// Here all waiting is done on the device by one-thread kernels (acquire loads with back-off and a
 // time-out that traps instead of hanging), so the host never blocks and the schedule of a
 // whole batch can be enqueued ahead -- or captured once in a CUDA graph and replayed: the message
 // counters live in device memory, so no launch carries a step-dependent argument.  `seq` in the

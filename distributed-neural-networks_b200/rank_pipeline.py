@@ -4,8 +4,9 @@ Reference counterpart: one ``node.py`` process per machine, stage = ``part_index
 (node.py:239-260), next hop = the node with ``part_index + 1`` (node.py:262-271), one gRPC
 ``SendTensor`` per request per hop (node.py:73-89).  Here the hop is a peer-memory ring
 (handoff.py): the producer stage's kernel stores its output straight into the consumer
-GPU's receive slot, and one-thread wait/flag kernels order the two streams -- the host of
-neither rank ever blocks inside a step.
+GPU's receive slot.  For the CIFAR tensor-core stages the slot handshake lives inside the stage
+kernels (one call and one launch per stage per step, csrc/ring_hooks.cuh); other stages order the
+two streams with one-thread wait/flag kernels.  The host of neither rank ever blocks inside a step.
 
 Launched with ``python -m torch.distributed.run --nproc-per-node N ...``; torch.distributed
 is used for rendezvous, the exchange of ring handles and the max-over-ranks of the timing.
