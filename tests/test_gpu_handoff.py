@@ -106,6 +106,14 @@ def test_forward_ring_handshake_inside_the_stage_kernels(cuda_engine, math):
         with torch.no_grad():
             assert torch.equal(ob, p1(p0(xb))), f"step {step}"
         ob.zero_()
+    # messages that are not 128 rows: the producer kernel still publishes them itself, the consumer falls back to one
+    # call per message through the one-thread handshake kernels -- same ring, same counters, same results
+    for step in range(2):
+        p0.forward_ring(xb.data_ptr(), None, 300, 0, None, prod8, 24 + 3 * step, s, 100)
+        p1.forward_ring(None, ob.data_ptr(), 300, 0, ring8, None, 24 + 3 * step, s, 100)
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            assert torch.equal(ob[:300], p1(p0(xb[:300]))), f"100-row messages, step {step}"
     with pytest.raises(L.EngineError, match="fewer slots"):
         p0.forward_ring(xb.data_ptr(), None, 1000, 0, None, prod8, 0, s, 64)
     # wrong side / oversize / missing operands are refused before anything is enqueued
