@@ -14,7 +14,7 @@ from ._lib import EngineError, launch_count
 from .gpt_model import (GPT, GPT2_MEDIUM, GPT2_SMALL, GPTConfig, balanced_ranges, from_hf_gpt2_state_dict)
 from .stages import (MODEL_PARTS_CLASSES, EngineStage, ModelPart0, ModelPart0_2Node,
                      ModelPart1_2Node, ModelPartFinal_GPT, ModelPartIntermediate,
-                     NeuralNetwork, gpt_parts_for)
+                     NeuralNetwork, gpt_parts_for, greedy_generate)
 from .topology import NodeConfig, Topology, load_config
 from . import wire
 from . import handoff, pipeline, service
@@ -23,6 +23,6 @@ __all__ = [
     "EngineError", "launch_count", "GPT", "GPTConfig", "GPT2_SMALL", "GPT2_MEDIUM", "balanced_ranges",
     "from_hf_gpt2_state_dict",
     "MODEL_PARTS_CLASSES", "EngineStage", "ModelPart0", "ModelPart0_2Node", "ModelPart1_2Node",
-    "ModelPartFinal_GPT", "ModelPartIntermediate", "NeuralNetwork", "gpt_parts_for",
+    "ModelPartFinal_GPT", "ModelPartIntermediate", "NeuralNetwork", "gpt_parts_for", "greedy_generate",
     "NodeConfig", "Topology", "load_config", "wire", "handoff", "pipeline", "service",
 ]

@@ -453,6 +453,25 @@ class ModelPartFinal_GPT(_GptPart):
         return ids
 
 
+@torch.no_grad()
+def greedy_generate(parts, idx, max_new_tokens: int):
+    """Greedy decoding through a chain of GPT parts: per new token the context (cropped to block_size,
+    like the public nanoGPT ``generate``) goes through first -> intermediate* -> final and the arg-max of the LAST
+    position is appended; the head never materialises [B,T,V] (``greedy_ids``).  The reference only ever does one
+    full-sequence forward (gpt_model_parts.py:44-50).  No KV cache yet: every step recomputes the whole context, so
+    this makes "greedy token ids" a generation metric, not a fast decoder.  idx: int64 [B,T0]; returns [B,T0+new]."""
+    block_size = parts[0].config.block_size
+    idx = idx.to(parts[0]._device)
+    for _ in range(max_new_tokens):
+        x = idx if idx.shape[1] <= block_size else idx[:, -block_size:]
+        x = parts[0](x.contiguous())
+        for p in parts[1:-1]:
+            x = p(x.to(p._device))
+        nxt = parts[-1].greedy_ids(x.to(parts[-1]._device))[:, -1:]
+        idx = torch.cat([idx, nxt.to(idx.device)], dim=1)
+    return idx
+
+
 # node.py:29-32
 MODEL_PARTS_CLASSES = {
     0: ModelPart0_2Node,

@@ -115,3 +115,19 @@ def pipeline(idx, sd, cfg: GPTConfig, n_parts: int):
     for s, e in ranges[1:-1]:
         x = part_middle(x, sd, s, e, cfg.n_head)
     return part_final(x, sd, *ranges[-1], cfg.n_head)
+
+
+@torch.no_grad()
+def greedy_generate(idx, sd, cfg: GPTConfig, n_parts: int, max_new_tokens: int):
+    """Greedy decoding through the stage chain, the way the public nanoGPT ``GPT.generate`` loops (crop the context
+    to block_size, run the model, take the LAST position) with arg-max instead of sampling.  Also returns, per new
+    token, the gap between the two largest logits so that tests can tell a real mismatch from a near-tie."""
+    gaps = []
+    for _ in range(max_new_tokens):
+        ctx = idx if idx.shape[1] <= cfg.block_size else idx[:, -cfg.block_size:]
+        logits = pipeline(ctx, sd, cfg, n_parts)[:, -1, :]
+        top2 = logits.topk(2, -1).values
+        gaps.append(top2[:, 0] - top2[:, 1])
+        idx = torch.cat([idx, logits.argmax(-1, keepdim=True)], dim=1)
+    return idx, torch.stack(gaps, dim=1)
+
