@@ -301,6 +301,13 @@ def engine_arm(args):
     r1.record(s0)
     torch.cuda.synchronize()
     us_k0_mb = 1e3 * r0.elapsed_time(r1) / (K * (BATCH // MICROBATCH))
+    out1 = pipe.out_dev
+    r0.record(s0)                           # stage 1 (fc1 + tail) alone at the same launch shape, for the second roofline
+    for i in range(K):
+        parts[1].forward_ptr(act.data_ptr(), out1.data_ptr(), BATCH, 0, s0.cuda_stream)
+    r1.record(s0)
+    torch.cuda.synchronize()
+    us_k1 = 1e3 * r0.elapsed_time(r1) / K
     sampler.active.clear()
     clocks = sampler.finish()
 
@@ -345,6 +352,15 @@ def engine_arm(args):
                 "us_per_128_sample_launch": us_k0_mb,
                 "hbm_view": {"achieved_gbs": BYTES_PART0 * BATCH / (us_k0 * 1e-6) / 1e9, "peak_gbs": peaks["hbm_gbs"]}}
 
+    # stage 1 is the memory-side kernel: fc1's weights once per launch + the [1024,4096] activation in
+    bytes_p1 = 512 * 4096 * 4 + 10 * 512 * 4 + BATCH * (4096 + 10) * 4
+    roofline_stage1 = {"kernel": f"part 1 (fc1_x3_splitk + fc_tail), one launch each per step = {BATCH} rows",
+                       "bound": "hbm", "achieved": bytes_p1 / (us_k1 * 1e-6) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                       "frac": bytes_p1 / (us_k1 * 1e-6) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                       "us_per_launch": us_k1, "algorithmic_bytes_per_launch": bytes_p1,
+                       "tensor_view": {"achieved_tflops": FLOP_PART1 * BATCH / (us_k1 * 1e-6) / 1e12,
+                                       "note": "fp32-grade 3xTF32: three tensor-core products per algorithmic FLOP"}}
+
     cpu = None
     if not args.no_cpu_baseline:
         r = time_cpu_pipeline(n_requests=600, warmup=5, budget_s=15.0)
@@ -368,6 +384,7 @@ def engine_arm(args):
                 "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
         "p50_request_latency_ms": statistics.median(lats),
         "front_door_grpc": front,
+        "roofline_stage1": roofline_stage1,
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "torch_eager_gpu": eager,
     }

@@ -49,6 +49,9 @@ _PROTOTYPES = {
     "b2p_stage_out_elems": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_stage_trace": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong), C.c_int]),
+    "b2p_stage_kv_reset": (C.c_int, [C.c_void_p, C.c_int64]),
+    "b2p_stage_forward_kv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
+                                       C.c_void_p]),
     "b2p_debug_attn_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "b2p_debug_fc_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),

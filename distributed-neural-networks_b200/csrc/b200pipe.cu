@@ -15,6 +15,7 @@
 #include "stage.cuh"
 #include "tc_gemm2.cuh"
 #include "fc_stage_tc.cuh"
+#include "kv_decode.cuh"
 
 using namespace b2p;
 
@@ -294,7 +295,9 @@ int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int
 // between the two workspace activations.  The residual stream stays fp32 in every
 // math mode; in BF16 mode the GEMM A operands (LN output, attention output, GELU
 // output) are written as bf16 by their producers.
-int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s) {
+// pos0 < 0: plain forward.  pos0 >= 0: the rows are positions pos0 .. pos0+T-1 of their sequences; their keys and values
+// go into the stage's KV cache, and a single new position (T == 1, pos0 > 0) attends to the cache instead of recomputing.
+int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s, int pos0 = -1) {
   const int C = st->d.n_embd, H = st->d.n_head, M = B * T;
   const bool bf = st->d.math == B2P_MATH_BF16;
   const float* cur = x;
@@ -305,7 +308,31 @@ int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cu
     float* x2 = (i + 1 == nb) ? final_out : st->ws_x[1];
     B2P_TRY(layernorm(st, cur, k.ln1_w, k.ln1_b, st->ws_ln, M, C, s));
     B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, k.attn_w, k.attn_b, nullptr, st->ws_qkv, bf, M, 3 * C, C, s));
-    if (bf) {
+    const bool decode = pos0 > 0;
+    if (pos0 >= 0) {
+      const int Tmax = st->d.block_size;
+      const size_t per_block = (size_t)st->kv_batch * H * Tmax * 64;
+      float* kc = st->kv_k + i * per_block;
+      float* vc = st->kv_v + i * per_block;
+      const int64_t n = (int64_t)M * H * 16;
+      if (bf)
+        B2P_LAUNCH_PDL(kv::kv_append<__nv_bfloat16>, ceil_div(n, 256), 256, 0, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
+                       kc, vc, B, T, C, H, Tmax, pos0);
+      else
+        B2P_LAUNCH_PDL(kv::kv_append<float>, ceil_div(n, 256), 256, 0, s, st->ws_qkv, kc, vc, B, T, C, H, Tmax, pos0);
+      if (decode) {
+        const size_t smem = ((size_t)Tmax + 64 + 128) * sizeof(float);
+        dim3 dgrid(H, B);
+        if (bf)
+          B2P_LAUNCH_PDL(kv::attention_decode<__nv_bfloat16>, dgrid, 128, smem, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
+                         kc, vc, reinterpret_cast<__nv_bfloat16*>(st->ws_att), C, H, Tmax, pos0);
+        else
+          B2P_LAUNCH_PDL(kv::attention_decode<float>, dgrid, 128, smem, s, st->ws_qkv, kc, vc, st->ws_att, C, H, Tmax, pos0);
+      }
+    }
+    if (decode) {
+      // (attention done above, from the cache)
+    } else if (bf) {
       B2P_TRY(attn::launch_attention_tc(reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
                                         reinterpret_cast<__nv_bfloat16*>(st->ws_att), B, T, C, H, s));
     } else {
@@ -335,8 +362,17 @@ int check_gpt_geometry(b2p_stage* st, int64_t batch, int64_t seq) {
 }
 
 int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t seq, cudaStream_t s,
-                int64_t* ids_out) {
+                int64_t* ids_out, int pos0 = -1) {
   B2P_TRY(check_gpt_geometry(st, batch, seq));
+  if (pos0 >= 0) {
+    if (!st->blocks.empty() && (!st->kv_k || batch > st->kv_batch))
+      return fail(B2P_ESTATE, "forward_kv: call b2p_stage_kv_reset for at least %lld sequences first", (long long)batch);
+    if (pos0 > 0 && seq != 1) return fail(B2P_EINVAL, "forward_kv: after the prefill (pos0 = 0) positions come one at a time");
+    if (pos0 + seq > st->d.block_size)
+      return fail(B2P_EINVAL, "forward_kv: position %lld is beyond block_size=%d (the cache holds absolute positions)",
+                  (long long)(pos0 + seq - 1), st->d.block_size);
+    if (st->d.block_size > 8192) return fail(B2P_ELIMIT, "forward_kv: block_size above 8192 does not fit the score buffer");
+  }
   const int B = (int)batch, T = (int)seq, M = B * T, C = st->d.n_embd, V = st->d.vocab_size;
   const float* x = static_cast<const float*>(in);
   if (st->d.kind == B2P_GPT_FIRST) {
@@ -344,16 +380,16 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
     // (with its own output) only after reading it for the last time.
     float* emb = st->blocks.empty() ? static_cast<float*>(out) : st->ws_x[1];
     B2P_LAUNCH(embed_f32, ceil_div((int64_t)M * 32, 256), 256, 0, s, static_cast<const int64_t*>(in),
-               st->dev(st->wte), st->dev(st->wpe), emb, M, T, C, V, st->bad_flag);
+               st->dev(st->wte), st->dev(st->wpe), emb, M, T, C, V, st->bad_flag, pos0 > 0 ? pos0 : 0);
     if (st->blocks.empty()) return 0;
-    return gpt_blocks(st, emb, static_cast<float*>(out), B, T, s);
+    return gpt_blocks(st, emb, static_cast<float*>(out), B, T, s, pos0);
   }
-  if (st->d.kind == B2P_GPT_MIDDLE) return gpt_blocks(st, x, static_cast<float*>(out), B, T, s);
+  if (st->d.kind == B2P_GPT_MIDDLE) return gpt_blocks(st, x, static_cast<float*>(out), B, T, s, pos0);
 
   // final: blocks -> ln_f -> lm_head                          gpt_model_parts.py:44-50
   const float* hx = x;
   if (!st->blocks.empty()) {
-    B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s));          // ws_att is free after the last block's proj
+    B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s, pos0));    // ws_att is free after the last block's proj
     hx = st->ws_att;
   }
   B2P_TRY(layernorm(st, hx, st->lnf_w, st->lnf_b, st->ws_ln, M, C, s));
@@ -471,7 +507,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
-  cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->trace); cudaFree(st->fc_ws);
+  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->trace); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -644,6 +680,37 @@ int b2p_stage_check(b2p_stage* st, void* stream) {
     return fail(B2P_EINVAL, "index out of range in self: a token id was outside [0, vocab_size=%d)", st->d.vocab_size);
   }
   return 0;
+}
+
+int b2p_stage_kv_reset(b2p_stage* st, int64_t batch) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  if (st->d.kind < B2P_GPT_FIRST) return fail(B2P_EINVAL, "kv_reset: only GPT stages keep a key/value cache");
+  if (!st->finalized) return fail(B2P_ESTATE, "kv_reset called before stage_finalize");
+  if (batch <= 0 || batch > 65535) return fail(B2P_EINVAL, "kv_reset: batch must be in 1..65535");
+  DeviceGuard g(st->d.device);
+  if (batch > st->kv_batch) {
+    if (st->kv_k) B2P_CUDA(cudaFree(st->kv_k));
+    if (st->kv_v) B2P_CUDA(cudaFree(st->kv_v));
+    st->kv_k = st->kv_v = nullptr;
+    st->kv_batch = 0;
+    const size_t n = std::max<size_t>(1, st->blocks.size()) * (size_t)batch * st->d.n_head * st->d.block_size * 64;
+    B2P_CUDA(cudaMalloc((void**)&st->kv_k, n * sizeof(float)));
+    B2P_CUDA(cudaMalloc((void**)&st->kv_v, n * sizeof(float)));
+    st->kv_batch = batch;
+  }
+  return 0;      // nothing to clear: a prefill at position 0 overwrites what the decode steps will read
+}
+
+int b2p_stage_forward_kv(b2p_stage* st, const void* in_dev, void* out_dev, int64_t* ids_dev, int64_t batch, int64_t seq,
+                         int64_t pos0, void* stream) {
+  if (!st || !in_dev) return fail(B2P_EINVAL, "null argument");
+  if (st->d.kind < B2P_GPT_FIRST) return fail(B2P_EINVAL, "forward_kv: only GPT stages keep a key/value cache");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_forward called before stage_finalize");
+  if (pos0 < 0) return fail(B2P_EINVAL, "forward_kv: pos0 must be >= 0");
+  if (st->d.kind == B2P_GPT_FINAL ? (!out_dev && !ids_dev) : !out_dev) return fail(B2P_EINVAL, "forward_kv: no output");
+  if (ids_dev && st->d.kind != B2P_GPT_FINAL) return fail(B2P_EINVAL, "forward_kv: greedy ids come from the final stage");
+  DeviceGuard g(st->d.device);
+  return gpt_forward(st, in_dev, out_dev, batch, seq, static_cast<cudaStream_t>(stream), ids_dev, (int)pos0);
 }
 
 int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev, int64_t batch, int64_t seq,

@@ -19,7 +19,7 @@ namespace b2p {
 __global__ void __launch_bounds__(256)
 embed_f32(const int64_t* __restrict__ idx, const float* __restrict__ wte,
           const float* __restrict__ wpe, float* __restrict__ out,
-          int M, int T, int C, int V, int* __restrict__ bad_flag) {
+          int M, int T, int C, int V, int* __restrict__ bad_flag, int pos0) {      // pos0: position of column 0 (KV-cache decoding)
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= M) return;
   long long tok = idx[warp];
@@ -28,7 +28,7 @@ embed_f32(const int64_t* __restrict__ idx, const float* __restrict__ wte,
     tok = tok < 0 ? 0 : V - 1;
   }
   const float4* a = reinterpret_cast<const float4*>(wte + (size_t)tok * C);
-  const float4* p = reinterpret_cast<const float4*>(wpe + (size_t)(warp % T) * C);
+  const float4* p = reinterpret_cast<const float4*>(wpe + (size_t)(pos0 + warp % T) * C);
   float4* o = reinterpret_cast<float4*>(out + (size_t)warp * C);
   for (int i = lane; i < C / 4; i += 32) {
     float4 x = __ldg(a + i), y = __ldg(p + i);

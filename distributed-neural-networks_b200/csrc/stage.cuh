@@ -53,6 +53,9 @@ struct b2p_stage {
   float* ws_logits = nullptr;       // forward_argmax chunk buffer (fp32 CUDA-core mode)
   size_t ws_logits_rows = 0;
   int* bad_flag = nullptr;          // device flag: out-of-range token id seen
+  float* kv_k = nullptr;            // KV cache (kv_decode.cuh): [block][B][H][block_size][64] keys ...
+  float* kv_v = nullptr;            // ... and values, allocated by b2p_stage_kv_reset
+  int64_t kv_batch = 0;             // sequences the cache is sized for
 
   int find(const std::string& n) const {
     for (size_t i = 0; i < w.size(); ++i)

@@ -328,6 +328,35 @@ class _GptPart(EngineStage):
         sd = _state_dict_of(src)
         self.load_state_dict({k: sd[k] for k in shapes if k in sd}, strict=False)
 
+    # ---- greedy decoding with a key/value cache (include/b200pipe.h: b2p_stage_kv_reset / b2p_stage_forward_kv) ----
+    def kv_reset(self, batch: int):
+        """Size this stage's KV cache for ``batch`` sequences; call before a prefill (``forward_kv(x, 0)``)."""
+        self._require_device()
+        self._finalize()
+        _lib.check(_lib.lib().b2p_stage_kv_reset(self._handle, batch))
+
+    def forward_kv(self, x, pos0: int, want_ids: bool = False):
+        """The ``x.shape[1]`` NEW positions pos0.. of every sequence: pos0 == 0 is the prefill, afterwards one position
+        per call, attending to the cache.  Returns what ``forward`` returns for those positions (``want_ids`` on the
+        final part: greedy ids [B,T] instead of logits)."""
+        self._require_device()
+        first = self.KIND == _lib.GPT_FIRST
+        x = self._prepare_input(x, torch.int64 if first else torch.float32)
+        b, t = x.shape[0], x.shape[1]
+        self._ensure_capacity(b * t)
+        self._finalize()
+        stream = torch.cuda.current_stream(self._device).cuda_stream
+        if want_ids:
+            out = torch.empty((b, t), dtype=torch.int64, device=self._device)
+            args = (None, C.c_void_p(out.data_ptr()))
+        else:
+            last = self.config.vocab_size if getattr(self, "HAS_HEAD", False) else self.config.n_embd
+            out = torch.empty((b, t, last), dtype=torch.float32, device=self._device)
+            args = (C.c_void_p(out.data_ptr()), None)
+        _lib.check(_lib.lib().b2p_stage_forward_kv(self._handle, C.c_void_p(x.data_ptr()), args[0], args[1], b, t, pos0,
+                                                   C.c_void_p(stream)))
+        return out
+
     def _full_keys(self):
         return list(self._shape_table)
 
@@ -454,21 +483,40 @@ class ModelPartFinal_GPT(_GptPart):
 
 
 @torch.no_grad()
-def greedy_generate(parts, idx, max_new_tokens: int):
-    """Greedy decoding through a chain of GPT parts: per new token the context (cropped to block_size,
-    like the public nanoGPT ``generate``) goes through first -> intermediate* -> final and the arg-max of the LAST
-    position is appended; the head never materialises [B,T,V] (``greedy_ids``).  The reference only ever does one
-    full-sequence forward (gpt_model_parts.py:44-50).  No KV cache yet: every step recomputes the whole context, so
-    this makes "greedy token ids" a generation metric, not a fast decoder.  idx: int64 [B,T0]; returns [B,T0+new]."""
+def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True):
+    """Greedy decoding through a chain of GPT parts: the arg-max of the LAST position is appended, the
+    head never materialises [B,T,V].  The reference only ever does one full-sequence forward
+    (gpt_model_parts.py:44-50).  With ``kv_cache`` the prompt is run once (prefill) and every further token costs one
+    position per stage (keys / values of earlier positions are kept per block, csrc/kv_decode.cuh); positions are
+    absolute, so once the context would exceed block_size the loop falls back to what the public nanoGPT ``generate``
+    does: re-run the chain on the context cropped to block_size.  idx: int64 [B,T0]; returns [B,T0+new]."""
     block_size = parts[0].config.block_size
     idx = idx.to(parts[0]._device)
-    for _ in range(max_new_tokens):
+
+    def chain(x, pos0=None):
+        for k, p in enumerate(parts):
+            x = x.to(p._device)
+            lastp = k == len(parts) - 1
+            if pos0 is None:
+                x = p.greedy_ids(x) if lastp else p(x.contiguous())
+            else:
+                x = p.forward_kv(x.contiguous(), pos0, want_ids=lastp)
+        return x[:, -1:].to(idx.device)
+
+    done = 0
+    if kv_cache and idx.shape[1] < block_size and max_new_tokens > 0:
+        for p in parts:
+            p.kv_reset(idx.shape[0])
+        nxt = chain(idx, 0)                                   # prefill
+        idx = torch.cat([idx, nxt], dim=1)
+        done = 1
+        while done < max_new_tokens and idx.shape[1] <= block_size:
+            nxt = chain(idx[:, -1:], idx.shape[1] - 1)        # the token just appended sits at position len-1
+            idx = torch.cat([idx, nxt], dim=1)
+            done += 1
+    for _ in range(max_new_tokens - done):
         x = idx if idx.shape[1] <= block_size else idx[:, -block_size:]
-        x = parts[0](x.contiguous())
-        for p in parts[1:-1]:
-            x = p(x.to(p._device))
-        nxt = parts[-1].greedy_ids(x.to(parts[-1]._device))[:, -1:]
-        idx = torch.cat([idx, nxt.to(idx.device)], dim=1)
+        idx = torch.cat([idx, chain(x)], dim=1)
     return idx
 
 

@@ -161,6 +161,18 @@ B2P_API int b2p_debug_fc_trace(long long* host_out, int n);
 B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev,
                              int64_t batch, int64_t seq, void* stream);
 
+/* Greedy decoding with a key/value cache (no counterpart in the reference, whose parts only ever run one
+ * full-sequence forward, gpt_model_parts.py:13-50).  kv_reset sizes the stage's cache for `batch` sequences of
+ * block_size positions.  forward_kv processes `seq` NEW positions pos0 .. pos0+seq-1 of every sequence: pos0 == 0 is the
+ * prefill (ordinary causal attention over the prompt, keys and values are stored); pos0 > 0 takes one position at a
+ * time (seq == 1) and attends to the cache.  Inputs and outputs as b2p_stage_forward ([B,seq] ids or [B,seq,C] hidden
+ * states in, hidden states or logits out); on the final stage ids_dev != NULL returns greedy ids [B,seq] instead of
+ * logits.  Positions are absolute (learned position embeddings): pos0 + seq <= block_size, beyond that a caller has to
+ * re-run the cropped context.  B2P_ESTATE without kv_reset, B2P_EINVAL for positions out of order or out of range. */
+B2P_API int b2p_stage_kv_reset(b2p_stage* st, int64_t batch);
+B2P_API int b2p_stage_forward_kv(b2p_stage* st, const void* in_dev, void* out_dev, int64_t* ids_dev, int64_t batch,
+                                 int64_t seq, int64_t pos0, void* stream);
+
 /* ---- dense contraction building block (tcgen05 tensor cores) ------------------------
  *   out[m,n] = act( sum_k A[m,k] * W[n,k] + bias[n] ) + res[m,n]
  * i.e. every nn.Linear call site on the path (cifar_model_parts.py:13-14,55-56; the

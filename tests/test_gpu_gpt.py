@@ -218,9 +218,10 @@ def test_hf_gpt2_checkpoint_through_the_engine(cuda_engine):
     assert torch.equal(got.argmax(-1), want.argmax(-1)) or ((want.topk(2, -1).values[..., 0] - want.topk(2, -1).values[..., 1]).min() < 2e-4)
 
 
+@pytest.mark.parametrize("kv_cache", [False, True])
 @pytest.mark.parametrize("math", ["fp32", "tf32x3"])
-def test_greedy_generation_matches_the_oracle(cuda_engine, math):
-    """SURVEY 8f-2 (functional form, no KV cache): 24 greedy tokens through a 2-part chain, the context growing past
+def test_greedy_generation_matches_the_oracle(cuda_engine, math, kv_cache):
+    """SURVEY 8f-2, with and without the key/value cache: 24 greedy tokens through a 2-part chain, the context growing past
     block_size so the crop is exercised; token ids bit-exact with the CPU oracle wherever the oracle's top-2 gap
     at that step exceeds the logit tolerance (after a near-tie the two sequences may legitimately diverge)."""
     cfg = gpt_model.GPTConfig(block_size=24, vocab_size=211, n_layer=2, n_head=2, n_embd=128)
@@ -236,7 +237,7 @@ def test_greedy_generation_matches_the_oracle(cuda_engine, math):
     parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math=math, max_tokens=3 * 24)]
     prompt = gpt_oracle.make_tokens(3, 5, cfg.vocab_size, seed=9)
     want, gaps = gpt_oracle.greedy_generate(prompt, sd, cfg, 2, 24)
-    got = cuda_engine.greedy_generate(parts, prompt, 24).cpu()
+    got = cuda_engine.greedy_generate(parts, prompt, 24, kv_cache=kv_cache).cpu()
     assert got.shape == want.shape == (3, 29)
     assert torch.equal(got[:, :5], prompt)
     checked = 0
@@ -248,4 +249,49 @@ def test_greedy_generation_matches_the_oracle(cuda_engine, math):
             checked += 1
     assert checked >= 48, f"only {checked} tokens were decidable"
     assert len(set(want[0, 5:].tolist())) > 5                 # a real sequence, not one token repeated
+
+
+@pytest.mark.parametrize("math,tol", [("fp32", LOGIT_TOL), ("tf32x3", LOGIT_TOL), ("bf16", 3e-2)])
+def test_kv_cache_steps_equal_the_full_forward(cuda_engine, math, tol):
+    """forward_kv: the prefill returns what forward returns, and every cached single-position step returns the last
+    row of a full forward over the longer context (3-part chain, ragged prompt length, geometry errors)."""
+    cfg = gpt_model.GPTConfig(block_size=80, vocab_size=300, n_layer=3, n_head=2, n_embd=128)
+    sd = gpt_oracle.init_state_dict(cfg, seed=21)
+    g = torch.Generator().manual_seed(2)
+    for k in sd:
+        if k.endswith("bias") or "ln_" in k:
+            sd[k] = sd[k] + 0.1 * torch.randn(sd[k].shape, generator=g)
+    model = cuda_engine.GPT(cuda_engine.GPTConfig(block_size=80, vocab_size=300, n_layer=3, n_head=2, n_embd=128))
+    model.load_state_dict(sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 3, math=math, max_tokens=2 * 80)]
+    idx = gpt_oracle.make_tokens(2, 70, cfg.vocab_size, seed=4).cuda()
+
+    def full(x):
+        for p in parts:
+            x = p(x)
+        return x
+
+    def cached(x, pos0):
+        for p in parts:
+            x = p.forward_kv(x, pos0)
+        return x
+
+    L = cuda_engine._lib
+    with torch.no_grad():
+        with pytest.raises(L.EngineError, match="kv_reset"):
+            parts[0].forward_kv(idx[:, :37], 0)
+        for p in parts:
+            p.kv_reset(2)
+        pre = cached(idx[:, :37], 0)
+        ref = full(idx[:, :37])
+        assert (pre - ref).abs().max().item() <= (0 if math != "bf16" else tol)     # same kernels, same bits
+        for pos in range(37, 70):
+            step = cached(idx[:, pos:pos + 1], pos)
+            want = full(idx[:, :pos + 1])[:, -1:]
+            err = (step - want).abs().max().item()
+            assert err <= tol, f"position {pos}: {err}"
+        with pytest.raises(L.EngineError, match="one at a time"):
+            parts[0].forward_kv(idx[:, :2], 5)
+        with pytest.raises(L.EngineError, match="beyond block_size"):
+            parts[0].forward_kv(idx[:, :1], 80)
 
