@@ -245,7 +245,7 @@ def engine_arm(args):
                     if i == 20:
                         t_all = time.perf_counter()
                     q0 = time.perf_counter()
-                    resp = stub.SendTensor(req)
+                    resp = stub.SendTensor(req, timeout=30)
                     if i >= 20:
                         fl.append(1e3 * (time.perf_counter() - q0))
                 assert resp.HasField("result_tensor"), resp.status
@@ -262,13 +262,13 @@ def engine_arm(args):
                 st2 = wire.NodeServiceStub(c2)
                 rq = wire.TensorRequest(request_id=f"c{k}", tensor=wire.ndarray_to_tensor(host_pool[2][k:k + 1].numpy()))
                 for _ in range(per_client):
-                    assert st2.SendTensor(rq).HasField("result_tensor")
+                    assert st2.SendTensor(rq, timeout=30).HasField("result_tensor")
         ths = [threading.Thread(target=client, args=(k,)) for k in range(n_clients)]
         t_all = time.perf_counter()
         for t in ths:
             t.start()
         for t in ths:
-            t.join()
+            t.join(timeout=120)
         dt = time.perf_counter() - t_all
         server.stop(0)
         runner.close()
