@@ -47,4 +47,4 @@ def timeit(fn, n=50):
 t_local = timeit(local_step)
 # the fake producer publishes 50 steps ahead is impossible (8 slots): interleave, the producer side is two tiny kernels per message
 t_ring = timeit(lambda: (prod_step(), cons_step()))
-print(f"B2P_SPAN_DEBUG={os.environ.get('B2P_SPAN_DEBUG', '0')}: consumer local {t_local:7.2f} us/step, from ring {t_ring:7.2f} us/step")
+print(f"consumer local {t_local:7.2f} us/step, from ring {t_ring:7.2f} us/step")
