@@ -11,10 +11,12 @@ default-init weights.  A "step" is one batch of 1024 through both stages.
   N=4/8  N/2 independent 2-stage pipelines (CIFAR has only two stages).
 `value`  samples/s with inputs resident in HBM; `e2e` the same through the host-facing
 call (pinned host input -> H2D -> stages -> D2H result inside the timed region).
-`--impl reference` times the CPU port of the reference's two-node localhost gRPC
-pipeline (oracle/node_oracle.py; the reference itself is Python and cannot travel to the
-GPU box) on the host cores; one reference step = ONE microbatch request of 128 samples
-(the reference cannot carry more than 255 samples per message: 4 MiB gRPC cap).
+`--impl reference` times the reference's own two-node localhost gRPC pipeline on the host
+cores: two processes of the UNMODIFIED node.py when oracle/_ref/ holds it (placed there by
+oracle/build_ref.py, it travels to the GPU box with the snapshot; cpu_baseline.kind =
+"reference"), else the CPU port oracle/node_oracle.py (kind = "port").  One reference step =
+ONE microbatch request of 128 samples (the reference cannot carry more than 255 samples per
+message: 4 MiB gRPC cap); the B=1 figure of BASELINE config 1 is reported beside it.
 """
 from __future__ import annotations
 
@@ -87,14 +89,14 @@ class ClockSampler(threading.Thread):
 # ============================================================================================
 # reference arm: CPU port of the two-node gRPC pipeline
 # ============================================================================================
-def time_cpu_pipeline(n_requests: int, warmup: int, batch: int = MICROBATCH, budget_s: float = 120.0):
+def time_cpu_pipeline(n_requests: int, warmup: int, batch: int = MICROBATCH, budget_s: float = 120.0, b1_requests: int = 100):
     import numpy as np
     import torch
     from oracle import cifar_oracle as co
     from oracle.node_oracle import TwoNodePipeline
     sd = co.init_state_dict(WEIGHT_SEED)
     xs = [co.make_input(batch, seed=INPUT_SEED + i).numpy() for i in range(4)]
-    lat = []
+    lat, lat1 = [], []
     with TwoNodePipeline(sd) as pipe:
         for i in range(warmup):
             pipe.request(xs[i % 4], f"warm{i}")
@@ -107,8 +109,21 @@ def time_cpu_pipeline(n_requests: int, warmup: int, batch: int = MICROBATCH, bud
             if time.perf_counter() - t_start > budget_s:
                 break
         total = time.perf_counter() - t_start
+        # the result must be the oracle's, whichever implementation served it
+        want = co.full(torch.from_numpy(xs[(len(lat) - 1) % 4]), sd).numpy()
+        assert np.abs(res - want).max() < 1e-6, "CPU pipeline result differs from the oracle"
+        # BASELINE config 1: batch 1 of 3x32x32 through the same two nodes
+        for i in range(5 + b1_requests):
+            t0 = time.perf_counter()
+            res1, status = pipe.request(xs[0][:1], f"one{i}")
+            if i >= 5:
+                lat1.append(time.perf_counter() - t0)
+        kind = pipe.kind
     return {"samples_per_s": batch * len(lat) / total, "requests": len(lat), "batch": batch,
-            "p50_ms": 1e3 * statistics.median(lat), "total_s": total,
+            "p50_ms": 1e3 * statistics.median(lat), "total_s": total, "kind": kind,
+            "p50_ms_b1": 1e3 * statistics.median(lat1) if lat1 else None,
+            "what": ("the unmodified reference node.py (oracle/_ref), two processes" if kind == "reference"
+                     else "the CPU port of the reference's node loop (oracle/node_oracle.py), two processes"),
             "cores": os.cpu_count(), "torch_threads": os.cpu_count()}   # node processes use torch's default = all cores
 
 
@@ -117,7 +132,7 @@ def reference_arm(args):
     if rank != 0:
         return 0
     r = time_cpu_pipeline(args.steps, args.warmup)
-    sample = (f"{r['requests']} requests of {r['batch']} samples (one microbatch each) through the CPU port of "
+    sample = (f"{r['requests']} requests of {r['batch']} samples (one microbatch each) through {r['what']} of "
               f"the 2-node localhost gRPC pipeline, torch threads {r['torch_threads']} per node process")
     line = {
         "impl": "reference", "metric": METRIC, "value": r["samples_per_s"], "unit": UNIT,
@@ -127,7 +142,10 @@ def reference_arm(args):
         "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH,
                    "step": "one 128-sample request (bounded sample: 1/8 of a 1024 batch)"},
         "p50_request_latency_ms": r["p50_ms"],
-        "cpu_baseline": {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+        "config1_b1": {"p50_request_latency_ms": r["p50_ms_b1"],
+                       "samples_per_s": 1e3 / r["p50_ms_b1"] if r["p50_ms_b1"] else None,
+                       "what": "BASELINE config 1: batch 1 of 3x32x32 through the two localhost gRPC nodes on CPU"},
+        "cpu_baseline": {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
                          "sample": sample},
         "e2e": {"value": r["samples_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -211,7 +229,17 @@ def engine_arm(args):
     pipe.synchronize()
     torch.cuda.synchronize()
     ms_e2e = 1e3 * (time.perf_counter() - w0)
-    checksum = float(pipe.out_host.sum())          # a real read of the last step's result
+    # a real check of the last step's result (outside the timed region): probabilities and arg-max classes of the
+    # batch that went through last, against the CPU oracle on the same host tensor
+    import numpy as np
+    from oracle import cifar_oracle as co
+    got = pipe.out_host.clone()
+    want = co.full(host_pool[(W + K - 1) % n_pool], {k: v.cpu() for k, v in sd.items()})
+    e2e_diff = float((got - want).abs().max())
+    e2e_argmax_equal = bool(torch.equal(got.argmax(1), want.argmax(1)))
+    top2 = want.topk(2, dim=1).values
+    near_ties = int(((top2[:, 0] - top2[:, 1]) < 1e-5).sum())
+    assert e2e_diff < 1e-5 or args.math == "tf32", f"engine result differs from the oracle by {e2e_diff}"
 
     # -- (3) request latency: B=1 through the same call, synchronous ---------------------------------------
     one = host_pool[0][:1].clone().pin_memory()
@@ -283,31 +311,32 @@ def engine_arm(args):
     s0 = pipe.compute[0]
     act = pipe.hidden[0]
     r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n_launch = 0
+    KR = max(K, 200)                        # at least 200 launches whatever --steps is: a 20-launch window is 1 ms
+    for i in range(5):
+        parts[0].forward_ptr(dev_pool[i].data_ptr(), act.data_ptr(), BATCH, 0, s0.cuda_stream)
     torch.cuda.synchronize()
     r0.record(s0)
-    for i in range(K):                      # the launch shape of the timed region: one launch per step (1024 rows)
+    for i in range(KR):                     # the launch shape of the timed region: one launch per step (1024 rows)
         x = dev_pool[(W + i) % n_pool]
         parts[0].forward_ptr(x.data_ptr(), act.data_ptr(), BATCH, 0, s0.cuda_stream)
-        n_launch += 1
     r1.record(s0)
     torch.cuda.synchronize()
-    us_k0 = 1e3 * r0.elapsed_time(r1) / n_launch
+    us_k0 = 1e3 * r0.elapsed_time(r1) / KR
     r0.record(s0)                           # for reference: the same kernel launched per 128-row microbatch
-    for i in range(K):
+    for i in range(KR // 4):
         x = dev_pool[(W + i) % n_pool]
         for lo in range(0, BATCH, MICROBATCH):
             parts[0].forward_ptr(x[lo:].data_ptr(), act[lo:].data_ptr(), MICROBATCH, 0, s0.cuda_stream)
     r1.record(s0)
     torch.cuda.synchronize()
-    us_k0_mb = 1e3 * r0.elapsed_time(r1) / (K * (BATCH // MICROBATCH))
+    us_k0_mb = 1e3 * r0.elapsed_time(r1) / ((KR // 4) * (BATCH // MICROBATCH))
     out1 = pipe.out_dev
     r0.record(s0)                           # stage 1 (fc1 + tail) alone at the same launch shape, for the second roofline
-    for i in range(K):
+    for i in range(KR):
         parts[1].forward_ptr(act.data_ptr(), out1.data_ptr(), BATCH, 0, s0.cuda_stream)
     r1.record(s0)
     torch.cuda.synchronize()
-    us_k1 = 1e3 * r0.elapsed_time(r1) / K
+    us_k1 = 1e3 * r0.elapsed_time(r1) / KR
     sampler.active.clear()
     clocks = sampler.finish()
 
@@ -348,7 +377,7 @@ def engine_arm(args):
     roofline = {"kernel": f"part0_tc (conv1+ReLU+pool+conv2+ReLU+pool), one launch per step = {BATCH} samples",
                 "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
                 "traffic": traffic, "peak_source": f"bf16_tflops_sustained of {peaks_kind}",
-                "us_per_launch": us_k0, "algorithmic_bytes_per_launch": BYTES_PART0 * BATCH,
+                "us_per_launch": us_k0, "launches_timed": KR, "algorithmic_bytes_per_launch": BYTES_PART0 * BATCH,
                 "us_per_128_sample_launch": us_k0_mb,
                 "hbm_view": {"achieved_gbs": BYTES_PART0 * BATCH / (us_k0 * 1e-6) / 1e9, "peak_gbs": peaks["hbm_gbs"]}}
 
@@ -364,9 +393,9 @@ def engine_arm(args):
     cpu = None
     if not args.no_cpu_baseline:
         r = time_cpu_pipeline(n_requests=600, warmup=5, budget_s=15.0)
-        cpu = {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-               "p50_request_latency_ms": r["p50_ms"],
-               "sample": f"{r['requests']} requests of {r['batch']} samples through the CPU port of the reference's "
+        cpu = {"value": r["samples_per_s"], "unit": UNIT, "cores": r["cores"], "kind": r["kind"],
+               "p50_request_latency_ms": r["p50_ms"], "p50_request_latency_ms_b1": r["p50_ms_b1"],
+               "sample": f"{r['requests']} requests of {r['batch']} samples through {r['what']} of the "
                          f"2-node localhost gRPC pipeline ({r['total_s']:.1f} s, torch threads {r['torch_threads']})"}
 
     line = {
@@ -381,7 +410,10 @@ def engine_arm(args):
                    "launch": "cuda_graph_per_step" if use_graph else "per_kernel",
                    "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
         "e2e": {"value": BATCH * K / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4,
-                "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K, "result_checksum": checksum},
+                "d2h_bytes_per_step": BATCH * 10 * 4, "ms_per_step": ms_e2e / K,
+                "max_abs_diff_vs_oracle": e2e_diff, "argmax_equal_oracle": e2e_argmax_equal,
+                "oracle_near_ties_below_1e-5": near_ties,
+                "checked": f"last step's {BATCH} probability rows and arg-max classes vs oracle/cifar_oracle.full on the same host batch"},
         "p50_request_latency_ms": statistics.median(lats),
         "front_door_grpc": front,
         "roofline_stage1": roofline_stage1,

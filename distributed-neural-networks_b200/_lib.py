@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200pipe.so")
 
 # mirror of the header's constants
-OK, EINVAL, ECUDA, ESTATE, EMISSING, ELIMIT = 0, -1, -2, -3, -4, -5
+OK, EINVAL, ECUDA, ESTATE, EMISSING, ELIMIT, ETIMEOUT = 0, -1, -2, -3, -4, -5, -6
 CIFAR_PART0, CIFAR_PART1, GPT_FIRST, GPT_MIDDLE, GPT_FINAL = range(5)
 MATH_FP32, MATH_TF32X3, MATH_TF32, MATH_BF16 = range(4)
 MATH_NAMES = {"fp32": MATH_FP32, "tf32x3": MATH_TF32X3, "tf32": MATH_TF32, "bf16": MATH_BF16}
@@ -46,6 +46,10 @@ _PROTOTYPES = {
                                         C.POINTER(C.c_int64), C.c_int32]),
     "b2p_stage_missing": (C.c_int, [C.c_void_p, C.c_char_p, C.c_size_t]),
     "b2p_stage_finalize": (C.c_int, [C.c_void_p]),
+    "b2p_stage_reserve": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64]),
+    "b2p_stage_set_pdl": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2p_ring_set_timeout": (C.c_int, [C.c_int, C.c_double]),
+    "b2p_ring_check": (C.c_int, [C.c_int]),
     "b2p_stage_out_elems": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),
     "b2p_stage_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b2p_stage_trace": (C.c_int, [C.c_void_p, C.POINTER(C.c_longlong), C.c_int]),

@@ -36,6 +36,28 @@ int dev_alloc(T** p, size_t n_elems) {
   return 0;
 }
 
+// Scratch that depends on the batch (split-K partials, hi/lo planes, arg-max partials) is sized by
+// b2p_stage_finalize (CIFAR part 1: 1024 rows; GPT: max_tokens) and b2p_stage_reserve.  A forward that needs more than
+// that grows it on the spot -- cudaFree + cudaMalloc, which synchronise the device -- and refuses to do so while its
+// stream is being captured (the allocation would invalidate the capture).
+template <typename T>
+int ensure_scratch(T** p, size_t* have, size_t need, size_t elem_bytes, cudaStream_t s, bool check_capture, const char* what) {
+  if (need <= *have) return 0;
+  if (check_capture) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone)
+      return fail(B2P_ESTATE, "forward needs a larger %s buffer than reserved and its stream is being captured: call "
+                              "b2p_stage_reserve for the largest batch before starting the capture", what);
+    cudaGetLastError();
+  }
+  if (*p) B2P_CUDA(cudaFree(*p));
+  *p = nullptr;
+  *have = 0;
+  B2P_CUDA(cudaMalloc((void**)p, need * elem_bytes));
+  *have = need;
+  return 0;
+}
+
 bool is_cifar(int kind) { return kind == B2P_CIFAR_PART0 || kind == B2P_CIFAR_PART1; }
 bool is_gpt(int kind) { return kind == B2P_GPT_FIRST || kind == B2P_GPT_MIDDLE || kind == B2P_GPT_FINAL; }
 
@@ -152,14 +174,7 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   const bool tcm = st->d.math != B2P_MATH_FP32;
   if (st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled()) {
     // fc1 with the activation split inside the kernel (fc_stage_tc.cuh), 32 K slices, then the shared tail
-    const size_t need = fcs::ws_bytes(batch);
-    if (need > st->fc_ws_bytes) {
-      if (st->fc_ws) B2P_CUDA(cudaFree(st->fc_ws));
-      st->fc_ws = nullptr;
-      st->fc_ws_bytes = 0;
-      B2P_CUDA(cudaMalloc((void**)&st->fc_ws, need));
-      st->fc_ws_bytes = need;
-    }
+    B2P_TRY(ensure_scratch(&st->fc_ws, &st->fc_ws_bytes, fcs::ws_bytes(batch), 1, s, true, "fc1 split-K"));
     const b2p_weight& w = st->w[0];
     const int parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, span);
     if (parts < 0) return parts;
@@ -173,15 +188,8 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     return 0;
   }
   const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);
-  const size_t need = (size_t)splits * batch * FC1_N * sizeof(float);
-  if (need > st->fc_ws_bytes) {
-    // grow the split-K scratch; synchronous, happens only when a larger batch shows up
-    if (st->fc_ws) B2P_CUDA(cudaFree(st->fc_ws));
-    st->fc_ws = nullptr;
-    st->fc_ws_bytes = 0;
-    B2P_CUDA(cudaMalloc((void**)&st->fc_ws, need));
-    st->fc_ws_bytes = need;
-  }
+  B2P_TRY(ensure_scratch(&st->fc_ws, &st->fc_ws_bytes, (size_t)splits * batch * FC1_N * sizeof(float), 1, s, true,
+                         "fc1 split-K"));
   if (tcm) {
     B2P_TRY(stage_linear(st, EPI_NONE, in, 0, -1, nullptr, st->fc_ws, false, (int)batch, FC1_N, FC1_K, s, splits,
                          (int64_t)batch * FC1_N));
@@ -215,13 +223,7 @@ int elementwise_grid(size_t n) { return (int)std::min<size_t>((n + 255) / 256, 1
 
 // hi | lo planes of an fp32 activation for the 3xTF32 contraction (grows on demand)
 int split_activation(b2p_stage* st, const float* A, size_t n, cudaStream_t s) {
-  if (n > st->ws_split_elems) {
-    if (st->ws_split) B2P_CUDA(cudaFree(st->ws_split));
-    st->ws_split = nullptr;
-    st->ws_split_elems = 0;
-    B2P_CUDA(cudaMalloc((void**)&st->ws_split, 2 * n * sizeof(float)));
-    st->ws_split_elems = n;
-  }
+  B2P_TRY(ensure_scratch(&st->ws_split, &st->ws_split_elems, n, 2 * sizeof(float), s, true, "hi/lo plane"));
   B2P_LAUNCH_PDL(split_tf32, elementwise_grid(n), 256, 0, s, A, st->ws_split, st->ws_split + st->ws_split_elems, n);
   return 0;
 }
@@ -361,6 +363,46 @@ int check_gpt_geometry(b2p_stage* st, int64_t batch, int64_t seq) {
   return 0;
 }
 
+int reserve_amax(b2p_stage* st, size_t need, cudaStream_t s, bool check_capture) {
+  if (need <= st->amax_elems) return 0;
+  size_t have_v = st->amax_elems, have_i = st->amax_elems;
+  st->amax_elems = 0;
+  B2P_TRY(ensure_scratch(&st->amax_val, &have_v, need, sizeof(float), s, check_capture, "arg-max partial"));
+  B2P_TRY(ensure_scratch(&st->amax_idx, &have_i, need, sizeof(int), s, false, "arg-max partial"));
+  st->amax_elems = need;
+  return 0;
+}
+
+// Everything a forward of `rows` rows (CIFAR: batch; GPT: batch*seq tokens) may need beyond the stage's fixed workspaces.
+int reserve_rows(b2p_stage* st, int64_t rows) {
+  const size_t M = (size_t)rows;
+  switch (st->d.kind) {
+    case B2P_CIFAR_PART0:
+      return 0;                                              // no scratch at all: everything lives in shared / tensor memory
+    case B2P_CIFAR_PART1: {
+      size_t need = (size_t)(st->d.math == B2P_MATH_FP32 ? FC1_SPLITS : FC1_SPLITS_TC) * M * FC1_N * sizeof(float);
+      if (st->d.math == B2P_MATH_TF32X3) {
+        need = std::max(need, fcs::ws_bytes((int64_t)M));
+        B2P_TRY(ensure_scratch(&st->ws_split, &st->ws_split_elems, M * FC1_K, 2 * sizeof(float), nullptr, false, ""));   // B2P_FC_FUSED=0 path
+      }
+      return ensure_scratch(&st->fc_ws, &st->fc_ws_bytes, need, 1, nullptr, false, "");
+    }
+    default: {
+      const size_t C = (size_t)st->d.n_embd;
+      if (st->d.math == B2P_MATH_TF32X3)
+        B2P_TRY(ensure_scratch(&st->ws_split, &st->ws_split_elems, M * 4 * C, 2 * sizeof(float), nullptr, false, ""));
+      if (st->d.kind == B2P_GPT_FINAL) {
+        if (st->d.math != B2P_MATH_FP32)
+          B2P_TRY(reserve_amax(st, M * 2 * (size_t)ceil_div(st->d.vocab_size, 128), nullptr, false));
+        else
+          B2P_TRY(ensure_scratch(&st->ws_logits, &st->ws_logits_rows, std::min<size_t>(M, 2048),
+                                 (size_t)st->d.vocab_size * sizeof(float), nullptr, false, ""));
+      }
+      return 0;
+    }
+  }
+}
+
 int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t seq, cudaStream_t s,
                 int64_t* ids_out, int pos0 = -1) {
   B2P_TRY(check_gpt_geometry(st, batch, seq));
@@ -397,15 +439,7 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
   if (st->d.math != B2P_MATH_FP32) {
     // tensor-core modes: arg-max fused into the LM-head epilogue, logits never materialised
     const int slots = 2 * ceil_div(V, 128);              // the head runs with 128-wide tiles here
-    const size_t need = (size_t)M * slots;
-    if (st->amax_elems < need) {
-      if (st->amax_val) B2P_CUDA(cudaFree(st->amax_val));
-      if (st->amax_idx) B2P_CUDA(cudaFree(st->amax_idx));
-      st->amax_val = nullptr; st->amax_idx = nullptr; st->amax_elems = 0;
-      B2P_CUDA(cudaMalloc((void**)&st->amax_val, need * sizeof(float)));
-      B2P_CUDA(cudaMalloc((void**)&st->amax_idx, need * sizeof(int)));
-      st->amax_elems = need;
-    }
+    B2P_TRY(reserve_amax(st, (size_t)M * slots, s, true));
     B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, st->amax_val /*unused*/, false, M, V, C, s, 1, 0,
                          st->amax_val, st->amax_idx, slots));
     B2P_LAUNCH_PDL(argmax_partials, ceil_div((int64_t)M * 32, 256), 256, 0, s, st->amax_val, st->amax_idx, ids_out, M, slots);
@@ -413,13 +447,7 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
   }
   // fp32 CUDA-core mode: logits in row chunks through a bounded scratch buffer, then row arg-max
   const size_t chunk = std::min<size_t>((size_t)M, 2048);
-  if (st->ws_logits_rows < chunk) {
-    if (st->ws_logits) B2P_CUDA(cudaFree(st->ws_logits));
-    st->ws_logits = nullptr;
-    st->ws_logits_rows = 0;
-    B2P_CUDA(cudaMalloc((void**)&st->ws_logits, chunk * (size_t)V * sizeof(float)));
-    st->ws_logits_rows = chunk;
-  }
+  B2P_TRY(ensure_scratch(&st->ws_logits, &st->ws_logits_rows, chunk, (size_t)V * sizeof(float), s, true, "logit chunk"));
   for (size_t m0 = 0; m0 < (size_t)M; m0 += chunk) {
     const int rows = (int)std::min(chunk, (size_t)M - m0);
     const char* a_rows = reinterpret_cast<const char*>(st->ws_ln) +
@@ -588,9 +616,35 @@ int b2p_stage_finalize(b2p_stage* st) {
       B2P_LAUNCH(split_tf32, elementwise_grid(n), 256, 0, 0, w.dev, static_cast<float*>(w.packed), w.packed_lo, n);
     }
   }
+  // batch-dependent scratch, so that no forward up to these sizes ever allocates (b2p_stage_reserve raises them)
+  B2P_TRY(reserve_rows(st, is_cifar(st->d.kind) ? 1024 : st->d.max_tokens));
   B2P_CUDA(cudaDeviceSynchronize());
   st->finalized = true;
   return 0;
+}
+
+int b2p_stage_reserve(b2p_stage* st, int64_t batch, int64_t seq) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_reserve called before stage_finalize");
+  if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  int64_t rows = batch;
+  if (is_gpt(st->d.kind)) {
+    if (seq <= 0) return fail(B2P_EINVAL, "seq must be positive for a GPT stage");
+    rows = batch * seq;
+    if (rows > st->d.max_tokens)
+      return fail(B2P_ELIMIT, "batch*seq=%lld exceeds the stage's max_tokens=%d (fixed at creation)", (long long)rows,
+                  st->d.max_tokens);
+  }
+  if (rows > (1LL << 30)) return fail(B2P_ELIMIT, "batch too large");
+  DeviceGuard g(st->d.device);
+  return reserve_rows(st, rows);
+}
+
+int b2p_stage_set_pdl(b2p_stage* st, int mask) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  const int prev = st->pdl_mask;
+  st->pdl_mask = mask < 0 ? -1 : (mask & 3);
+  return prev < 0 ? pdl_switch().load() : prev;
 }
 
 int b2p_stage_out_elems(b2p_stage* st, int64_t batch, int64_t seq, int64_t* elems) {
@@ -610,6 +664,7 @@ int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev, int64_t 
   if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
   if (batch > (1LL << 30)) return fail(B2P_ELIMIT, "batch too large");
   DeviceGuard g(st->d.device);
+  PdlScope pdl(st->pdl_mask);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (st->d.kind) {
     case B2P_CIFAR_PART0:
@@ -710,6 +765,7 @@ int b2p_stage_forward_kv(b2p_stage* st, const void* in_dev, void* out_dev, int64
   if (st->d.kind == B2P_GPT_FINAL ? (!out_dev && !ids_dev) : !out_dev) return fail(B2P_EINVAL, "forward_kv: no output");
   if (ids_dev && st->d.kind != B2P_GPT_FINAL) return fail(B2P_EINVAL, "forward_kv: greedy ids come from the final stage");
   DeviceGuard g(st->d.device);
+  PdlScope pdl(st->pdl_mask);
   return gpt_forward(st, in_dev, out_dev, batch, seq, static_cast<cudaStream_t>(stream), ids_dev, (int)pos0);
 }
 
@@ -719,6 +775,7 @@ int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev
   if (st->d.kind != B2P_GPT_FINAL) return fail(B2P_EINVAL, "forward_argmax is only defined for the GPT final stage");
   if (!st->finalized) return fail(B2P_ESTATE, "stage_forward_argmax called before stage_finalize");
   DeviceGuard g(st->d.device);
+  PdlScope pdl(st->pdl_mask);
   return gpt_forward(st, in_dev, nullptr, batch, seq, static_cast<cudaStream_t>(stream), ids_dev);
 }
 
@@ -792,6 +849,7 @@ extern "C" int b2p_stage_forward_ring_span(b2p_stage* st, const void* in_dev, vo
   const bool hooked_in = ring_in && st->d.kind == B2P_CIFAR_PART1 && st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled() &&
                          !ring_out && (rows_per_msg == fcs::BM || (msgs == 1 && batch <= fcs::BM)) &&
                          ring_in->slot_bytes == (size_t)fcs::BM * fcs::K_IN * 4;
+  PdlScope pdl(st->pdl_mask);
   if (hooked_out) {
     DeviceGuard g(st->d.device);
     return cifar_part0_forward(st, static_cast<const float*>(in_dev), static_cast<float*>(out_dev), batch, s,
@@ -886,6 +944,9 @@ extern "C" int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* 
   if (!x_dev || !fc1_weight_dev || !fc1_bias_dev || !fc2_weight_dev || !fc2_bias_dev || !out_dev)
     return fail(B2P_EINVAL, "null argument");
   if (batch <= 0) return fail(B2P_EINVAL, "batch must be positive (got %lld)", (long long)batch);
+  if ((reinterpret_cast<uintptr_t>(x_dev) | reinterpret_cast<uintptr_t>(fc1_weight_dev) |
+       reinterpret_cast<uintptr_t>(fc1_bias_dev) | reinterpret_cast<uintptr_t>(fc2_weight_dev)) & 15)
+    return fail(B2P_EINVAL, "x, fc1_weight, fc1_bias and fc2_weight must be 16-byte aligned (they are read with 128-bit loads)");
   if (batch > B2P_NOALLOC_MAX_BATCH)
     return fail(B2P_ELIMIT,
                 "batch %lld exceeds the fixed scratch of the allocation-free entry point (at most %d rows per "

@@ -223,8 +223,8 @@ fc_tail_f32(const float* __restrict__ ws, int M,
   pdl_wait();
   if (m >= M) {              // one extra CTA when ring slots have to be released: the fc1 kernel (their only reader)
     const int msgs = (M + span.rows_per_msg - 1) / span.rows_per_msg;      // has completed -- the wait above waited for that
-    if (tid < msgs) {
-      const int slot = span_slot(span, tid);
+    for (int i = tid; i < msgs; i += blockDim.x) {      // a ring may hold up to 1024 slots: more messages than threads
+      const int slot = span_slot(span, i);
       const unsigned long long k = ld_count(span.count + slot) + 1;
       span.count[slot] = k;
       st_relaxed_sys(span.released + slot, k);    // nothing to publish but "my reads are over"

@@ -104,9 +104,24 @@ inline std::atomic<int>& pdl_switch() {
   }()};
   return on;
 }
+// Per-call override (b2p_stage_set_pdl): every stage entry point installs its stage's mask for the duration of the
+// call on the calling thread, so two pipelines in one process -- or two threads -- never see each other's setting.
+// -1: no override, the process-wide default above applies.
+inline int& pdl_call_mask() {
+  static thread_local int m = -1;
+  return m;
+}
+struct PdlScope {
+  int prev;
+  explicit PdlScope(int mask) : prev(pdl_call_mask()) { if (mask >= 0) pdl_call_mask() = mask & 3; }
+  ~PdlScope() { pdl_call_mask() = prev; }
+};
 // bit 0: the light kernel chains (GEMMs, LayerNorm, attention, fc tail, splits); bit 1: the CIFAR part-0
 // kernel, whose CTAs each take a whole SM's shared memory while they wait.
-inline bool pdl_enabled(int bit = 1) { return (pdl_switch().load(std::memory_order_relaxed) & bit) != 0; }
+inline bool pdl_enabled(int bit = 1) {
+  const int call = pdl_call_mask();
+  return ((call >= 0 ? call : pdl_switch().load(std::memory_order_relaxed)) & bit) != 0;
+}
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl_bit(int bit, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
@@ -149,6 +164,16 @@ struct DeviceGuard {
 };
 
 inline int ceil_div(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// ---- device-side wait policy -----------------------------------------------------------------
+// Every wait a kernel of this library performs on something ANOTHER kernel or GPU has to do (a handoff-ring flag,
+// ring_hooks.cuh) gives up after g_wait_limit_ns: it records what it was waiting for in g_ring_error, returns, and
+// from then on every ring wait on this GPU returns at once, so the stage kernels drain (with meaningless results)
+// instead of hanging or killing the context.  The host reads and clears the record with b2p_ring_check().
+// 0 = wait for ever (a serving process whose front door may sit idle).  Waits on the kernel's OWN pipeline
+// (mbarriers) can only fail through a protocol bug; they trap, 10 s after the ring limit, and never when it is 0.
+__device__ unsigned long long g_wait_limit_ns = 20000000000ull;
+__device__ unsigned long long g_ring_error[4];   // [0] 0 = clean, else 1 + wait kind; [1] flag address; [2] target; [3] last value seen
 
 // ---- device helpers ----------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -87,6 +87,9 @@ ring_copy(uint4* __restrict__ dst, const uint4* __restrict__ src, size_t n16, un
   if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
 }
 
+// the GPU whose stream runs this side's handshake kernels: the consumer's for the owning side, else the producer's
+inline int ring_side_device(const b2p_ring* r) { return r->owner ? r->consumer_dev : r->producer_dev; }
+
 inline unsigned long long* published(b2p_ring* r, uint64_t seq) { return r->flags + (seq % r->slots); }
 inline unsigned long long* released(b2p_ring* r, uint64_t seq) { return r->flags + r->slots + (seq % r->slots); }
 
@@ -120,8 +123,12 @@ int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes) {
   const size_t flag_bytes = ((size_t)2 * slots * sizeof(unsigned long long) + 255) & ~size_t(255);
   void* base = nullptr;
   B2P_CUDA(cudaMalloc(&base, flag_bytes + slot_pad * slots));
-  B2P_CUDA(cudaMemset(base, 0, flag_bytes));
-  B2P_CUDA(cudaDeviceSynchronize());
+  cudaError_t ce0 = cudaMemset(base, 0, flag_bytes);
+  if (ce0 == cudaSuccess) ce0 = cudaDeviceSynchronize();
+  if (ce0 != cudaSuccess) {
+    cudaFree(base);
+    return fail(B2P_ECUDA, "ring: clearing the flags failed: %s", cudaGetErrorString(ce0));
+  }
   b2p_ring* r = new b2p_ring();
   r->consumer_dev = device;
   r->slots = slots;
@@ -133,12 +140,13 @@ int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes) {
   cudaError_t ce = cudaMalloc((void**)&r->local_count, (3 * slots + 4) * sizeof(unsigned long long));
   if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (3 * slots + 4) * sizeof(unsigned long long));
   r->ticket = reinterpret_cast<int*>(r->local_count + slots);
+  if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
   if (ce != cudaSuccess) {
+    cudaFree(r->local_count);
     cudaFree(base);
     delete r;
     return fail(B2P_ECUDA, "ring: counter allocation failed: %s", cudaGetErrorString(ce));
   }
-  B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
   return 0;
 }
@@ -180,10 +188,16 @@ int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device) {
   r->flags = static_cast<unsigned long long*>(base);
   r->data = static_cast<unsigned char*>(base) + flag_bytes;
   r->ipc = true;
-  B2P_CUDA(cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long)));
-  B2P_CUDA(cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long)));
+  cudaError_t ce = cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long));
+  if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long));
+  if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
+  if (ce != cudaSuccess) {
+    cudaFree(r->local_count);
+    cudaIpcCloseMemHandle(base);
+    delete r;
+    return fail(B2P_ECUDA, "ring: counter allocation failed: %s", cudaGetErrorString(ce));
+  }
   r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
-  B2P_CUDA(cudaDeviceSynchronize());
   *out = r;
   return 0;
 }
@@ -209,10 +223,15 @@ int b2p_ring_open_local(b2p_ring** out, b2p_ring* consumer_side, int producer_de
   r->ticket = nullptr;
   {
     DeviceGuard g(producer_device);
-    B2P_CUDA(cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long)));
-    B2P_CUDA(cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long)));
+    cudaError_t ce = cudaMalloc((void**)&r->local_count, (3 * r->slots + 4) * sizeof(unsigned long long));
+    if (ce == cudaSuccess) ce = cudaMemset(r->local_count, 0, (3 * r->slots + 4) * sizeof(unsigned long long));
+    if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
+    if (ce != cudaSuccess) {
+      cudaFree(r->local_count);
+      delete r;
+      return fail(B2P_ECUDA, "ring: counter allocation failed: %s", cudaGetErrorString(ce));
+    }
     r->ticket = reinterpret_cast<int*>(r->local_count + r->slots);
-    B2P_CUDA(cudaDeviceSynchronize());
   }
   *out = r;
   return 0;
@@ -233,6 +252,31 @@ int b2p_ring_destroy(b2p_ring* ring) {
   return 0;
 }
 
+int b2p_ring_set_timeout(int device, double seconds) {
+  using namespace b2p;
+  if (!(seconds >= 0.0) || seconds > 1e6) return fail(B2P_EINVAL, "ring: time-out must be 0 (wait for ever) .. 1e6 seconds");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2P_ECUDA, "ring: device %d not present", device);
+  const unsigned long long ns = (unsigned long long)(seconds * 1e9);
+  B2P_CUDA(cudaMemcpyToSymbol(g_wait_limit_ns, &ns, sizeof(ns)));
+  return 0;
+}
+
+int b2p_ring_check(int device) {
+  using namespace b2p;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(B2P_ECUDA, "ring: device %d not present", device);
+  unsigned long long rec[4] = {0, 0, 0, 0};
+  B2P_CUDA(cudaMemcpyFromSymbol(rec, g_ring_error, sizeof(rec)));
+  if (rec[0] == 0) return 0;
+  const unsigned long long zero[4] = {0, 0, 0, 0};
+  B2P_CUDA(cudaMemcpyToSymbol(g_ring_error, zero, sizeof(zero)));
+  return fail(B2P_ETIMEOUT,
+              "ring: a device-side wait on GPU %d gave up (%s flag at %#llx: waited for %llu, last saw %llu); results of "
+              "the steps enqueued since are invalid -- the peer stage stalled for longer than the ring time-out",
+              device, rec[0] == 2 ? "remote `released`" : "local `published`/`released`", rec[1], rec[2], rec[3]);
+}
+
 int b2p_ring_set_mode(b2p_ring* ring, int mode) {
   if (!ring || mode < 0 || mode > 1) return b2p::fail(B2P_EINVAL, "ring: mode must be 0 (copy engine) or 1 (SM copy kernel)");
   ring->mode = mode;
@@ -242,6 +286,7 @@ int b2p_ring_set_mode(b2p_ring* ring, int mode) {
 int b2p_ring_acquire(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream) {
   using namespace b2p;
   if (!ring || !slot_dev) return fail(B2P_EINVAL, "null argument");
+  DeviceGuard g(ring_side_device(ring));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   B2P_LAUNCH(ring_acquire_k, 1, 1, 0, s, ring->local_count + (seq % ring->slots), released(ring, seq));
   *slot_dev = ring->data + (seq % ring->slots) * ring->slot_bytes;
@@ -251,6 +296,7 @@ int b2p_ring_acquire(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream
 int b2p_ring_publish(b2p_ring* ring, uint64_t seq, void* stream) {
   using namespace b2p;
   if (!ring) return fail(B2P_EINVAL, "null argument");
+  DeviceGuard g(ring_side_device(ring));
   B2P_LAUNCH(ring_publish_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
              published(ring, seq));
   return 0;
@@ -261,6 +307,7 @@ int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uint64_t se
   if (!ring || !src_dev) return fail(B2P_EINVAL, "null argument");
   if (bytes > ring->slot_bytes) return fail(B2P_ELIMIT, "ring: message of %zu bytes exceeds the slot size %zu", bytes, ring->slot_bytes);
   void* slot = nullptr;
+  DeviceGuard g(ring_side_device(ring));
   B2P_TRY(b2p_ring_acquire(ring, seq, &slot, stream));
   B2P_TRY(ring_copy_into(ring, slot, src_dev, bytes, static_cast<cudaStream_t>(stream)));
   return b2p_ring_publish(ring, seq, stream);
@@ -269,6 +316,7 @@ int b2p_ring_send(b2p_ring* ring, const void* src_dev, size_t bytes, uint64_t se
 int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream) {
   using namespace b2p;
   if (!ring || !slot_dev) return fail(B2P_EINVAL, "null argument");
+  DeviceGuard g(ring_side_device(ring));
   B2P_LAUNCH(ring_recv_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
              published(ring, seq));
   *slot_dev = ring->data + (seq % ring->slots) * ring->slot_bytes;
@@ -278,6 +326,7 @@ int b2p_ring_recv(b2p_ring* ring, uint64_t seq, void** slot_dev, void* stream) {
 int b2p_ring_release(b2p_ring* ring, uint64_t seq, void* stream) {
   using namespace b2p;
   if (!ring) return fail(B2P_EINVAL, "null argument");
+  DeviceGuard g(ring_side_device(ring));
   B2P_LAUNCH(ring_release_k, 1, 1, 0, static_cast<cudaStream_t>(stream), ring->local_count + (seq % ring->slots),
              released(ring, seq));
   return 0;

@@ -13,6 +13,8 @@
 #pragma once
 #include <cstdint>
 
+#include "common.cuh"
+
 namespace b2p {
 
 struct RingHook {                  // all null: no ring on this side
@@ -46,29 +48,53 @@ __device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long
 __device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+// A wait that has run out of time (g_wait_limit_ns, common.cuh) records itself -- first one wins -- and returns; once
+// a record exists every later ring wait on this GPU returns immediately.  No trap: a trap is a sticky context error
+// that takes every stage, ring and graph of the process with it, and the peer rank soon after.
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool ring_gave_up() { return ld_volatile_u64(&g_ring_error[0]) != 0ull; }
+__device__ __noinline__ void ring_wait_timed_out(const unsigned long long* flag, unsigned long long target,
+                                                 unsigned long long seen, int kind) {
+  if (atomicCAS(&g_ring_error[0], 0ull, (unsigned long long)(kind + 1)) == 0ull) {
+    g_ring_error[1] = (unsigned long long)(uintptr_t)flag;
+    g_ring_error[2] = target;
+    g_ring_error[3] = seen;
+    __threadfence_system();
+  }
+}
 // Measured on 2 x B200: a system-scope fence costs ~2.5 us when peer traffic is outstanding, so the hooks use as few
 // as the memory model allows and keep them off the critical path where they can.
 // Flag in LOCAL memory (the consumer waiting for `published`): acquire loads.
 __device__ __forceinline__ void spin_until_ge(const unsigned long long* flag, unsigned long long target) {
   if (ld_acquire_sys(flag) >= target) return;
   const uint64_t t0 = hook_ns();
+  const unsigned long long limit = ld_volatile_u64(&g_wait_limit_ns);
   unsigned ns = 32;
-  while (ld_acquire_sys(flag) < target) {           // one thread; traps after 20 s instead of hanging
+  unsigned long long v;
+  while ((v = ld_acquire_sys(flag)) < target) {     // one thread; gives up after the limit instead of hanging
     __nanosleep(ns);
     if (ns < 1024) ns *= 2;
-    if (hook_ns() - t0 > 20000000000ull) __trap();
+    if (ring_gave_up()) return;
+    if (limit && hook_ns() - t0 > limit) { ring_wait_timed_out(flag, target, v, 0); return; }
   }
 }
 // Flag on ANOTHER GPU (the producer waiting for `released`): every poll is an NVLink round trip, so poll relaxed
 // and pay for the acquire once, after the value has been seen.
 __device__ __forceinline__ void spin_until_ge_remote(const unsigned long long* flag, unsigned long long target) {
-  if (ld_relaxed_sys(flag) < target) {
+  unsigned long long v;
+  if ((v = ld_relaxed_sys(flag)) < target) {
     const uint64_t t0 = hook_ns();
+    const unsigned long long limit = ld_volatile_u64(&g_wait_limit_ns);
     unsigned ns = 64;
-    while (ld_relaxed_sys(flag) < target) {
+    while ((v = ld_relaxed_sys(flag)) < target) {
       __nanosleep(ns);
       if (ns < 1024) ns *= 2;
-      if (hook_ns() - t0 > 20000000000ull) __trap();
+      if (ring_gave_up()) break;
+      if (limit && hook_ns() - t0 > limit) { ring_wait_timed_out(flag, target, v, 1); break; }
     }
   }
   asm volatile("fence.acq_rel.sys;" ::: "memory");

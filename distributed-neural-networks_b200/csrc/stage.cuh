@@ -29,6 +29,7 @@ struct b2p_stage {
   b2p_stage_desc d{};
   std::vector<b2p_weight> w;
   bool finalized = false;
+  int pdl_mask = -1;                // b2p_stage_set_pdl: -1 = the process-wide default (b2p_set_pdl)
 
   // ---- CIFAR part 0 ----
   float* w1t = nullptr;             // [27][32]

@@ -78,7 +78,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint64_t t0 = global_ns();
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 0x3FF) == 0 && global_ns() - t0 > 4000000000ull) __trap();   // 4 s: no legitimate wait is this long
+    if ((++spins & 0x3FF) == 0) {
+      // A role of a ring-fed kernel may legitimately sit here for as long as the ring wait it depends on (which gives
+      // up by itself, common.cuh); beyond that only a protocol bug keeps a barrier closed: trap rather than hang.
+      unsigned long long limit;
+      asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(limit) : "l"(&g_wait_limit_ns) : "memory");
+      if (limit && global_ns() - t0 > limit + 10000000000ull) __trap();
+    }
   }
 }
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0,

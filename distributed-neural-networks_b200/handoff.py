@@ -76,3 +76,16 @@ class Ring:
             self.close()
         except Exception:
             pass
+
+
+def set_timeout(device: int, seconds: float):
+    """How long a device-side ring wait on GPU ``device`` waits before it gives up (default 20 s; 0 = for ever, for a
+    serving process whose front door may idle).  b2p_ring_set_timeout."""
+    _lib.check(_lib.lib().b2p_ring_set_timeout(device, float(seconds)))
+
+
+def check(device: int):
+    """Raises ``EngineError`` (code ETIMEOUT) when a ring wait on GPU ``device`` has given up since the last check:
+    the steps enqueued since then produced meaningless results.  Nothing trapped -- stages, rings and graphs stay
+    usable.  b2p_ring_check."""
+    _lib.check(_lib.lib().b2p_ring_check(device))

@@ -59,6 +59,8 @@ class LocalPipeline:
         self._consumed = [dict() for _ in hidden_shapes]
         for s in stages:
             s._finalize()
+            if getattr(s, "WHOLE_BATCH_OK", False):
+                s.reserve(self.max_batch)          # no forward of this pipeline allocates (graph capture, serving)
         # CUDA graphs of the whole device-resident schedule, keyed by (input address, batch, seq)
         self._graphs: dict = {}
         self.graph_kernel_launches = 0      # kernels executed through graph replays (for accounting)
@@ -83,16 +85,16 @@ class LocalPipeline:
             # same per-row arithmetic (fixed K slicing), bit-identical results, an eighth of the launches.
             s = self.compute[0]
             self._joined = []                  # no other stream took part (run_device_graph joins nothing)
-            prev = _lib.lib().b2p_set_pdl(3)
             src = x
             for k, st in enumerate(self.stages):
                 dst = out[:b] if k == n_st - 1 else self.hidden[k][:b]
+                st.set_pdl(3)                       # per stage, not process-wide: other pipelines keep their own setting
                 st.forward_ptr(src.data_ptr(), dst.data_ptr(), b, seq, s.cuda_stream)
                 src = dst
-            _lib.lib().b2p_set_pdl(prev)
             return out[:b]
         self._joined = self.compute[1:]
-        prev_pdl = _lib.lib().b2p_set_pdl(3 if self._pdl else 0)    # shared GPU: no early starts (measured: 0.199 vs 0.238 ms/step)
+        for st in self.stages:
+            st.set_pdl(3 if self._pdl else 0)       # shared GPU: no early starts (measured: 0.199 vs 0.238 ms/step)
         for i, lo in enumerate(range(0, b, self.mb)):
             n = min(self.mb, b - lo)
             src = x[lo:lo + n]
@@ -117,7 +119,6 @@ class LocalPipeline:
                     prev_done = torch.cuda.Event()
                     prev_done.record(s)
                     src = self.hidden[k][lo:lo + n]
-        _lib.lib().b2p_set_pdl(prev_pdl)
         return out[:b]
 
     # -- the same schedule as one CUDA graph ---------------------------------------------------

@@ -179,6 +179,18 @@ class EngineStage(nn.Module):
             self._handle, C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), batch, seq, C.c_void_p(stream)))
         return out
 
+    def reserve(self, batch: int, seq: int = 1):
+        """Size the batch-dependent scratch for forwards of up to ``batch`` rows (b2p_stage_reserve): afterwards no
+        forward of that size allocates, so the schedule can be captured in a CUDA graph.  Start-up call."""
+        self._require_device()
+        self._finalize()
+        _lib.check(_lib.lib().b2p_stage_reserve(self._handle, batch, seq))
+
+    def set_pdl(self, mask: int):
+        """Programmatic-dependent-launch mask of THIS stage's kernels (b2p_stage_set_pdl); -1 = process default."""
+        self._require_device()
+        return _lib.lib().b2p_stage_set_pdl(self._handle, mask)
+
     # raw-pointer entry for the pipeline scheduler (no tensor allocation, no checks)
     def forward_ptr(self, in_ptr: int, out_ptr: int, batch: int, seq: int, stream: int):
         _lib.check(_lib.lib().b2p_stage_forward(
@@ -334,6 +346,7 @@ class _GptPart(EngineStage):
         self._require_device()
         self._finalize()
         _lib.check(_lib.lib().b2p_stage_kv_reset(self._handle, batch))
+        self._kv_batch = int(batch)
 
     def forward_kv(self, x, pos0: int, want_ids: bool = False):
         """The ``x.shape[1]`` NEW positions pos0.. of every sequence: pos0 == 0 is the prefill, afterwards one position
@@ -343,6 +356,8 @@ class _GptPart(EngineStage):
         first = self.KIND == _lib.GPT_FIRST
         x = self._prepare_input(x, torch.int64 if first else torch.float32)
         b, t = x.shape[0], x.shape[1]
+        if pos0 > 0 and b * t > self.max_tokens:
+            raise RuntimeError("forward_kv: the workspace cannot grow after the prefill (the cache would be lost)")
         self._ensure_capacity(b * t)
         self._finalize()
         stream = torch.cuda.current_stream(self._device).cuda_stream
@@ -387,13 +402,18 @@ class _GptPart(EngineStage):
         return d
 
     def _ensure_capacity(self, tokens: int):
-        """Workspaces are sized at stage creation; grow by re-creating the stage."""
+        """Workspaces are sized at stage creation; grow by re-creating the stage.  The re-created stage has no KV
+        cache, so a cache sized by an earlier ``kv_reset`` is sized again (its contents are gone: growing is only
+        legal before the prefill, which is the only forward_kv call that can carry more tokens than any before)."""
         if tokens > self.max_tokens:
             self.max_tokens = tokens
             if self._handle is not None:
                 dev = self._device
                 self._release()
                 self.to(dev)
+                kvb = getattr(self, "_kv_batch", 0)
+                if kvb:
+                    self.kv_reset(kvb)
 
     def _check_hidden(self, x):
         c = self.config.n_embd
@@ -506,6 +526,7 @@ def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True):
     done = 0
     if kv_cache and idx.shape[1] < block_size and max_new_tokens > 0:
         for p in parts:
+            p._ensure_capacity(idx.shape[0] * idx.shape[1])   # grow BEFORE the cache exists (re-creating a stage drops it)
             p.kv_reset(idx.shape[0])
         nxt = chain(idx, 0)                                   # prefill
         idx = torch.cat([idx, nxt], dim=1)

@@ -21,7 +21,11 @@
  *   - the caller owns all input/output DEVICE buffers; the library owns weights,
  *     workspaces and handoff rings;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
- *     calls only enqueue work, they never synchronise unless stated;
+ *     calls only enqueue work, they never synchronise unless stated.  The forward calls
+ *     allocate nothing as long as the batch stays within what b2p_stage_finalize /
+ *     b2p_stage_reserve sized (see b2p_stage_reserve); a larger batch grows the scratch
+ *     on the spot, which synchronises the device and is refused (B2P_ESTATE) while the
+ *     stream is being captured;
  *   - there is NO CPU fallback: without a CUDA device every compute call fails
  *     with B2P_ECUDA.
  */
@@ -50,6 +54,7 @@ extern "C" {
 #define B2P_ESTATE   -3   /* call out of order (e.g. forward before finalize)    */
 #define B2P_EMISSING -4   /* finalize: a required weight was never loaded        */
 #define B2P_ELIMIT   -5   /* size beyond a documented maximum                    */
+#define B2P_ETIMEOUT -6   /* a device-side ring wait gave up (b2p_ring_check)    */
 
 /* stage kinds: one per reference part class */
 #define B2P_CIFAR_PART0   0   /* ModelPart0_2Node   cifar_model_parts.py:29-42   */
@@ -82,7 +87,7 @@ typedef struct b2p_stage_desc {
   int32_t start_layer;   /* GPT: first global block index of this stage           */
   int32_t end_layer;     /* GPT: last global block index (inclusive)              */
   int32_t n_head;        /* GPT                                                   */
-  int32_t n_embd;        /* GPT: C, multiple of 64, head dim must be 64           */
+  int32_t n_embd;        /* GPT: C, multiple of 128 (at most 2048), head dim 64   */
   int32_t vocab_size;    /* GPT first/final                                       */
   int32_t block_size;    /* GPT: max T (gpt_model_parts.py:15 assert)             */
   int32_t max_tokens;    /* GPT: largest B*T one forward() will carry (workspace) */
@@ -99,7 +104,10 @@ B2P_API int64_t     b2p_launch_count(void);
 /* Programmatic dependent launch (overlap each kernel's prologue with its predecessor's tail).
  * mask bit 0: the light kernel chains (GEMMs, LayerNorm, attention, fc tail); bit 1: the CIFAR
  * part-0 kernel, whose waiting CTAs each hold a whole SM -- clear it when two stages share one
- * GPU on two streams.  Default 3.  Returns the previous mask.  Process-wide. */
+ * GPU on two streams.  Default 3.  Returns the previous mask.
+ * b2p_set_pdl sets the process-wide DEFAULT; b2p_stage_set_pdl sets it for one stage (mask < 0:
+ * back to the default) and is what a scheduler should use -- two pipelines, or two threads, in
+ * one process then never see each other's setting. */
 B2P_API int b2p_set_pdl(int mask);
 
 /* ---- stage lifecycle (seam 1; node.py:300-317) ------------------------------- */
@@ -122,6 +130,15 @@ B2P_API int b2p_stage_missing(b2p_stage* st, char* names_buf, size_t buf_len);
 /* Pack weights for the selected math mode (bf16 copies, tf32 hi/lo planes,
  * transposes).  Must be called once after loading, before forward. */
 B2P_API int b2p_stage_finalize(b2p_stage* st);
+
+/* Size the stage's batch-dependent scratch (fc1 split-K partial sums, hi/lo planes of the
+ * 3xTF32 GEMM operands, arg-max partials of the fused LM head) for forwards of up to `batch`
+ * rows (GPT: batch*seq tokens, at most max_tokens).  finalize already does this for 1024 rows
+ * (CIFAR) / max_tokens (GPT); call reserve when larger batches will come, at start-up, NOT on
+ * the serving path and not inside a stream capture: it may cudaFree/cudaMalloc (device-wide
+ * synchronisation).  After it, no forward of that size or smaller allocates. */
+B2P_API int b2p_stage_reserve(b2p_stage* st, int64_t batch, int64_t seq);
+B2P_API int b2p_stage_set_pdl(b2p_stage* st, int mask);
 
 /* Output element count for a given input geometry (host helper). */
 B2P_API int b2p_stage_out_elems(b2p_stage* st, int64_t batch, int64_t seq, int64_t* elems);
@@ -212,7 +229,16 @@ B2P_API int b2p_split_tf32(const float* x_dev, float* hi_dev, float* lo_dev, int
  *     from an earlier call are harmless (every value read is first rewritten);
  *   - the first call on each GPU looks the array's device address up once
  *     (cudaGetSymbolAddress); make that first call before starting any stream
- *     capture on that GPU. */
+ *     capture on that GPU;
+ *   - "allocates nothing" holds from a GPU's SECOND call on.  With CUDA's default lazy
+ *     module loading the very first use of this library on a GPU (this call, or any
+ *     other) loads the library image there, which is when the driver sets the 4 MiB
+ *     array aside -- an implicit allocation plus a synchronisation.  So make one call
+ *     per GPU at start-up, off the latency-critical thread and BEFORE the host's own
+ *     pool claims the remaining memory (or run with CUDA_MODULE_LOADING=EAGER);
+ *     otherwise that first call can fail with B2P_ECUDA for lack of memory;
+ *   - the cached address does not survive cudaDeviceReset(): a process that resets a
+ *     device must not call this entry point on it again. */
 #define B2P_NOALLOC_MAX_BATCH 256
 B2P_API int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* fc1_weight_dev,
                                             const float* fc1_bias_dev, const float* fc2_weight_dev,
@@ -224,9 +250,19 @@ B2P_API int b2p_cifar_part1_forward_noalloc(const float* x_dev, const float* fc1
  * GPU plus two 64-bit sequence flags per slot (full / free).  The consumer
  * process creates it, exports an opaque handle (CUDA IPC), and the producer
  * process opens it; inside one process ring_open_local() skips IPC.  Data moves
- * with one device-to-device copy over NVLink; signalling is done with stream
- * memory operations, so neither side ever blocks the host. */
+ * with one device-to-device copy over NVLink (or rides on the producing kernel's own
+ * stores); signalling is done on the device, by one-thread kernels on the caller's
+ * stream or inside the stage kernels, so neither side ever blocks the host.
+ *
+ * Device-side waits give up after a time-out (default 20 s) instead of hanging: the wait
+ * records what it was waiting for, every later ring wait on that GPU returns at once, the
+ * enqueued kernels drain with meaningless results, and b2p_ring_check reports
+ * B2P_ETIMEOUT (and clears the record).  Nothing traps, so the context, the stages and
+ * the rings stay usable.  b2p_ring_set_timeout(device, 0) waits for ever -- for a serving
+ * process whose front door may sit idle between requests. */
 #define B2P_RING_HANDLE_BYTES 256
+B2P_API int b2p_ring_set_timeout(int device, double seconds);   /* per GPU; 0 = no time-out */
+B2P_API int b2p_ring_check(int device);                         /* synchronous read of the GPU's time-out record */
 B2P_API int b2p_ring_create(b2p_ring** out, int device, int slots, size_t slot_bytes);
 B2P_API int b2p_ring_export(b2p_ring* ring, void* handle_out /* B2P_RING_HANDLE_BYTES */);
 B2P_API int b2p_ring_open(b2p_ring** out, const void* handle, int producer_device);

@@ -46,8 +46,10 @@ PARTS = {0: cifar_oracle.part0, 1: cifar_oracle.part1}        # node.py:29-32
 
 
 def _wire():
-    import dnn_b200
-    return dnn_b200.wire
+    """The oracle's OWN messages and stub (oracle/node_wire.py): the reference's gencode when oracle/_ref/ holds
+    it, else a protobuf-runtime restatement -- never the product's dnn_b200.wire."""
+    from oracle import node_wire
+    return node_wire
 
 
 class NodeOracle:
@@ -133,11 +135,25 @@ def _free_port():
     return p
 
 
-class TwoNodePipeline:
-    """Context manager: two node_oracle processes on 127.0.0.1 + a blocking stub."""
+def reference_available() -> bool:
+    """True when oracle/_ref/ holds the unmodified reference node program (oracle/build_ref.py)."""
+    from oracle import build_ref
+    return build_ref.available()
 
-    def __init__(self, sd, threads: int | None = None):
+
+class TwoNodePipeline:
+    """Context manager: a two-node localhost pipeline + a blocking stub.
+
+    impl = "reference": two processes of the UNMODIFIED reference ``node.py`` from oracle/_ref/ (CUDA hidden from
+                        them, so DEVICE resolves to "cpu", node.py:25) -- cpu_baseline.kind "reference";
+    impl = "port":      two processes of this file's restatement -- cpu_baseline.kind "port";
+    impl = None:        the reference when oracle/_ref/ is there, else the port.  ``self.kind`` says which ran."""
+
+    def __init__(self, sd, threads: int | None = None, impl: str | None = None):
         self.sd, self.threads = sd, threads
+        self.kind = impl or ("reference" if reference_available() else "port")
+        if self.kind == "reference" and not reference_available():
+            raise RuntimeError("oracle/_ref/ is not populated (run oracle/build_ref.py where /root/reference exists)")
         self.procs = []
 
     def __enter__(self):
@@ -159,10 +175,17 @@ class TwoNodePipeline:
             # run with torch's default threading (all cores), so do not let that leak in
             env.pop("OMP_NUM_THREADS", None)
             env.pop("MKL_NUM_THREADS", None)
+        if self.kind == "reference":
+            ref_dir = os.path.join(ROOT, "oracle", "_ref")
+            env["CUDA_VISIBLE_DEVICES"] = ""          # the CPU baseline: node.py:25 picks "cuda" when it sees one
+            cmd = lambda nid: [sys.executable, os.path.join(ref_dir, "node.py"), "--node_id", nid, "--config", cpath]
+            cwd = ref_dir
+        else:
+            cmd = lambda nid: [sys.executable, "-m", "oracle.node_oracle", "--node_id", nid, "--config", cpath]
+            cwd = ROOT
         for nid in ("node2", "node1"):
-            self.procs.append(subprocess.Popen(
-                [sys.executable, "-m", "oracle.node_oracle", "--node_id", nid, "--config", cpath],
-                cwd=ROOT, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL))
+            self.procs.append(subprocess.Popen(cmd(nid), cwd=cwd, env=env, stdout=subprocess.DEVNULL,
+                                               stderr=subprocess.DEVNULL))
         self.channel = grpc.insecure_channel(f"127.0.0.1:{p1}")
         grpc.channel_ready_future(self.channel).result(timeout=180)
         self.stub = _wire().NodeServiceStub(self.channel)
@@ -179,10 +202,13 @@ class TwoNodePipeline:
 
     def request(self, x: np.ndarray, request_id: str = "req"):
         w = _wire()
-        rep = self.stub.SendTensor(w.TensorRequest(request_id=request_id, tensor=w.ndarray_to_tensor(x)))
+        x = np.ascontiguousarray(x)                              # the client of node.py:172-189
+        rep = self.stub.SendTensor(w.TensorRequest(request_id=request_id, tensor=w.Tensor(
+            tensor_data=x.tobytes(), shape=list(x.shape), dtype=str(x.dtype))))
         if not rep.HasField("result_tensor"):
             return None, rep.status
-        return w.tensor_to_ndarray(rep.result_tensor).copy(), rep.status
+        t = rep.result_tensor
+        return np.frombuffer(t.tensor_data, dtype=np.dtype(t.dtype)).reshape(tuple(t.shape)).copy(), rep.status
 
     def __exit__(self, *exc):
         self.channel.close()

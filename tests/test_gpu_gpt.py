@@ -295,3 +295,102 @@ def test_kv_cache_steps_equal_the_full_forward(cuda_engine, math, tol):
         with pytest.raises(L.EngineError, match="beyond block_size"):
             parts[0].forward_kv(idx[:, :1], 80)
 
+
+def test_default_max_tokens_with_a_batched_prompt_longer_than_block_size_in_total(cuda_engine):
+    """max_tokens left at its default (block_size) while B*T0 > block_size: the workspace has to grow BEFORE the KV
+    cache is sized -- re-creating the stage afterwards would drop the cache."""
+    cfg = gpt_model.GPTConfig(block_size=32, vocab_size=97, n_layer=2, n_head=2, n_embd=128)
+    sd = gpt_oracle.init_state_dict(cfg, seed=3)
+    for k in sd:
+        if k.endswith("weight") and "ln_" not in k and "wte" not in k and "wpe" not in k and "lm_head" not in k:
+            sd[k] = sd[k] * 12
+    model = cuda_engine.GPT(cuda_engine.GPTConfig(block_size=32, vocab_size=97, n_layer=2, n_head=2, n_embd=128))
+    model.load_state_dict(sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math="fp32")]      # max_tokens = 32
+    prompt = gpt_oracle.make_tokens(4, 20, cfg.vocab_size, seed=1)                                   # 80 tokens > 32
+    want, gaps = gpt_oracle.greedy_generate(prompt, sd, cfg, 2, 6)
+    got = cuda_engine.greedy_generate(parts, prompt, 6, kv_cache=True).cpu()
+    assert got.shape == want.shape
+    for b in range(4):
+        for t in range(6):
+            if gaps[b, t] <= 10 * TIE:
+                break
+            assert got[b, 20 + t] == want[b, 20 + t]
+    # forward_kv alone, re-creating the stage at the prefill: the cache is sized again, not lost
+    parts2 = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math="fp32")]
+    for p in parts2:
+        p.kv_reset(4)
+    x = prompt.cuda()
+    with torch.no_grad():
+        for p in parts2:
+            x = p.forward_kv(x, 0)
+    assert x.shape == (4, 20, 97)
+
+
+# ---- BASELINE configs 3 and 4 at their own geometry -------------------------------------------------------------
+# The CPU oracle cannot run 12 / 24 layers at T=1024 in test time, so each test builds ONE stage of the config as
+# BASELINE states it (same C, H, T, vocabulary, blocks per stage) over a short model and feeds it a seeded input:
+# token ids for a first stage, a seeded hidden state (or the oracle's output of the stage before) for the others.
+# B = 2 sequences of T = 1024: the 128-row query tiles and 64-row key tiles then cross the sequence boundary inside
+# one launch, which a single sequence never exercises.
+def _check_logits(got, want, tol, what):
+    err = (got - want).abs().max().item()
+    top2 = want.topk(2, -1).values
+    decided = (top2[..., 0] - top2[..., 1]) > 2 * tol
+    flips = int((got.argmax(-1)[decided] != want.argmax(-1)[decided]).sum())
+    print(f"\n{what}: max|dlogit|={err:.3e}; decided {int(decided.sum())}/{decided.numel()} positions, flips {flips}")
+    assert err <= tol
+    assert flips == 0
+
+
+@pytest.mark.parametrize("mode,tol_h,tol_l", [("bf16", 5e-2, 5e-2), ("tf32x3", 2e-4, 2e-4)])
+def test_gpt2_medium_stage_geometry(cuda_engine, mode, tol_h, tol_l):
+    """BASELINE config 4 (gpt_model_parts.py:26-50): a 3-block ModelPartIntermediate and a ModelPartFinal_GPT with the
+    50 257-way head at C=1024, H=16, T=1024, microbatch of 2 sequences, bf16 (the config's dtype) and tf32x3."""
+    C_, H_, T_, V_ = 1024, 16, 1024, 50257
+    cfg = gpt_model.GPTConfig(block_size=T_, vocab_size=V_, n_layer=4, n_head=H_, n_embd=C_)
+    sd = gpt_oracle.init_state_dict(cfg, seed=31)
+    g = torch.Generator().manual_seed(17)
+    for k in sd:                                # non-trivial biases / LayerNorm parameters
+        if k.endswith("bias") or "ln_" in k:
+            sd[k] = sd[k] + 0.05 * torch.randn(sd[k].shape, generator=g)
+    model = _engine_model(cuda_engine, (T_, V_, 4, H_, C_), sd)
+    mid = cuda_engine.ModelPartIntermediate(model, 0, 2, math=mode, max_tokens=2 * T_).to("cuda:0").eval()
+    last = cuda_engine.ModelPartFinal_GPT(model, 3, 3, math=mode, max_tokens=2 * T_).to("cuda:0").eval()
+    x = 0.5 * torch.randn(2, T_, C_, generator=g)
+    want_h = gpt_oracle.part_middle(x, sd, 0, 2, H_)
+    want_l = gpt_oracle.part_final(want_h, sd, 3, 3, H_)
+    with torch.no_grad():
+        got_h = mid(x.cuda())
+        got_l = last(want_h.cuda())             # fed the oracle's hidden state: stage errors do not compound
+        ids = last.greedy_ids(want_h.cuda())
+        chained = last(got_h)                   # and the two engine stages chained, as the pipeline runs them
+    err_h = (got_h.cpu() - want_h).abs().max().item()
+    print(f"\ngpt2-medium geometry, {mode}: 3-block stage max|dh|={err_h:.3e} (|h| up to {want_h.abs().max():.1f})")
+    assert err_h <= tol_h
+    _check_logits(got_l.cpu(), want_l, tol_l, f"gpt2-medium final stage, {mode}")
+    assert torch.equal(ids, got_l.argmax(-1))
+    assert (chained.cpu() - want_l).abs().max().item() <= 2 * tol_l
+    # the two sequences are independent: sequence 1 alone gives the same rows (no leak across the boundary)
+    with torch.no_grad():
+        solo = mid(x[1:].cuda())
+    assert (solo - got_h[1:]).abs().max().item() <= (1e-6 if mode != "bf16" else 2e-2)
+
+
+@pytest.mark.parametrize("mode,tol", [("bf16", 5e-2), ("tf32x3", 2e-4)])
+def test_gpt2_small_geometry_batched(cuda_engine, mode, tol):
+    """BASELINE config 3 geometry (C=768, H=12, T=1024, V=50257) with B = 2: first stage (embedding + 3 blocks, the
+    config's 12 layers / 4 stages) into a final stage (1 block + ln_f + head)."""
+    cfg = gpt_model.GPTConfig(block_size=1024, vocab_size=50257, n_layer=4, n_head=12, n_embd=768)
+    sd = gpt_oracle.init_state_dict(cfg, seed=23)
+    idx = gpt_oracle.make_tokens(2, 1024, cfg.vocab_size, seed=12)
+    want_h = gpt_oracle.part_first(idx, sd, 0, 2, 12, 1024)
+    want_l = gpt_oracle.part_final(want_h, sd, 3, 3, 12)
+    model = _engine_model(cuda_engine, (1024, 50257, 4, 12, 768), sd)
+    first = cuda_engine.ModelPart0(model, 0, 2, math=mode, max_tokens=2048).to("cuda:0").eval()
+    last = cuda_engine.ModelPartFinal_GPT(model, 3, 3, math=mode, max_tokens=2048).to("cuda:0").eval()
+    with torch.no_grad():
+        got_h = first(idx.cuda())
+        got_l = last(got_h)
+    assert (got_h.cpu() - want_h).abs().max().item() <= tol
+    _check_logits(got_l.cpu(), want_l, tol if mode != "bf16" else 5e-2, f"gpt2-small B=2, {mode}")

@@ -77,3 +77,30 @@ def test_noalloc_rejects_oversized_and_bad_arguments(cuda_engine):
     assert "exceeds" in msg and str(L.NOALLOC_MAX_BATCH) in msg
     assert L.lib().b2p_cifar_part1_forward_noalloc(None, None, None, None, None, None, 1, None) == L.EINVAL
     assert _noalloc(engine, x[:0], w, out[:0]) == L.EINVAL     # empty batch: nothing to launch
+    # the kernels read x and the weights with 128-bit loads: a pointer that is not 16-byte aligned is refused
+    flat = torch.zeros(4 * 4096 + 4, device=dev)
+    skew = flat[1:1 + 4 * 4096].view(4, 4096)
+    assert skew.data_ptr() % 16 != 0
+    assert _noalloc(engine, skew, w, out[:4]) == L.EINVAL
+    assert "16-byte aligned" in L.lib().b2p_last_error().decode()
+
+
+def test_noalloc_leaves_free_device_memory_unchanged(cuda_engine):
+    """What the name promises, measured: once the GPU has seen its first call (which is when the driver loads the
+    library image and sets the fixed array aside), further calls neither take nor return device memory."""
+    engine = cuda_engine
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    sd = co.init_state_dict(1234)
+    w = {k: sd[k].to(dev).contiguous() for k in ("fc1.weight", "fc1.bias", "fc2.weight", "fc2.bias")}
+    xs = [torch.rand(b, 4096, device=dev) for b in (engine._lib.NOALLOC_MAX_BATCH, 5, 130)]
+    outs = [torch.empty(x.shape[0], 10, device=dev) for x in xs]
+    assert _noalloc(engine, xs[0], w, outs[0]) == 0             # first call on this GPU: one-time set-up
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(dev)                     # cudaMemGetInfo: driver-level, sees through torch's pool
+    for _ in range(3):
+        for x, out in zip(xs, outs):
+            assert _noalloc(engine, x, w, out) == 0
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(dev)
+    assert free1 == free0, f"free device memory moved by {free0 - free1} bytes across allocation-free calls"
