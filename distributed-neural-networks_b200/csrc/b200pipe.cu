@@ -10,6 +10,7 @@
 #include "attn_tc.cuh"
 #include "cifar_simt.cuh"
 #include "cifar_tc.cuh"
+#include "cifar_tc2.cuh"
 #include "common.cuh"
 #include "gpt_simt.cuh"
 #include "stage.cuh"
@@ -130,6 +131,11 @@ int alloc_gpt_workspace(b2p_stage* st) {
 
 const RingSpan kNoSpan{};
 
+bool part0_v1() {
+  static const bool on = [] { const char* e = getenv("B2P_PART0_V1"); return e && e[0] == '1'; }();
+  return on;
+}
+
 int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batch, cudaStream_t s,
                         RingSpan span = kNoSpan) {
   const int dev = st->d.device;
@@ -139,7 +145,10 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   if (st->d.math == B2P_MATH_FP32)
     B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
                st->dev(3), out, (int)batch);
-  else   // conv2 on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
+  else if (!part0_v1())   // both convolutions on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
+    B2P_LAUNCH_PDL_BIT(2, cifar_tc2::part0_tc2, grid, cifar_tc2::kThreads, cifar_tc2::SMEM_BYTES, s, in, st->a1img, st->w2tm,
+                       st->w2img + 8 * cifar_tc::W2_TAP_BYTES, st->dev(1), st->dev(3), out, (int)batch, st->trace, span);
+  else   // round 1's kernel (conv1 on the CUDA cores), kept for A/B measurements: B2P_PART0_V1=1
   {
     cifar_tc::Conv1Const c1;
     static_assert(sizeof(c1) == sizeof(st->w1_host), "host copy layout");
@@ -521,6 +530,8 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
                                          (int)sizeof(Part0Smem));
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(cifar_tc::part0_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, cifar_tc::SMEM_BYTES);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(cifar_tc2::part0_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, cifar_tc2::SMEM_BYTES);
     if (e != cudaSuccess) {
       b2p_stage_destroy(st);
       return fail(B2P_ECUDA, "cudaFuncSetAttribute(part0 kernels): %s", cudaGetErrorString(e));
@@ -535,7 +546,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
-  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->trace); cudaFree(st->fc_ws);
+  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->trace); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -594,6 +605,11 @@ int b2p_stage_finalize(b2p_stage* st) {
     if (st->d.math != B2P_MATH_FP32) {
       if (!st->w2img) B2P_CUDA(cudaMalloc((void**)&st->w2img, cifar_tc::W2_BYTES));
       B2P_LAUNCH(cifar_tc::pack_conv2_f16x2, ceil_div(9 * 128 * 4, 256), 256, 0, 0, st->dev(2), st->w2img);
+      if (!st->a1img) B2P_CUDA(cudaMalloc((void**)&st->a1img, 2 * cifar_tc2::PLANE_BYTES));
+      if (!st->w2tm) B2P_CUDA(cudaMalloc((void**)&st->w2tm, 128 * cifar_tc2::W2T_WORDS * sizeof(uint32_t)));
+      B2P_CUDA(cudaMemset(st->a1img, 0, 2 * cifar_tc2::PLANE_BYTES));
+      B2P_LAUNCH(cifar_tc2::pack_conv1_poolwin, ceil_div(128 * 64, 256), 256, 0, 0, st->dev(0), st->a1img);
+      B2P_LAUNCH(cifar_tc2::pack_conv2_tmem, ceil_div(128 * cifar_tc2::W2T_WORDS, 256), 256, 0, 0, st->dev(2), st->w2tm);
       // host copy of the transposed conv1 weights + bias: they travel as a kernel parameter (cifar_tc::Conv1Const)
       B2P_CUDA(cudaMemcpy(st->w1_host, st->w1t, 27 * 32 * sizeof(float), cudaMemcpyDeviceToHost));
       B2P_CUDA(cudaMemcpy(st->w1_host + 27 * 32, st->dev(1), 32 * sizeof(float), cudaMemcpyDeviceToHost));

@@ -172,3 +172,444 @@ __global__ void pack_conv1_poolwin(const float* __restrict__ w1, unsigned char* 
   *reinterpret_cast<unsigned short*>(img + PLANE_BYTES + off) = (unsigned short)(p >> 16);
 }
 
+// ---- the kernel ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
+          const unsigned char* __restrict__ a1img,        // pack_conv1_poolwin: 2 x 16 KB
+          const uint32_t* __restrict__ w2t,               // pack_conv2_tmem: [128][128]
+          const unsigned char* __restrict__ w2tap8,       // tap 8 of cifar_tc::pack_conv2_f16x2: 8 KB
+          const float* __restrict__ b1, const float* __restrict__ b2,
+          float* __restrict__ out,                        // [B,4096]
+          int batch, long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..2][sample 0..7][event 0..7]
+          RingSpan span) {                                // span.data: rows go into handoff-ring slots instead of out
+#define B2P_TRACE2(role, n, ev, cond) \
+  do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  // ---- one-time set-up (touches only constant weights: runs before pdl_wait) ----------------------------------
+  pdl_trigger();
+  for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
+  if (tid < 32) s.b1[tid] = b1[tid];
+  if (tid >= 32 && tid < 96) s.b2[tid - 32] = b2[tid - 32];
+  if (tid == 0) { s.acq_upto = 0; s.staged = 0; s.out_free = 0; }
+  if (warp == kMmaWarp) {
+    if (lane == 0) {
+      mbar_init(&s.bar_w, 1);
+      mbar_init(&s.bar_patch_full, 4);
+      mbar_init(&s.bar_patch_empty, 1);
+      mbar_init(&s.bar_d1_full, 1);
+      mbar_init(&s.bar_d1_empty, kE1Warps);
+      mbar_init(&s.bar_act_ready, 2 * kE1Warps);
+      mbar_init(&s.bar_act_free, 1);
+      mbar_init(&s.bar_d2_full, 1);
+      mbar_init(&s.bar_d2_empty, kE2Warps);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(&s.tmem_slot, 512);
+    tmem_relinquish();
+  }
+  fence_proxy_async();               // the zeroed activation halo must be visible to the tensor core
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = s.tmem_slot;
+  if (warp == kMmaWarp && lane == 0) {                     // conv1's A tiles and conv2's tap 8 -> shared memory
+    mbar_expect_tx(&s.bar_w, 2 * PLANE_BYTES + cifar_tc::W2_TAP_BYTES);
+    bulk_g2s(s.a1, a1img, PLANE_BYTES, &s.bar_w);
+    bulk_g2s(s.a1 + PLANE_BYTES, a1img + PLANE_BYTES, PLANE_BYTES, &s.bar_w);
+    bulk_g2s(s.w2tap8, w2tap8, cifar_tc::W2_TAP_BYTES, &s.bar_w);
+  }
+  if (tid < 128) {                                         // conv2's A, taps 0..7 -> tensor memory: thread = row = lane
+    const uint4* src = reinterpret_cast<const uint4*>(w2t + (size_t)tid * W2T_WORDS);
+    const uint32_t row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + TM_A2;
+#pragma unroll 1
+    for (int i = 0; i < 4; ++i) {
+      uint32_t v[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 w = __ldg(src + i * 8 + j);
+        v[4 * j] = w.x; v[4 * j + 1] = w.y; v[4 * j + 2] = w.z; v[4 * j + 3] = w.w;
+      }
+      tmem_st32(row + 32 * i, v);
+    }
+    tmem_st_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (dbg && blockIdx.x == 0 && tid == 0) dbg[3 * 64] = clock64();      // end of set-up
+  if (warp != kMmaWarp) pdl_wait();   // input readers and output writers: both may touch the previous kernel's data
+
+  if (warp == kMmaWarp) {
+    // =========================== MMA issuer ========================================================================
+    if (lane == 0) {
+      mbar_wait(&s.bar_w, 0);
+      constexpr uint32_t idesc128 = make_idesc_f16(128, 128), idesc256 = make_idesc_f16(128, 256);
+      const uint64_t d_act = make_desc_sw64(smem_u32(s.act));
+      const uint64_t d_w8 = make_desc_sw64(smem_u32(s.w2tap8));
+      const uint64_t d_phi = make_desc_sw128(smem_u32(s.patch)), d_plo = make_desc_sw128(smem_u32(s.patch) + PLANE_BYTES);
+      const uint64_t d_ahi = make_desc_sw128(smem_u32(s.a1)), d_alo = make_desc_sw128(smem_u32(s.a1) + PLANE_BYTES);
+      const uint32_t t_d1 = tmem_base + TM_D1, t_d2 = tmem_base + TM_D2, t_a2 = tmem_base + TM_A2;
+      int n_samples = 0;
+      for (int b = blockIdx.x; b < batch; b += gridDim.x) ++n_samples;
+
+      // conv1 of half `k1 & 1` of sample k1 >> 1: 9 MMAs, lo terms first, the first hi*hi one scales them by 2^-11
+      auto issue_c1 = [&](uint32_t k1) {
+        mbar_wait(&s.bar_patch_full, k1 & 1);
+        mbar_wait(&s.bar_d1_empty, (k1 & 1) ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          umma<0>(t_d1, d_alo + 2 * c, d_phi + 2 * c, idesc128, c != 0);
+          umma<0>(t_d1, d_ahi + 2 * c, d_plo + 2 * c, idesc128, 1u);
+        }
+        umma_ss_f16_scale11(t_d1, d_ahi, d_phi, idesc128);
+        umma<0>(t_d1, d_ahi + 2, d_phi + 2, idesc128, 1u);
+        umma<0>(t_d1, d_ahi + 4, d_phi + 4, idesc128, 1u);
+        umma_commit(&s.bar_d1_full);
+        umma_commit(&s.bar_patch_empty);
+      };
+      // conv2 of image rows 8h..8h+7 of sample n: 18 MMAs of N = 256 (128 pixels x hi|lo)
+      auto issue_q2 = [&](uint32_t n, uint32_t h) {
+        const uint32_t k2 = 2 * n + h;
+        if (h == 0) mbar_wait(&s.bar_act_ready, n & 1);
+        mbar_wait(&s.bar_d2_empty, (k2 & 1) ^ 1);
+        tc_fence_after();
+        const uint64_t d_half = d_act + ((h * 8 * ACT_ROW_BYTES) >> 4);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap % 3;
+#pragma unroll
+          for (int ks = 0; ks < 2; ++ks) {
+            const uint64_t db = d_half + ((kw * ACT_COPY_BYTES + kh * ACT_ROW_BYTES + ks * 32) >> 4);
+            if (tap < 8) umma_ts_f16(t_d2, t_a2 + tap * 16 + ks * 8, db, idesc256, (tap | ks) != 0);
+            else umma<0>(t_d2, d_w8 + 2 * ks, db, idesc256, 1u);
+          }
+        }
+        umma_commit(&s.bar_d2_full);
+        if (h == 1) umma_commit(&s.bar_act_free);
+      };
+
+      if (n_samples > 0) { issue_c1(0); issue_c1(1); }
+      for (int n = 0; n < n_samples; ++n) {
+        B2P_TRACE2(0, n, 0, true);
+        issue_q2(n, 0);
+        B2P_TRACE2(0, n, 1, true);
+        if (n + 1 < n_samples) issue_c1(2 * (n + 1));
+        B2P_TRACE2(0, n, 2, true);
+        issue_q2(n, 1);
+        B2P_TRACE2(0, n, 3, true);
+        if (n + 1 < n_samples) issue_c1(2 * (n + 1) + 1);
+        B2P_TRACE2(0, n, 4, true);
+      }
+    }
+    __syncwarp();
+  } else if (warp < kE1Warp0) {
+    // =========================== conv1 patch producers ================================================================
+    // thread = pooled pixel of the current half; per channel its 4x4 input window becomes 16 K-values (32 B hi, 32 B lo)
+    const int t = tid - kPatchWarp0 * 32;                    // 0..127
+    const int pr = t >> 4, pc = t & 15;
+    float4 pre[6];
+    if ((int)blockIdx.x < batch) {
+      const float4* xin = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 3072);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) pre[j] = ld_produced(xin + t + 128 * j);
+    }
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      named_bar(1, kPatchThreads);                           // the previous sample's window reads are done
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const int e = (t + 128 * j) * 4;
+        float* d = &s.in[e >> 10][((e >> 5) & 31) + 1][(e & 31) + 1];
+        d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
+      }
+      named_bar(1, kPatchThreads);
+      if (b + (int)gridDim.x < batch) {                      // next image: in flight while this one is processed
+        const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
+#pragma unroll
+        for (int j = 0; j < 6; ++j) pre[j] = ld_produced(xin + t + 128 * j);
+      }
+#pragma unroll 1
+      for (uint32_t h = 0; h < 2; ++h) {
+        const uint32_t k1 = 2 * n + h;
+        mbar_wait(&s.bar_patch_empty, (k1 & 1) ^ 1);         // the MMAs that read the previous half's patches are done
+        const int py = 8 * h + pr;
+        unsigned char* row_hi = s.patch + t * 128;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          uint32_t hi[8], lo[8];
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * pc]);
+            const float2 a = rp[0], bq = rp[1];
+            const uint32_t p0 = split_pack(a.x), p1 = split_pack(a.y), p2 = split_pack(bq.x), p3 = split_pack(bq.y);
+            hi[2 * r] = __byte_perm(p0, p1, 0x5410);     hi[2 * r + 1] = __byte_perm(p2, p3, 0x5410);
+            lo[2 * r] = __byte_perm(p0, p1, 0x7632);     lo[2 * r + 1] = __byte_perm(p2, p3, 0x7632);
+          }
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {             // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
+            const int off = ((2 * c + half) ^ (t & 7)) * 16;
+            *reinterpret_cast<uint4*>(row_hi + off) = make_uint4(hi[4 * half], hi[4 * half + 1], hi[4 * half + 2], hi[4 * half + 3]);
+            *reinterpret_cast<uint4*>(row_hi + PLANE_BYTES + off) = make_uint4(lo[4 * half], lo[4 * half + 1], lo[4 * half + 2], lo[4 * half + 3]);
+          }
+        }
+        fence_proxy_async();                                 // generic-proxy writes -> async proxy (UMMA)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.bar_patch_full);
+      }
+    }
+  } else if (warp < kE2Warp0) {
+    // =========================== conv1 epilogue =======================================================================
+    // TMEM lane = (channel, dy, dx) of a 2x2 pool window, column = pooled pixel.  Warp (q, p): channels 8q..8q+7,
+    // columns 64p..64p+63 of the half.  Pooling = max over the 4 lanes of a channel, done with lane-SWAPPING shuffles
+    // (partners exchange half of their columns, so nothing is computed twice); then bias, ReLU, fp16 hi/lo split, an
+    // 8x8 transpose across the 8 channel lanes, and each lane owns one pixel's 16-byte hi and lo chunks.
+    const int q = warp & 3, p = (warp - kE1Warp0) >> 2;
+    const int o = lane >> 2, d = lane & 3;
+    const float bias = s.b1[8 * q + o];
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D1 + 64 * p;
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+#pragma unroll 1
+      for (uint32_t h = 0; h < 2; ++h) {
+        const uint32_t k1 = 2 * n + h;
+        mbar_wait(&s.bar_d1_full, k1 & 1);
+        tc_fence_after();
+        B2P_TRACE2(1, n, 2 * h, warp == kE1Warp0 && lane == 0);
+        uint4 chunk_hi[2], chunk_lo[2];
+#pragma unroll
+        for (int gi = 0; gi < 2; ++gi) {
+          uint32_t v[32];
+          tmem_ld32(t_row + 32 * gi, v);
+          tmem_ld_wait();
+          float m1[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {                     // dx partner: keep column 2j + (d&1), hand over the other
+            const float a = __uint_as_float(v[2 * j]), c2 = __uint_as_float(v[2 * j + 1]);
+            const float recv = __shfl_xor_sync(0xffffffffu, (d & 1) ? a : c2, 1);
+            m1[j] = max_nan((d & 1) ? c2 : a, recv);
+          }
+          uint32_t u[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {                      // dy partner: keep m1[2i + (d>>1)]  ->  column 4i + d
+            const float recv = __shfl_xor_sync(0xffffffffu, (d & 2) ? m1[2 * i] : m1[2 * i + 1], 2);
+            const float m = max_nan((d & 2) ? m1[2 * i + 1] : m1[2 * i], recv);
+            u[i] = split_pack(max_nan(m + bias, 0.f));       // max(a)+b == max(a+b); ReLU
+          }
+          // 8x8 transpose over (channel lane o, register i): afterwards lane (o', d) holds pixel column 4o'+d, channels 8q+i
+#pragma unroll
+          for (int k = 1; k < 8; k <<= 1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              if (i & k) continue;
+              const bool up = (o & k) != 0;
+              const uint32_t recv = __shfl_xor_sync(0xffffffffu, up ? u[i] : u[i | k], 4 * k);
+              if (up) u[i] = recv; else u[i | k] = recv;
+            }
+          }
+          chunk_hi[gi] = make_uint4(__byte_perm(u[0], u[1], 0x5410), __byte_perm(u[2], u[3], 0x5410),
+                                    __byte_perm(u[4], u[5], 0x5410), __byte_perm(u[6], u[7], 0x5410));
+          chunk_lo[gi] = make_uint4(__byte_perm(u[0], u[1], 0x7632), __byte_perm(u[2], u[3], 0x7632),
+                                    __byte_perm(u[4], u[5], 0x7632), __byte_perm(u[6], u[7], 0x7632));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.bar_d1_empty);         // the accumulator may be overwritten (next half's MMAs)
+        if (h == 0) mbar_wait(&s.bar_act_free, (n & 1) ^ 1); // conv2 of the previous sample has read the activation
+        B2P_TRACE2(1, n, 2 * h + 1, warp == kE1Warp0 && lane == 0);
+#pragma unroll
+        for (int gi = 0; gi < 2; ++gi) {
+          const int y = 8 * h + 4 * p + 2 * gi + (lane >> 4), xc = lane & 15;     // this lane's pixel of the 16x16 activation
+#pragma unroll
+          for (int kw = 0; kw < 3; ++kw) {
+            const int xs = xc - kw + 1;                        // its column in copy kw (copy kw holds pixel (y, x+kw-1) at x)
+            if (xs < 0 || xs > 15) continue;
+            unsigned char* dst = s.act + kw * ACT_COPY_BYTES + ((y + 1) * 2 + (xs >> 3)) * 1024 + (xs & 7) * 64 +
+                                 ((q ^ ((xs & 7) >> 1)) * 16);
+            *reinterpret_cast<uint4*>(dst) = chunk_hi[gi];
+            *reinterpret_cast<uint4*>(dst + 512) = chunk_lo[gi];
+          }
+        }
+        fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.bar_act_ready);
+      }
+    }
+  } else if (warp < kAcqWarp) {
+    // =========================== conv2 epilogue =======================================================================
+    // Accumulator of a half sample: lane r < 64 = channel r:  column 16G+e = W_hi*a_hi (e < 8) | W_hi*a_lo (e >= 8) of
+    // pixel 8G+e%8;  lane 64+r:  W_lo*a_hi (e < 8).  Warp (q, p): lanes 32q.., image rows 8h+4p .. +3 (columns 128p ..).
+    // The warps on lanes 64..127 only forward their term (scaled by 2^-11, as fp16) to the warp 64 lanes below through
+    // shared memory, two image rows at a time; the receiving warps add the three terms, pool 2x2 inside the thread, add
+    // the bias, apply ReLU and write 4 consecutive outputs of the flatten order into the staging tile.
+    const int q = warp & 3, p = (warp - kE2Warp0) >> 2;
+    const bool sender = q >= 2;
+    const int pair = (q & 1) * 2 + p;                         // sender (q,p) <-> receiver (q-2,p)
+    const int bar_full = 4 + pair, bar_free = 8 + pair;       // named barriers, 64 threads each
+    const int oc = 32 * (q & 1) + lane;
+    const float bias = s.b2[oc];
+    unsigned char* xrow = s.xch + pair * 2048 + lane * 64;
+    const int xsw = (lane >> 1) & 3;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D2 + 128 * p;
+    uint32_t n = 0, it = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+#pragma unroll 1
+      for (uint32_t h = 0; h < 2; ++h) {
+        const uint32_t k2 = 2 * n + h;
+        mbar_wait(&s.bar_d2_full, k2 & 1);
+        tc_fence_after();
+        B2P_TRACE2(2, n, 2 * h, warp == kE2Warp0 + 3 && lane == 0);
+        if (!sender && h == 0) {                              // the previous sample's bulk copies must be done reading `out`
+          while (ld_acquire_cta(&s.out_free) < (int)n) { }
+        }
+#pragma unroll 1
+        for (int rp = 0; rp < 2; ++rp, ++it) {                // two image rows = four 8-pixel groups = 64 columns
+          const uint32_t t_rp = t_row + 64 * rp;
+          if (sender) {
+            uint32_t a[4][8];
+#pragma unroll
+            for (int g = 0; g < 4; ++g) tmem_ld8(t_rp + 16 * g, a[g]);
+            tmem_ld_wait();
+            if (it > 0) named_bar(bar_free, 64);              // the receiver has read what the previous round left here
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint32_t w[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const __half2 h2 = __floats2half2_rn(__uint_as_float(a[g][2 * j]) * (1.0f / 2048.0f),
+                                                     __uint_as_float(a[g][2 * j + 1]) * (1.0f / 2048.0f));
+                w[j] = *reinterpret_cast<const uint32_t*>(&h2);
+              }
+              *reinterpret_cast<uint4*>(xrow + ((g ^ xsw) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            __threadfence_block();
+            bar_arrive(bar_full, 64);
+          } else {
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {                     // left / right 8 pixels of the two rows
+              uint32_t r0[16], r1[16];
+              cifar_tc::tmem_ld16(t_rp + 16 * g, r0);         // row y:   hi x8 | lo x8
+              cifar_tc::tmem_ld16(t_rp + 32 + 16 * g, r1);    // row y+1
+              tmem_ld_wait();
+              if (g == 0) named_bar(bar_full, 64);
+              const uint4 x0 = *reinterpret_cast<const uint4*>(xrow + ((g ^ xsw) * 16));
+              const uint4 x1 = *reinterpret_cast<const uint4*>(xrow + (((2 + g) ^ xsw) * 16));
+              const uint32_t xw0[4] = {x0.x, x0.y, x0.z, x0.w}, xw1[4] = {x1.x, x1.y, x1.z, x1.w};
+              float v0[8], v1[8];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&xw0[j]));
+                const float2 c1 = __half22float2(*reinterpret_cast<const __half2*>(&xw1[j]));
+                v0[2 * j] = fmaf(__uint_as_float(r0[8 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r0[2 * j])) + c0.x;
+                v0[2 * j + 1] = fmaf(__uint_as_float(r0[9 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r0[2 * j + 1])) + c0.y;
+                v1[2 * j] = fmaf(__uint_as_float(r1[8 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r1[2 * j])) + c1.x;
+                v1[2 * j + 1] = fmaf(__uint_as_float(r1[9 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r1[2 * j + 1])) + c1.y;
+              }
+              float4 o4;
+              float* op = &o4.x;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                op[j] = max_nan(max_nan(max_nan(v0[2 * j], v0[2 * j + 1]), max_nan(v1[2 * j], v1[2 * j + 1])) + bias, 0.f);
+              *reinterpret_cast<float4*>(&s.out[oc * OUT_PITCH + (4 * h + 2 * p + rp) * 8 + 4 * g]) = o4;
+            }
+            __threadfence_block();
+            bar_arrive(bar_free, 64);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.bar_d2_empty);          // the accumulator may be overwritten (other half's MMAs)
+        B2P_TRACE2(2, n, 2 * h + 1, warp == kE2Warp0 + 3 && lane == 0);
+        if (!sender && h == 1) {
+          fence_proxy_async();                                // this thread's writes to `out` -> visible to the copy engine
+          named_bar(2, 128);                                  // the four receiving warps: all 4096 outputs are staged
+          if (q == 0 && p == 0 && lane == 0) st_release_cta(&s.staged, (int)n + 1);
+        }
+      }
+    }
+    // the last round's "free" arrivals of the receivers have no matching wait: balance the barrier so that no
+    // arrival is left pending at exit
+    if (sender && it > 0) named_bar(bar_free, 64);
+  } else if (warp == kAcqWarp) {
+    // =========================== handoff-ring acquirer (ring_hooks.cuh; as in cifar_tc.cuh) ==========================
+    if (span.data && lane == 0) {
+      int acquired = -1;
+      uint32_t n = 0;
+      for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+        const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
+        if (msg != acquired) {
+          const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
+          if (k > 0) {
+            if (b == msg * span.rows_per_msg) {                          // one CTA per message polls over NVLink
+              spin_until_ge_remote(span.released + slot, k);
+              st_release_gpu(span.acq_seen + slot, k);
+            } else {
+              while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
+            }
+          }
+          acquired = msg;
+        }
+        st_release_cta(&s.acq_upto, (int)n + 1);
+      }
+    }
+  } else {
+    // =========================== publisher ==============================================================================
+    // One finished sample leaves as 64 bulk copies of 256 B (a channel row each; the staging tile is padded), two per
+    // lane, into HBM or -- ring mode -- straight into the consumer GPU's slot.  Ring mode then counts the row into the
+    // message's ticket; whoever counts the last row publishes the message (one system-scope release per message).
+    uint32_t n = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+      float* dst_row = out + (size_t)b * 4096;
+      int msg = 0, slot = 0;
+      if (span.data) {
+        msg = b / span.rows_per_msg;
+        slot = span_slot(span, msg);
+        dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
+      }
+      if (lane == 0) {
+        while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
+        if (span.data) while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the slot must have been released by the consumer
+      }
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int c = lane + 32 * k;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row + c * 64),
+                     "r"(smem_u32(&s.out[c * OUT_PITCH])), "r"(256) : "memory");
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      cifar_tc::bulk_wait_read();
+      __syncwarp();
+      if (lane == 0) st_release_cta(&s.out_free, (int)n + 1);
+      if (span.data) {
+        cifar_tc::bulk_wait_all();
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+          const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
+          if (atomicAdd(span.tickets + slot, 1) == rows - 1) {
+            span.tickets[slot] = 0;                             // ready for the slot's next message
+            __threadfence();
+            const unsigned long long k = ld_count(span.count + slot) + 1;
+            span.count[slot] = k;
+            st_release_sys(span.published + slot, k);
+          }
+        }
+      }
+    }
+    cifar_tc::bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
+#undef B2P_TRACE2
+}
+
+}  // namespace cifar_tc2
+}  // namespace b2p

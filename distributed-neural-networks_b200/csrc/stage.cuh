@@ -35,7 +35,9 @@ struct b2p_stage {
   float* w1t = nullptr;             // [27][32]
   float w1_host[27 * 32 + 32] = {};  // host copy of w1t and conv1.bias: kernel-parameter operand of part0_tc
   float* w2t = nullptr;             // [288][64]
-  unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's B tiles (split fp16)
+  unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's [W_hi ; W_lo] tiles, one per tap (split fp16)
+  unsigned char* a1img = nullptr;   // tensor-core modes: conv1 as pool-window GEMM, A tiles hi | lo (cifar_tc2.cuh)
+  uint32_t* w2tm = nullptr;         // tensor-core modes: tensor-memory image of conv2's [W_hi ; W_lo], taps 0..7
   long long* trace = nullptr;       // optional kernel timeline buffer (b2p_stage_trace)
   // ---- CIFAR part 1 ----
   float* fc_ws = nullptr;           // split-K partials [splits][M][512]
