@@ -147,7 +147,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else if (!part0_v1())   // both convolutions on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH_PDL_BIT(2, cifar_tc2::part0_tc2, grid, cifar_tc2::kThreads, cifar_tc2::SMEM_BYTES, s, in, st->a1img, st->w2tm,
-                       st->w2img + 8 * cifar_tc::W2_TAP_BYTES, st->dev(1), st->dev(3), out, (int)batch, st->trace, span);
+                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->trace, span);
   else   // round 1's kernel (conv1 on the CUDA cores), kept for A/B measurements: B2P_PART0_V1=1
   {
     cifar_tc::Conv1Const c1;
@@ -546,7 +546,7 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
-  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->trace); cudaFree(st->fc_ws);
+  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->w2tap8); cudaFree(st->trace); cudaFree(st->fc_ws);
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -610,6 +610,8 @@ int b2p_stage_finalize(b2p_stage* st) {
       B2P_CUDA(cudaMemset(st->a1img, 0, 2 * cifar_tc2::PLANE_BYTES));
       B2P_LAUNCH(cifar_tc2::pack_conv1_poolwin, ceil_div(128 * 64, 256), 256, 0, 0, st->dev(0), st->a1img);
       B2P_LAUNCH(cifar_tc2::pack_conv2_tmem, ceil_div(128 * cifar_tc2::W2T_WORDS, 256), 256, 0, 0, st->dev(2), st->w2tm);
+      if (!st->w2tap8) B2P_CUDA(cudaMalloc((void**)&st->w2tap8, cifar_tc::W2_TAP_BYTES));
+      B2P_LAUNCH(cifar_tc2::pack_conv2_tap8, 2, 256, 0, 0, st->dev(2), st->w2tap8);
       // host copy of the transposed conv1 weights + bias: they travel as a kernel parameter (cifar_tc::Conv1Const)
       B2P_CUDA(cudaMemcpy(st->w1_host, st->w1t, 27 * 32 * sizeof(float), cudaMemcpyDeviceToHost));
       B2P_CUDA(cudaMemcpy(st->w1_host + 27 * 32, st->dev(1), 32 * sizeof(float), cudaMemcpyDeviceToHost));

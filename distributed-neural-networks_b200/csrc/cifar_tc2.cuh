@@ -8,12 +8,13 @@
 // (72 narrow MMAs per sample) could never do better than ~40 %.  Here the roles are swapped:
 //
 //   conv2  D[128 x 256] += A[128 x 16] * B[256 x 16]^T  per 3x3 tap and 16 input channels, where
-//          A = [W_hi ; W_lo]  (64 output channels, fp16 hi part stacked on the lo part) sits in TENSOR MEMORY for taps
-//              0..7 (128 columns; tap 8 is read from shared memory: 144 columns would not leave room for the
-//              accumulators), and
+//          A = rows 2c, 2c+1 = fp16 hi part, lo part of output channel c (64 channels -> M = 128), in TENSOR MEMORY
+//              for taps 0..7 (128 columns; tap 8 is read from shared memory: 144 columns would not leave room for
+//              the accumulators), and
 //          B = 128 pixels (8 image rows) of the conv1 activation, hi rows and lo rows interleaved in groups of 8,
-//              so ONE instruction yields  W_hi*a_hi | W_hi*a_lo  (lanes 0..63)  and  W_lo*a_hi | (W_lo*a_lo, unused)
-//              (lanes 64..127): the three products of the split-fp16 scheme in 36 wide MMAs per sample.
+//              so ONE instruction yields  W_hi*a_hi | W_hi*a_lo  (even lanes)  and  W_lo*a_hi | (W_lo*a_lo, unused)
+//              (odd lanes): the three products of the split-fp16 scheme in 36 wide MMAs per sample, and the cross
+//              term sits in the NEIGHBOURING lane of the same warp -- one shuffle away in the epilogue.
 //          The B operand of tap (kh,kw) is a plain shifted window of the activation (three x-shifted copies with a
 //          zero halo, as in round 1): no im2col.  The accumulator comes out [channel][pixel], i.e. already in the
 //          reference's flatten order c*64+h*8+w, and the 2x2 pool is between a thread's own columns.
@@ -24,11 +25,12 @@
 //          The epilogue pools across the 4 lanes of a channel with lane-swapping shuffles, transposes 8x8 across
 //          lanes and writes the fp16 hi/lo activation rows for conv2.
 //
-// Warp roles (23 warps, one persistent CTA per SM, samples blockIdx.x, +gridDim.x, ...):
-//   0        MMA issuer            1..4    conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo)
-//   5..12    conv1 epilogue        13..20  conv2 epilogue (lanes 64..127 hand their cross term to lanes 0..63
-//   21       ring acquirer                  through shared memory) -> padded staging tile
-//   22       publisher: bulk copies of the finished sample to HBM or straight into the next GPU's ring slot
+// Warp roles (23 warps, one persistent CTA per SM, samples blockIdx.x, +gridDim.x, ...).  The SM's warp arbiter
+// favours high warp ids, so the roles whose latency the tensor pipe waits for come last:
+//   0..3     conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo)
+//   4..19    epilogue warps: drain conv2's accumulator (-> staging tile) and run conv1's epilogue, alternately
+//   20       ring acquirer         21      publisher: bulk copies of the finished sample to HBM or straight into the
+//   22       MMA issuer                    next GPU's ring slot
 //
 // Arithmetic and range are those of round 1's kernel: x ~= hi + lo * 2^-11 with fp16 hi/lo, products exact in the
 // fp32 accumulator, the lo*lo term dropped.  |input| and |conv1 output| must stay below 65504 (fp16 range); beyond
@@ -46,11 +48,9 @@ using cifar_tc::make_desc_sw64;
 using cifar_tc::make_idesc_f16;
 using cifar_tc::named_bar;
 
-constexpr int kMmaWarp = 0;
-constexpr int kPatchWarp0 = 1, kPatchThreads = 128;
-constexpr int kE1Warp0 = 5, kE1Warps = 8;
-constexpr int kE2Warp0 = 13, kE2Warps = 8;
-constexpr int kAcqWarp = 21, kPubWarp = 22;
+constexpr int kPatchWarp0 = 0, kPatchThreads = 128;
+constexpr int kE1Warp0 = 4, kEpiWarps = 16;           // epilogue warps 4..19
+constexpr int kAcqWarp = 20, kPubWarp = 21, kMmaWarp = 22;
 constexpr int kThreads = 23 * 32;                     // 736
 
 // tensor-memory map (512 columns)
@@ -62,19 +62,17 @@ constexpr int ACT_ROW_BYTES = 2048;                   // one image row of one co
 constexpr int ACT_COPY_BYTES = 18 * ACT_ROW_BYTES;    // rows -1..16
 constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;         // 110 592
 constexpr int PLANE_BYTES = 128 * 128;                // a 128-row operand tile with 128-byte rows
-constexpr int OUT_PITCH = 68;                         // floats per channel row of the staging tile (64 + 4: no bank conflicts)
 constexpr int W2T_WORDS = 128;                        // tensor-memory image of conv2's weights: 32-bit words per row
 
 struct Smem {
   unsigned char act[ACT_BYTES];                       // conv2's B operand: 3 x-shifted copies, hi/lo interleaved by 8 pixels
   unsigned char patch[2 * PLANE_BYTES];               // conv1's B operand: [hi | lo][128 pooled pixels][128 B], 96 B used
   unsigned char a1[2 * PLANE_BYTES];                  // conv1's A operand: [hi | lo][128 rows (oc,dy,dx)][128 B]
-  unsigned char w2tap8[cifar_tc::W2_TAP_BYTES];       // conv2 tap 8: [W_hi ; W_lo] rows of 64 B, 64B-swizzled
-  float out[64 * OUT_PITCH];                          // one finished sample, [channel][h*8+w]
-  unsigned char xch[4 * 2048];                        // conv2 epilogue: cross terms of lanes 64..127 on their way to lanes 0..63
+  unsigned char w2tap8[cifar_tc::W2_TAP_BYTES];       // conv2 tap 8: 128 rows (2c | 2c+1 = hi | lo of channel c) of 64 B, 64B-swizzled
+  float out[64 * 64];                                 // one finished sample in flatten order, [channel][h*8+w]
   float in[3][34][34];                                // zero-padded input image
   float b1[32], b2[64];
-  uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready, bar_act_free,
+  uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
       bar_d2_full, bar_d2_empty;
   uint32_t tmem_slot;
   int acq_upto, staged, out_free;                     // ring / staging hand-offs (see cifar_tc.cuh)
@@ -129,28 +127,47 @@ __device__ __forceinline__ uint32_t split_pack(float x) {
   const __half lo = __float2half_rn((x - __half2float(hi)) * 2048.0f);
   return (uint32_t)__half_as_ushort(hi) | ((uint32_t)__half_as_ushort(lo) << 16);
 }
-__device__ __forceinline__ void bar_arrive(int id, int threads) {
-  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+// two values at once: (a, b) -> fp16x2 hi parts and fp16x2 lo parts (packed conversions: 4 instructions per value)
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  const __half2 h = __floats2half2_rn(a, b);
+  const float2 hf = __half22float2(h);
+  const __half2 l = __floats2half2_rn((a - hf.x) * 2048.0f, (b - hf.y) * 2048.0f);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 
 // ---- one-off weight repacks (b2p_stage_finalize) -----------------------------------------------------------------
-// conv2.weight [64,32,3,3] -> the tensor-memory image of A = [W_hi ; W_lo] for taps 0..7: row r (0..63 hi part of
-// channel r, 64..127 lo part of channel r-64), 32-bit word tap*16 + ks*8 + j = input channels ks*16 + 2j | 2j+1
-// (low | high half): exactly what tcgen05.mma reads as A[r][k] from lane r, column j of a K=16 step.
+// conv2.weight [64,32,3,3] -> the tensor-memory image of A for taps 0..7: row r = hi part (r even) or lo part (r odd)
+// of channel r/2, 32-bit word tap*16 + ks*8 + j = input channels ks*16 + 2j | 2j+1 (low | high half): exactly what
+// tcgen05.mma reads as A[r][k] from lane r, column j of a K=16 step.
 __global__ void pack_conv2_tmem(const float* __restrict__ w2, uint32_t* __restrict__ img) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 128 * W2T_WORDS) return;
   const int r = i / W2T_WORDS, word = i % W2T_WORDS;
   const int tap = word >> 4, ks = (word >> 3) & 1, j = word & 7;
-  const int oc = r & 63, kh = tap / 3, kw = tap % 3;
+  const int oc = r >> 1, kh = tap / 3, kw = tap % 3;
   uint32_t v = 0;
 #pragma unroll
   for (int e = 0; e < 2; ++e) {
     const int ic = ks * 16 + 2 * j + e;
     const uint32_t p = split_pack(w2[((oc * 32 + ic) * 3 + kh) * 3 + kw]);
-    v |= (r < 64 ? (p & 0xffffu) : (p >> 16)) << (16 * e);
+    v |= ((r & 1) ? (p >> 16) : (p & 0xffffu)) << (16 * e);
   }
   img[i] = v;
+}
+// ... and tap 8 (kh = kw = 2) as the byte image of its shared-memory tile: the same 128 rows, 64 B (32 input channels)
+// each, 64B-swizzled K-major (16-byte chunk c of row r at chunk c ^ ((r >> 1) & 3)).
+__global__ void pack_conv2_tap8(const float* __restrict__ w2, unsigned char* __restrict__ img) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;      // one 16-byte chunk each
+  if (i >= 128 * 4) return;
+  const int r = i >> 2, c = i & 3, oc = r >> 1;
+  unsigned short v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const uint32_t p = split_pack(w2[((oc * 32 + 8 * c + e) * 3 + 2) * 3 + 2]);
+    v[e] = (unsigned short)((r & 1) ? (p >> 16) : (p & 0xffffu));
+  }
+  *reinterpret_cast<uint4*>(img + r * 64 + ((c ^ ((r >> 1) & 3)) * 16)) = *reinterpret_cast<const uint4*>(v);
 }
 // conv1.weight [32,3,3,3] -> A operand of the pool-window GEMM: two 128B-swizzled K-major tiles (hi, lo) of 128 rows;
 // row m = oc*4 + dy*2 + dx, k = c*16 + r*4 + s multiplies input pixel (2py-1+r, 2px-1+s) of channel c, so its weight is
@@ -177,10 +194,10 @@ __global__ void __launch_bounds__(kThreads, 1)
 part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           const unsigned char* __restrict__ a1img,        // pack_conv1_poolwin: 2 x 16 KB
           const uint32_t* __restrict__ w2t,               // pack_conv2_tmem: [128][128]
-          const unsigned char* __restrict__ w2tap8,       // tap 8 of cifar_tc::pack_conv2_f16x2: 8 KB
+          const unsigned char* __restrict__ w2tap8,       // pack_conv2_tap8: 8 KB
           const float* __restrict__ b1, const float* __restrict__ b2,
           float* __restrict__ out,                        // [B,4096]
-          int batch, long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..2][sample 0..7][event 0..7]
+          int batch, long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..3][sample 0..7][event 0..7], entry 192 = end of set-up
           RingSpan span) {                                // span.data: rows go into handoff-ring slots instead of out
 #define B2P_TRACE2(role, n, ev, cond) \
   do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
@@ -201,11 +218,12 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       mbar_init(&s.bar_patch_full, 4);
       mbar_init(&s.bar_patch_empty, 1);
       mbar_init(&s.bar_d1_full, 1);
-      mbar_init(&s.bar_d1_empty, kE1Warps);
-      mbar_init(&s.bar_act_ready, 2 * kE1Warps);
+      mbar_init(&s.bar_d1_empty, kEpiWarps);
+      mbar_init(&s.bar_act_ready[0], kEpiWarps);
+      mbar_init(&s.bar_act_ready[1], kEpiWarps);
       mbar_init(&s.bar_act_free, 1);
       mbar_init(&s.bar_d2_full, 1);
-      mbar_init(&s.bar_d2_empty, kE2Warps);
+      mbar_init(&s.bar_d2_empty, kEpiWarps);
       fence_barrier_init();
     }
     __syncwarp();
@@ -273,16 +291,26 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         umma_commit(&s.bar_d1_full);
         umma_commit(&s.bar_patch_empty);
       };
-      // conv2 of image rows 8h..8h+7 of sample n: 18 MMAs of N = 256 (128 pixels x hi|lo)
+      // conv2 of image rows 8h..8h+7 of sample n: 18 MMAs of N = 256 (128 pixels x hi|lo).  Tap row kh reads activation
+      // rows 8h+kh-1 .. 8h+kh+6, so of the upper half only kh = 2 touches row 8, the first row conv1's SECOND half
+      // produces: those six MMAs wait for it separately, the other twelve start as soon as the first half is there.
       auto issue_q2 = [&](uint32_t n, uint32_t h) {
         const uint32_t k2 = 2 * n + h;
-        if (h == 0) mbar_wait(&s.bar_act_ready, n & 1);
+        if (h == 0) {
+          mbar_wait(&s.bar_act_ready[0], n & 1);
+          B2P_TRACE2(0, n, 1, true);
+        }
         mbar_wait(&s.bar_d2_empty, (k2 & 1) ^ 1);
+        B2P_TRACE2(0, n, h ? 5 : 2, true);
         tc_fence_after();
         const uint64_t d_half = d_act + ((h * 8 * ACT_ROW_BYTES) >> 4);
 #pragma unroll
         for (int tap = 0; tap < 9; ++tap) {
           const int kh = tap / 3, kw = tap % 3;
+          if (tap == 6 && h == 0) {
+            mbar_wait(&s.bar_act_ready[1], n & 1);
+            tc_fence_after();
+          }
 #pragma unroll
           for (int ks = 0; ks < 2; ++ks) {
             const uint64_t db = d_half + ((kw * ACT_COPY_BYTES + kh * ACT_ROW_BYTES + ks * 32) >> 4);
@@ -298,13 +326,13 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       for (int n = 0; n < n_samples; ++n) {
         B2P_TRACE2(0, n, 0, true);
         issue_q2(n, 0);
-        B2P_TRACE2(0, n, 1, true);
-        if (n + 1 < n_samples) issue_c1(2 * (n + 1));
-        B2P_TRACE2(0, n, 2, true);
-        issue_q2(n, 1);
         B2P_TRACE2(0, n, 3, true);
-        if (n + 1 < n_samples) issue_c1(2 * (n + 1) + 1);
+        if (n + 1 < n_samples) issue_c1(2 * (n + 1));
         B2P_TRACE2(0, n, 4, true);
+        issue_q2(n, 1);
+        B2P_TRACE2(0, n, 6, true);
+        if (n + 1 < n_samples) issue_c1(2 * (n + 1) + 1);
+        B2P_TRACE2(0, n, 7, true);
       }
     }
     __syncwarp();
@@ -329,6 +357,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
       }
       named_bar(1, kPatchThreads);
+      B2P_TRACE2(3, n, 1, t == 0);
       if (b + (int)gridDim.x < batch) {                      // next image: in flight while this one is processed
         const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
 #pragma unroll
@@ -338,6 +367,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       for (uint32_t h = 0; h < 2; ++h) {
         const uint32_t k1 = 2 * n + h;
         mbar_wait(&s.bar_patch_empty, (k1 & 1) ^ 1);         // the MMAs that read the previous half's patches are done
+        B2P_TRACE2(3, n, 2 + 2 * h, t == 0);
         const int py = 8 * h + pr;
         unsigned char* row_hi = s.patch + t * 128;
 #pragma unroll
@@ -347,9 +377,8 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           for (int r = 0; r < 4; ++r) {
             const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * pc]);
             const float2 a = rp[0], bq = rp[1];
-            const uint32_t p0 = split_pack(a.x), p1 = split_pack(a.y), p2 = split_pack(bq.x), p3 = split_pack(bq.y);
-            hi[2 * r] = __byte_perm(p0, p1, 0x5410);     hi[2 * r + 1] = __byte_perm(p2, p3, 0x5410);
-            lo[2 * r] = __byte_perm(p0, p1, 0x7632);     lo[2 * r + 1] = __byte_perm(p2, p3, 0x7632);
+            split2(a.x, a.y, hi[2 * r], lo[2 * r]);
+            split2(bq.x, bq.y, hi[2 * r + 1], lo[2 * r + 1]);
           }
 #pragma unroll
           for (int half = 0; half < 2; ++half) {             // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
@@ -361,180 +390,150 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         fence_proxy_async();                                 // generic-proxy writes -> async proxy (UMMA)
         __syncwarp();
         if (lane == 0) mbar_arrive(&s.bar_patch_full);
-      }
-    }
-  } else if (warp < kE2Warp0) {
-    // =========================== conv1 epilogue =======================================================================
-    // TMEM lane = (channel, dy, dx) of a 2x2 pool window, column = pooled pixel.  Warp (q, p): channels 8q..8q+7,
-    // columns 64p..64p+63 of the half.  Pooling = max over the 4 lanes of a channel, done with lane-SWAPPING shuffles
-    // (partners exchange half of their columns, so nothing is computed twice); then bias, ReLU, fp16 hi/lo split, an
-    // 8x8 transpose across the 8 channel lanes, and each lane owns one pixel's 16-byte hi and lo chunks.
-    const int q = warp & 3, p = (warp - kE1Warp0) >> 2;
-    const int o = lane >> 2, d = lane & 3;
-    const float bias = s.b1[8 * q + o];
-    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D1 + 64 * p;
-    uint32_t n = 0;
-    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
-#pragma unroll 1
-      for (uint32_t h = 0; h < 2; ++h) {
-        const uint32_t k1 = 2 * n + h;
-        mbar_wait(&s.bar_d1_full, k1 & 1);
-        tc_fence_after();
-        B2P_TRACE2(1, n, 2 * h, warp == kE1Warp0 && lane == 0);
-        uint4 chunk_hi[2], chunk_lo[2];
-#pragma unroll
-        for (int gi = 0; gi < 2; ++gi) {
-          uint32_t v[32];
-          tmem_ld32(t_row + 32 * gi, v);
-          tmem_ld_wait();
-          float m1[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {                     // dx partner: keep column 2j + (d&1), hand over the other
-            const float a = __uint_as_float(v[2 * j]), c2 = __uint_as_float(v[2 * j + 1]);
-            const float recv = __shfl_xor_sync(0xffffffffu, (d & 1) ? a : c2, 1);
-            m1[j] = max_nan((d & 1) ? c2 : a, recv);
-          }
-          uint32_t u[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {                      // dy partner: keep m1[2i + (d>>1)]  ->  column 4i + d
-            const float recv = __shfl_xor_sync(0xffffffffu, (d & 2) ? m1[2 * i] : m1[2 * i + 1], 2);
-            const float m = max_nan((d & 2) ? m1[2 * i + 1] : m1[2 * i], recv);
-            u[i] = split_pack(max_nan(m + bias, 0.f));       // max(a)+b == max(a+b); ReLU
-          }
-          // 8x8 transpose over (channel lane o, register i): afterwards lane (o', d) holds pixel column 4o'+d, channels 8q+i
-#pragma unroll
-          for (int k = 1; k < 8; k <<= 1) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              if (i & k) continue;
-              const bool up = (o & k) != 0;
-              const uint32_t recv = __shfl_xor_sync(0xffffffffu, up ? u[i] : u[i | k], 4 * k);
-              if (up) u[i] = recv; else u[i | k] = recv;
-            }
-          }
-          chunk_hi[gi] = make_uint4(__byte_perm(u[0], u[1], 0x5410), __byte_perm(u[2], u[3], 0x5410),
-                                    __byte_perm(u[4], u[5], 0x5410), __byte_perm(u[6], u[7], 0x5410));
-          chunk_lo[gi] = make_uint4(__byte_perm(u[0], u[1], 0x7632), __byte_perm(u[2], u[3], 0x7632),
-                                    __byte_perm(u[4], u[5], 0x7632), __byte_perm(u[6], u[7], 0x7632));
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s.bar_d1_empty);         // the accumulator may be overwritten (next half's MMAs)
-        if (h == 0) mbar_wait(&s.bar_act_free, (n & 1) ^ 1); // conv2 of the previous sample has read the activation
-        B2P_TRACE2(1, n, 2 * h + 1, warp == kE1Warp0 && lane == 0);
-#pragma unroll
-        for (int gi = 0; gi < 2; ++gi) {
-          const int y = 8 * h + 4 * p + 2 * gi + (lane >> 4), xc = lane & 15;     // this lane's pixel of the 16x16 activation
-#pragma unroll
-          for (int kw = 0; kw < 3; ++kw) {
-            const int xs = xc - kw + 1;                        // its column in copy kw (copy kw holds pixel (y, x+kw-1) at x)
-            if (xs < 0 || xs > 15) continue;
-            unsigned char* dst = s.act + kw * ACT_COPY_BYTES + ((y + 1) * 2 + (xs >> 3)) * 1024 + (xs & 7) * 64 +
-                                 ((q ^ ((xs & 7) >> 1)) * 16);
-            *reinterpret_cast<uint4*>(dst) = chunk_hi[gi];
-            *reinterpret_cast<uint4*>(dst + 512) = chunk_lo[gi];
-          }
-        }
-        fence_proxy_async();                                   // generic-proxy writes -> async proxy (UMMA)
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s.bar_act_ready);
+        B2P_TRACE2(3, n, 3 + 2 * h, t == 0);
       }
     }
   } else if (warp < kAcqWarp) {
-    // =========================== conv2 epilogue =======================================================================
-    // Accumulator of a half sample: lane r < 64 = channel r:  column 16G+e = W_hi*a_hi (e < 8) | W_hi*a_lo (e >= 8) of
-    // pixel 8G+e%8;  lane 64+r:  W_lo*a_hi (e < 8).  Warp (q, p): lanes 32q.., image rows 8h+4p .. +3 (columns 128p ..).
-    // The warps on lanes 64..127 only forward their term (scaled by 2^-11, as fp16) to the warp 64 lanes below through
-    // shared memory, two image rows at a time; the receiving warps add the three terms, pool 2x2 inside the thread, add
-    // the bias, apply ReLU and write 4 consecutive outputs of the flatten order into the staging tile.
-    const int q = warp & 3, p = (warp - kE2Warp0) >> 2;
-    const bool sender = q >= 2;
-    const int pair = (q & 1) * 2 + p;                         // sender (q,p) <-> receiver (q-2,p)
-    const int bar_full = 4 + pair, bar_free = 8 + pair;       // named barriers, 64 threads each
-    const int oc = 32 * (q & 1) + lane;
-    const float bias = s.b2[oc];
-    unsigned char* xrow = s.xch + pair * 2048 + lane * 64;
-    const int xsw = (lane >> 1) & 3;
-    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D2 + 128 * p;
-    uint32_t n = 0, it = 0;
-    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
-#pragma unroll 1
-      for (uint32_t h = 0; h < 2; ++h) {
-        const uint32_t k2 = 2 * n + h;
-        mbar_wait(&s.bar_d2_full, k2 & 1);
-        tc_fence_after();
-        B2P_TRACE2(2, n, 2 * h, warp == kE2Warp0 + 3 && lane == 0);
-        if (!sender && h == 0) {                              // the previous sample's bulk copies must be done reading `out`
-          while (ld_acquire_cta(&s.out_free) < (int)n) { }
-        }
-#pragma unroll 1
-        for (int rp = 0; rp < 2; ++rp, ++it) {                // two image rows = four 8-pixel groups = 64 columns
-          const uint32_t t_rp = t_row + 64 * rp;
-          if (sender) {
-            uint32_t a[4][8];
+    // =========================== epilogue warps (16): conv2 drain and conv1 epilogue in the tensor pipe's order =========
+    // The MMA stream is  Q2(n,0) C1(n+1,0) Q2(n,1) C1(n+1,1) ...  and conv2 has ONE accumulator, so the time to drain it
+    // is what the tensor pipe waits for.  All 16 warps therefore drain it together (E2, one image-row pair each), and
+    // between two drains do their share of the conv1 epilogue (E1, 32 pooled pixels each): read and pool right away,
+    // but write the activation only after the second drain -- it may not be overwritten before Q2(n,1) has completed,
+    // which is also the moment that drain starts, and the drain goes first.
+    const int q = warp & 3, part = (warp - kE1Warp0) >> 2;    // TMEM lane quarter; 0..3
+    // ---- E2 geometry: lane 2c = channel 16q + c (even lanes finish), columns 64*part .. +63 = image rows 8h+2*part, +1
+    const bool even = (lane & 1) == 0;
+    const int oc2 = 16 * q + (lane >> 1);
+    const float bias2 = s.b2[oc2];
+    const uint32_t t_row2 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D2 + 64 * part;
+    // ---- E1 geometry: lane = (channel 8q + o, window position d), columns 32*part .. +31 = pooled rows 8h+2*part, +1
+    const int o = lane >> 2, d = lane & 3;
+    const float bias1 = s.b1[8 * q + o];
+    const uint32_t t_row1 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D1 + 32 * part;
+    const bool tracer = warp == kE1Warp0 && lane == 0;
+
+    uint4 chunk_hi, chunk_lo;                                  // E1 result held between read and write
+    // conv1 epilogue, first part: TMEM -> pooled, biased, rectified, transposed, split
+    auto e1_read = [&](uint32_t k1) {
+      mbar_wait(&s.bar_d1_full, k1 & 1);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld32(t_row1, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.bar_d1_empty);           // the accumulator may be overwritten (next half's MMAs)
+      float m1[16];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) tmem_ld8(t_rp + 16 * g, a[g]);
-            tmem_ld_wait();
-            if (it > 0) named_bar(bar_free, 64);              // the receiver has read what the previous round left here
+      for (int j = 0; j < 16; ++j) {                         // dx partner: keep column 2j + (d&1), hand over the other
+        const float a = __uint_as_float(v[2 * j]), c2 = __uint_as_float(v[2 * j + 1]);
+        const float recv = __shfl_xor_sync(0xffffffffu, (d & 1) ? a : c2, 1);
+        m1[j] = max_nan((d & 1) ? c2 : a, recv);
+      }
+      float u[8];
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              uint32_t w[4];
+      for (int i = 0; i < 8; ++i) {                          // dy partner: keep m1[2i + (d>>1)]  ->  column 4i + d
+        const float recv = __shfl_xor_sync(0xffffffffu, (d & 2) ? m1[2 * i] : m1[2 * i + 1], 2);
+        const float m = max_nan((d & 2) ? m1[2 * i + 1] : m1[2 * i], recv);
+        u[i] = max_nan(m + bias1, 0.f);                      // max(a)+b == max(a+b); ReLU
+      }
+      // 8x8 transpose over (channel lane o, register i): afterwards lane (o', d) holds pixel column 4o'+d, channels 8q+i
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const __half2 h2 = __floats2half2_rn(__uint_as_float(a[g][2 * j]) * (1.0f / 2048.0f),
-                                                     __uint_as_float(a[g][2 * j + 1]) * (1.0f / 2048.0f));
-                w[j] = *reinterpret_cast<const uint32_t*>(&h2);
-              }
-              *reinterpret_cast<uint4*>(xrow + ((g ^ xsw) * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
-            }
-            __threadfence_block();
-            bar_arrive(bar_full, 64);
-          } else {
+      for (int k = 1; k < 8; k <<= 1) {
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {                     // left / right 8 pixels of the two rows
-              uint32_t r0[16], r1[16];
-              cifar_tc::tmem_ld16(t_rp + 16 * g, r0);         // row y:   hi x8 | lo x8
-              cifar_tc::tmem_ld16(t_rp + 32 + 16 * g, r1);    // row y+1
-              tmem_ld_wait();
-              if (g == 0) named_bar(bar_full, 64);
-              const uint4 x0 = *reinterpret_cast<const uint4*>(xrow + ((g ^ xsw) * 16));
-              const uint4 x1 = *reinterpret_cast<const uint4*>(xrow + (((2 + g) ^ xsw) * 16));
-              const uint32_t xw0[4] = {x0.x, x0.y, x0.z, x0.w}, xw1[4] = {x1.x, x1.y, x1.z, x1.w};
-              float v0[8], v1[8];
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float2 c0 = __half22float2(*reinterpret_cast<const __half2*>(&xw0[j]));
-                const float2 c1 = __half22float2(*reinterpret_cast<const __half2*>(&xw1[j]));
-                v0[2 * j] = fmaf(__uint_as_float(r0[8 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r0[2 * j])) + c0.x;
-                v0[2 * j + 1] = fmaf(__uint_as_float(r0[9 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r0[2 * j + 1])) + c0.y;
-                v1[2 * j] = fmaf(__uint_as_float(r1[8 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r1[2 * j])) + c1.x;
-                v1[2 * j + 1] = fmaf(__uint_as_float(r1[9 + 2 * j]), 1.0f / 2048.0f, __uint_as_float(r1[2 * j + 1])) + c1.y;
-              }
-              float4 o4;
-              float* op = &o4.x;
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                op[j] = max_nan(max_nan(max_nan(v0[2 * j], v0[2 * j + 1]), max_nan(v1[2 * j], v1[2 * j + 1])) + bias, 0.f);
-              *reinterpret_cast<float4*>(&s.out[oc * OUT_PITCH + (4 * h + 2 * p + rp) * 8 + 4 * g]) = o4;
-            }
-            __threadfence_block();
-            bar_arrive(bar_free, 64);
-          }
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s.bar_d2_empty);          // the accumulator may be overwritten (other half's MMAs)
-        B2P_TRACE2(2, n, 2 * h + 1, warp == kE2Warp0 + 3 && lane == 0);
-        if (!sender && h == 1) {
-          fence_proxy_async();                                // this thread's writes to `out` -> visible to the copy engine
-          named_bar(2, 128);                                  // the four receiving warps: all 4096 outputs are staged
-          if (q == 0 && p == 0 && lane == 0) st_release_cta(&s.staged, (int)n + 1);
+        for (int i = 0; i < 8; ++i) {
+          if (i & k) continue;
+          const bool up = (o & k) != 0;
+          const float recv = __shfl_xor_sync(0xffffffffu, up ? u[i] : u[i | k], 4 * k);
+          if (up) u[i] = recv; else u[i | k] = recv;
         }
       }
+      split2(u[0], u[1], chunk_hi.x, chunk_lo.x);
+      split2(u[2], u[3], chunk_hi.y, chunk_lo.y);
+      split2(u[4], u[5], chunk_hi.z, chunk_lo.z);
+      split2(u[6], u[7], chunk_hi.w, chunk_lo.w);
+    };
+    // conv1 epilogue, second part: this lane's pixel (16-byte hi and lo chunk of its 8 channels) into the three copies
+    auto e1_write = [&](uint32_t h) {
+      const int y = 8 * h + 2 * part + (lane >> 4), xc = lane & 15;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int xs = xc - kw + 1;                            // its column in copy kw (copy kw holds pixel (y, x+kw-1) at x)
+        if (xs < 0 || xs > 15) continue;
+        unsigned char* dst = s.act + kw * ACT_COPY_BYTES + ((y + 1) * 2 + (xs >> 3)) * 1024 + (xs & 7) * 64 +
+                             ((q ^ ((xs & 7) >> 1)) * 16);
+        *reinterpret_cast<uint4*>(dst) = chunk_hi;
+        *reinterpret_cast<uint4*>(dst + 512) = chunk_lo;
+      }
+      fence_proxy_async();                                     // generic-proxy writes -> async proxy (UMMA)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.bar_act_ready[h]);
+    };
+    // conv2 drain of one image-row pair: the odd lanes hand W_lo*a_hi to the even lane below (one shuffle per value);
+    // the even lanes add the three terms, pool 2x2 inside the thread, add the bias, apply ReLU, store 4 outputs
+    auto e2_drain = [&](uint32_t n, uint32_t h) {
+      mbar_wait(&s.bar_d2_full, (2 * n + h) & 1);
+      tc_fence_after();
+      uint32_t r[4][16];
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        cifar_tc::tmem_ld16(t_row2 + 16 * g, r[2 * g]);            // row y:   hi x8 | lo x8   (left / right 8 pixels)
+        cifar_tc::tmem_ld16(t_row2 + 32 + 16 * g, r[2 * g + 1]);   // row y+1
+      }
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.bar_d2_empty);             // the accumulator may be overwritten (other half's MMAs)
+      if (h == 0 && n > 0) {                                   // the previous sample's bulk copy must be done reading `out`
+        while (ld_acquire_cta(&s.out_free) < (int)n) { }
+      }
+#pragma unroll
+      for (int g = 0; g < 2; ++g) {
+        float v0[8], v1[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float x0 = __shfl_down_sync(0xffffffffu, __uint_as_float(r[2 * g][j]), 1);
+          const float x1 = __shfl_down_sync(0xffffffffu, __uint_as_float(r[2 * g + 1][j]), 1);
+          v0[j] = fmaf(__uint_as_float(r[2 * g][8 + j]) + x0, 1.0f / 2048.0f, __uint_as_float(r[2 * g][j]));
+          v1[j] = fmaf(__uint_as_float(r[2 * g + 1][8 + j]) + x1, 1.0f / 2048.0f, __uint_as_float(r[2 * g + 1][j]));
+        }
+        float4 o4;
+        float* op = &o4.x;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          op[j] = max_nan(max_nan(max_nan(v0[2 * j], v0[2 * j + 1]), max_nan(v1[2 * j], v1[2 * j + 1])) + bias2, 0.f);
+        if (even) *reinterpret_cast<float4*>(&s.out[oc2 * 64 + (4 * h + part) * 8 + 4 * g]) = o4;
+      }
+    };
+
+    int n_samples = 0;
+    for (int b = blockIdx.x; b < batch; b += gridDim.x) ++n_samples;
+    if (n_samples > 0) {                                       // sample 0's conv1: nothing to wait for
+      e1_read(0); e1_write(0);
+      e1_read(1); e1_write(1);
     }
-    // the last round's "free" arrivals of the receivers have no matching wait: balance the barrier so that no
-    // arrival is left pending at exit
-    if (sender && it > 0) named_bar(bar_free, 64);
+    for (int n = 0; n < n_samples; ++n) {
+      const bool more = n + 1 < n_samples;
+      B2P_TRACE2(2, n, 0, tracer);
+      e2_drain(n, 0);
+      B2P_TRACE2(2, n, 1, tracer);
+      if (more) e1_read(2 * (n + 1));                          // held in registers: Q2(n,1) still reads the activation
+      B2P_TRACE2(1, n, 0, tracer);
+      e2_drain(n, 1);
+      B2P_TRACE2(2, n, 2, tracer);
+      fence_proxy_async();                                     // this thread's writes to `out` -> visible to the copy engine
+      named_bar(2, 16 * 32);                                   // all 4096 outputs are staged
+      if (tracer) st_release_cta(&s.staged, n + 1);
+      if (more) {
+        mbar_wait(&s.bar_act_free, n & 1);                     // Q2(n,1) has completed (it had: its drain is done)
+        e1_write(0);
+        B2P_TRACE2(1, n, 1, tracer);
+        e1_read(2 * (n + 1) + 1);
+        B2P_TRACE2(1, n, 2, tracer);
+        e1_write(1);
+        B2P_TRACE2(1, n, 3, tracer);
+      }
+    }
   } else if (warp == kAcqWarp) {
     // =========================== handoff-ring acquirer (ring_hooks.cuh; as in cifar_tc.cuh) ==========================
     if (span.data && lane == 0) {
@@ -559,8 +558,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     }
   } else {
     // =========================== publisher ==============================================================================
-    // One finished sample leaves as 64 bulk copies of 256 B (a channel row each; the staging tile is padded), two per
-    // lane, into HBM or -- ring mode -- straight into the consumer GPU's slot.  Ring mode then counts the row into the
+    // One finished sample leaves as ONE 16 KB bulk copy into HBM or -- ring mode -- straight into the consumer GPU's slot.  Ring mode then counts the row into the
     // message's ticket; whoever counts the last row publishes the message (one system-scope release per message).
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
@@ -576,13 +574,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         if (span.data) while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the slot must have been released by the consumer
       }
       __syncwarp();
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int c = lane + 32 * k;
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row + c * 64),
-                     "r"(smem_u32(&s.out[c * OUT_PITCH])), "r"(256) : "memory");
+      if (lane == 0) {
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out)),
+                     "r"(64 * 64 * 4) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       cifar_tc::bulk_wait_read();
       __syncwarp();
       if (lane == 0) st_release_cta(&s.out_free, (int)n + 1);

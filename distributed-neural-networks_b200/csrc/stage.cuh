@@ -37,6 +37,7 @@ struct b2p_stage {
   float* w2t = nullptr;             // [288][64]
   unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's [W_hi ; W_lo] tiles, one per tap (split fp16)
   unsigned char* a1img = nullptr;   // tensor-core modes: conv1 as pool-window GEMM, A tiles hi | lo (cifar_tc2.cuh)
+  unsigned char* w2tap8 = nullptr;  // ... and its tap 8 as a shared-memory tile image
   uint32_t* w2tm = nullptr;         // tensor-core modes: tensor-memory image of conv2's [W_hi ; W_lo], taps 0..7
   long long* trace = nullptr;       // optional kernel timeline buffer (b2p_stage_trace)
   // ---- CIFAR part 1 ----

@@ -14,3 +14,4 @@ try:
 except Exception as e:
     print('no bench', e)
 PY
+timeout 120 python scripts/trace_part0.py 1024 > gpurun_out/p0_trace.log 2>&1; grep -E "^n=[23] " gpurun_out/p0_trace.log
