@@ -720,13 +720,13 @@ int b2p_stage_trace(b2p_stage* st, long long* host_out, int n) {
   if (!st || !host_out || n < 256) return fail(B2P_EINVAL, "trace buffer must hold at least 256 entries");
   DeviceGuard g(st->d.device);
   if (!st->trace) {
-    B2P_CUDA(cudaMalloc((void**)&st->trace, 256 * sizeof(long long)));
-    B2P_CUDA(cudaMemset(st->trace, 0, 256 * sizeof(long long)));
+    B2P_CUDA(cudaMalloc((void**)&st->trace, 1024 * sizeof(long long)));
+    B2P_CUDA(cudaMemset(st->trace, 0, 1024 * sizeof(long long)));
     memset(host_out, 0, 256 * sizeof(long long));
     return 0;
   }
   B2P_CUDA(cudaDeviceSynchronize());
-  B2P_CUDA(cudaMemcpy(host_out, st->trace, 256 * sizeof(long long), cudaMemcpyDeviceToHost));
+  B2P_CUDA(cudaMemcpy(host_out, st->trace, (size_t)std::min(n, 1024) * sizeof(long long), cudaMemcpyDeviceToHost));
   return 0;
 }
 

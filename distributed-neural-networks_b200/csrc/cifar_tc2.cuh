@@ -59,8 +59,8 @@ constexpr uint32_t TM_D2 = 128;                       // conv2 accumulator of on
 constexpr uint32_t TM_D1 = 384;                       // conv1 accumulator of one half sample: 128 columns
 
 constexpr int ACT_ROW_BYTES = 2048;                   // one image row of one copy: 2 groups x (8 hi rows + 8 lo rows) x 64 B
-constexpr int ACT_COPY_BYTES = 18 * ACT_ROW_BYTES;    // rows -1..16
-constexpr int ACT_BYTES = 3 * ACT_COPY_BYTES;         // 110 592
+constexpr int ACT_COPY_BYTES = 17 * ACT_ROW_BYTES;    // rows -1..15; the zero row 16 of a copy is row -1 of the next one
+constexpr int ACT_BYTES = (3 * 17 + 1) * ACT_ROW_BYTES;   // 106 496
 constexpr int PLANE_BYTES = 128 * 128;                // a 128-row operand tile with 128-byte rows
 constexpr int W2T_WORDS = 128;                        // tensor-memory image of conv2's weights: 32-bit words per row
 
@@ -241,6 +241,9 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     bulk_g2s(s.a1 + PLANE_BYTES, a1img + PLANE_BYTES, PLANE_BYTES, &s.bar_w);
     bulk_g2s(s.w2tap8, w2tap8, cifar_tc::W2_TAP_BYTES, &s.bar_w);
   }
+  // (Requesting these 512 bytes per thread at the top of the kernel, to hide their latency behind the rest of the
+  //  set-up, was measured SLOWER by 3.9 us per launch: 64 more live registers in the prologue change the allocation of
+  //  the whole kernel, which runs at its 80-register limit.)
   if (tid < 128) {                                         // conv2's A, taps 0..7 -> tensor memory: thread = row = lane
     const uint4* src = reinterpret_cast<const uint4*>(w2t + (size_t)tid * W2T_WORDS);
     const uint32_t row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + TM_A2;

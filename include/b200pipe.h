@@ -161,8 +161,10 @@ B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
 B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 
 /* Developer aid (no reference counterpart): the first call arms a per-stage trace buffer,
- * later calls synchronise and copy out 256 clock64 stamps of CTA 0 of the CIFAR part-0
- * tensor-core kernel ([role 0..2][sample 0..7][event 0..7], entry 192 = end of set-up). */
+ * later calls synchronise and copy out min(n, 1024) stamps of the CIFAR part-0 tensor-core
+ * kernel: clock64 of CTA 0 as [role 0..3][sample 0..7][event 0..7] (entry 192 = end of set-up,
+ * 250..254 = entry / exit), and from entry 256 on the %globaltimer entry and exit time of every
+ * CTA (2 entries each).  n >= 256. */
 B2P_API int b2p_stage_trace(b2p_stage* st, long long* host_out, int n);
 
 /* Developer aid (no reference counterpart): clock64 timeline of CTA (0,0,0) of the last tensor-core
