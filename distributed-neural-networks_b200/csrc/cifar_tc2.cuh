@@ -25,12 +25,11 @@
 //          The epilogue pools across the 4 lanes of a channel with lane-swapping shuffles, transposes 8x8 across
 //          lanes and writes the fp16 hi/lo activation rows for conv2.
 //
-// Warp roles (23 warps, one persistent CTA per SM, samples blockIdx.x, +gridDim.x, ...).  The SM's warp arbiter
-// favours high warp ids, so the roles whose latency the tensor pipe waits for come last:
-//   0..3     conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo)
+// Warp roles (20 warps, one persistent CTA per SM, samples blockIdx.x, +gridDim.x, ...):
+//   0..1     conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo)
+//   2        publisher: bulk copy of the finished sample to HBM or straight into the next GPU's ring slot (+ ring handshake)
+//   3        MMA issuer
 //   4..19    epilogue warps: drain conv2's accumulator (-> staging tile) and run conv1's epilogue, alternately
-//   20       ring acquirer         21      publisher: bulk copies of the finished sample to HBM or straight into the
-//   22       MMA issuer                    next GPU's ring slot
 //
 // Arithmetic and range are those of round 1's kernel: x ~= hi + lo * 2^-11 with fp16 hi/lo, products exact in the
 // fp32 accumulator, the lo*lo term dropped.  |input| and |conv1 output| must stay below 65504 (fp16 range); beyond
@@ -48,10 +47,10 @@ using cifar_tc::make_desc_sw64;
 using cifar_tc::make_idesc_f16;
 using cifar_tc::named_bar;
 
-constexpr int kPatchWarp0 = 0, kPatchThreads = 128;
+constexpr int kPatchWarp0 = 0, kPatchThreads = 64;
+constexpr int kPubWarp = 2, kMmaWarp = 3;
 constexpr int kE1Warp0 = 4, kEpiWarps = 16;           // epilogue warps 4..19
-constexpr int kAcqWarp = 20, kPubWarp = 21, kMmaWarp = 22;
-constexpr int kThreads = 23 * 32;                     // 736
+constexpr int kThreads = 20 * 32;                     // 640 threads: 96 registers each (at 736 threads the 80-register limit decided everything)
 
 // tensor-memory map (512 columns)
 constexpr uint32_t TM_A2 = 0;                         // conv2 weights, taps 0..7: 8 taps x 2 K-steps x 8 columns
@@ -75,7 +74,7 @@ struct Smem {
   uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
       bar_d2_full, bar_d2_empty;
   uint32_t tmem_slot;
-  int acq_upto, staged, out_free;                     // ring / staging hand-offs (see cifar_tc.cuh)
+  int staged, out_free;                               // staging hand-offs between the epilogue warps and the publisher
 };
 constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
 static_assert(SMEM_BYTES <= 232448, "shared memory budget of one CTA on sm_100");
@@ -211,11 +210,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
   if (tid < 32) s.b1[tid] = b1[tid];
   if (tid >= 32 && tid < 96) s.b2[tid - 32] = b2[tid - 32];
-  if (tid == 0) { s.acq_upto = 0; s.staged = 0; s.out_free = 0; }
+  if (tid == 0) { s.staged = 0; s.out_free = 0; }
   if (warp == kMmaWarp) {
     if (lane == 0) {
       mbar_init(&s.bar_w, 1);
-      mbar_init(&s.bar_patch_full, 4);
+      mbar_init(&s.bar_patch_full, kPatchThreads / 32);
       mbar_init(&s.bar_patch_empty, 1);
       mbar_init(&s.bar_d1_full, 1);
       mbar_init(&s.bar_d1_empty, kEpiWarps);
@@ -339,23 +338,23 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       }
     }
     __syncwarp();
-  } else if (warp < kE1Warp0) {
+  } else if (warp < kPubWarp) {
     // =========================== conv1 patch producers ================================================================
     // thread = pooled pixel of the current half; per channel its 4x4 input window becomes 16 K-values (32 B hi, 32 B lo)
-    const int t = tid - kPatchWarp0 * 32;                    // 0..127
-    const int pr = t >> 4, pc = t & 15;
-    float4 pre[6];
+    const int t = tid - kPatchWarp0 * 32;                    // 0..63: pooled pixels t and t + 64 of the half
+    constexpr int NLD = 768 / kPatchThreads;                 // float4 loads per thread and image
+    float4 pre[NLD];
     if ((int)blockIdx.x < batch) {
       const float4* xin = reinterpret_cast<const float4*>(x + (size_t)blockIdx.x * 3072);
 #pragma unroll
-      for (int j = 0; j < 6; ++j) pre[j] = ld_produced(xin + t + 128 * j);
+      for (int j = 0; j < NLD; ++j) pre[j] = ld_produced(xin + t + kPatchThreads * j);
     }
     uint32_t n = 0;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       named_bar(1, kPatchThreads);                           // the previous sample's window reads are done
 #pragma unroll
-      for (int j = 0; j < 6; ++j) {
-        const int e = (t + 128 * j) * 4;
+      for (int j = 0; j < NLD; ++j) {
+        const int e = (t + kPatchThreads * j) * 4;
         float* d = &s.in[e >> 10][((e >> 5) & 31) + 1][(e & 31) + 1];
         d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
       }
@@ -364,30 +363,33 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       if (b + (int)gridDim.x < batch) {                      // next image: in flight while this one is processed
         const float4* xin = reinterpret_cast<const float4*>(x + (size_t)(b + gridDim.x) * 3072);
 #pragma unroll
-        for (int j = 0; j < 6; ++j) pre[j] = ld_produced(xin + t + 128 * j);
+        for (int j = 0; j < NLD; ++j) pre[j] = ld_produced(xin + t + kPatchThreads * j);
       }
 #pragma unroll 1
       for (uint32_t h = 0; h < 2; ++h) {
         const uint32_t k1 = 2 * n + h;
         mbar_wait(&s.bar_patch_empty, (k1 & 1) ^ 1);         // the MMAs that read the previous half's patches are done
         B2P_TRACE2(3, n, 2 + 2 * h, t == 0);
-        const int py = 8 * h + pr;
-        unsigned char* row_hi = s.patch + t * 128;
+#pragma unroll 1
+        for (int i = t; i < 128; i += kPatchThreads) {       // pooled pixel i of this half
+          const int py = 8 * h + (i >> 4), pc = i & 15;
+          unsigned char* row_hi = s.patch + i * 128;
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          uint32_t hi[8], lo[8];
+          for (int c = 0; c < 3; ++c) {
+            uint32_t hi[8], lo[8];
 #pragma unroll
-          for (int r = 0; r < 4; ++r) {
-            const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * pc]);
-            const float2 a = rp[0], bq = rp[1];
-            split2(a.x, a.y, hi[2 * r], lo[2 * r]);
-            split2(bq.x, bq.y, hi[2 * r + 1], lo[2 * r + 1]);
-          }
+            for (int r = 0; r < 4; ++r) {
+              const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * pc]);
+              const float2 a = rp[0], bq = rp[1];
+              split2(a.x, a.y, hi[2 * r], lo[2 * r]);
+              split2(bq.x, bq.y, hi[2 * r + 1], lo[2 * r + 1]);
+            }
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {             // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
-            const int off = ((2 * c + half) ^ (t & 7)) * 16;
-            *reinterpret_cast<uint4*>(row_hi + off) = make_uint4(hi[4 * half], hi[4 * half + 1], hi[4 * half + 2], hi[4 * half + 3]);
-            *reinterpret_cast<uint4*>(row_hi + PLANE_BYTES + off) = make_uint4(lo[4 * half], lo[4 * half + 1], lo[4 * half + 2], lo[4 * half + 3]);
+            for (int half = 0; half < 2; ++half) {           // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
+              const int off = ((2 * c + half) ^ (i & 7)) * 16;
+              *reinterpret_cast<uint4*>(row_hi + off) = make_uint4(hi[4 * half], hi[4 * half + 1], hi[4 * half + 2], hi[4 * half + 3]);
+              *reinterpret_cast<uint4*>(row_hi + PLANE_BYTES + off) = make_uint4(lo[4 * half], lo[4 * half + 1], lo[4 * half + 2], lo[4 * half + 3]);
+            }
           }
         }
         fence_proxy_async();                                 // generic-proxy writes -> async proxy (UMMA)
@@ -396,7 +398,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         B2P_TRACE2(3, n, 3 + 2 * h, t == 0);
       }
     }
-  } else if (warp < kAcqWarp) {
+  } else if (warp >= kE1Warp0) {
     // =========================== epilogue warps (16): conv2 drain and conv1 epilogue in the tensor pipe's order =========
     // The MMA stream is  Q2(n,0) C1(n+1,0) Q2(n,1) C1(n+1,1) ...  and conv2 has ONE accumulator, so the time to drain it
     // is what the tensor pipe waits for.  All 16 warps therefore drain it together (E2, one image-row pair each), and
@@ -537,59 +539,45 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         B2P_TRACE2(1, n, 3, tracer);
       }
     }
-  } else if (warp == kAcqWarp) {
-    // =========================== handoff-ring acquirer (ring_hooks.cuh; as in cifar_tc.cuh) ==========================
-    if (span.data && lane == 0) {
+  } else {
+    // =========================== publisher (+ ring handshake, ring_hooks.cuh) =========================================
+    // One finished sample leaves as ONE 16 KB bulk copy into HBM or -- ring mode -- straight into the consumer GPU's slot.
+    // Ring mode: before the copy the slot must have been released by the consumer; ONE CTA per message -- the one that
+    // holds the message's first row -- polls the consumer's counter over NVLink and posts what it saw in local memory,
+    // the others wait on that local word (sys-scope reads of one remote line serialise).  After the copy the row is
+    // counted into the message's ticket; whoever counts the last row publishes the message (one system-scope release).
+    if (lane == 0) {
       int acquired = -1;
       uint32_t n = 0;
       for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
-        const int msg = b / span.rows_per_msg, slot = span_slot(span, msg);
-        if (msg != acquired) {
-          const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
-          if (k > 0) {
-            if (b == msg * span.rows_per_msg) {                          // one CTA per message polls over NVLink
-              spin_until_ge_remote(span.released + slot, k);
-              st_release_gpu(span.acq_seen + slot, k);
-            } else {
-              while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
+        float* dst_row = out + (size_t)b * 4096;
+        int msg = 0, slot = 0;
+        if (span.data) {
+          msg = b / span.rows_per_msg;
+          slot = span_slot(span, msg);
+          dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
+          if (msg != acquired) {
+            const unsigned long long k = ld_count(span.count + slot);    // messages already published into this slot
+            if (k > 0) {
+              if (b == msg * span.rows_per_msg) {
+                spin_until_ge_remote(span.released + slot, k);
+                st_release_gpu(span.acq_seen + slot, k);
+              } else {
+                while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
+              }
             }
+            acquired = msg;
           }
-          acquired = msg;
         }
-        st_release_cta(&s.acq_upto, (int)n + 1);
-      }
-    }
-  } else {
-    // =========================== publisher ==============================================================================
-    // One finished sample leaves as ONE 16 KB bulk copy into HBM or -- ring mode -- straight into the consumer GPU's slot.  Ring mode then counts the row into the
-    // message's ticket; whoever counts the last row publishes the message (one system-scope release per message).
-    uint32_t n = 0;
-    for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
-      float* dst_row = out + (size_t)b * 4096;
-      int msg = 0, slot = 0;
-      if (span.data) {
-        msg = b / span.rows_per_msg;
-        slot = span_slot(span, msg);
-        dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
-      }
-      if (lane == 0) {
         while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
-        if (span.data) while (ld_acquire_cta(&s.acq_upto) <= (int)n) { }     // the slot must have been released by the consumer
-      }
-      __syncwarp();
-      if (lane == 0) {
         asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out)),
                      "r"(64 * 64 * 4) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      }
-      cifar_tc::bulk_wait_read();
-      __syncwarp();
-      if (lane == 0) st_release_cta(&s.out_free, (int)n + 1);
-      if (span.data) {
-        cifar_tc::bulk_wait_all();
-        __threadfence();
-        __syncwarp();
-        if (lane == 0) {
+        cifar_tc::bulk_wait_read();
+        st_release_cta(&s.out_free, (int)n + 1);
+        if (span.data) {
+          cifar_tc::bulk_wait_all();
+          __threadfence();
           const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
           if (atomicAdd(span.tickets + slot, 1) == rows - 1) {
             span.tickets[slot] = 0;                             // ready for the slot's next message
@@ -600,8 +588,9 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           }
         }
       }
+      cifar_tc::bulk_wait_all();
     }
-    cifar_tc::bulk_wait_all();
+    __syncwarp();
   }
 
   tc_fence_before();
