@@ -68,7 +68,7 @@ struct Smem {
   unsigned char patch[2 * PLANE_BYTES];               // conv1's B operand: [hi | lo][128 pooled pixels][128 B], 96 B used
   unsigned char a1[2 * PLANE_BYTES];                  // conv1's A operand: [hi | lo][128 rows (oc,dy,dx)][128 B]
   unsigned char w2tap8[cifar_tc::W2_TAP_BYTES];       // conv2 tap 8: 128 rows (2c | 2c+1 = hi | lo of channel c) of 64 B, 64B-swizzled
-  float out[64 * 64];                                 // one finished sample in flatten order, [channel][h*8+w]
+  float out[2][64 * 64];                              // finished samples in flatten order [channel][h*8+w], double-buffered
   float in[3][34][34];                                // zero-padded input image
   float b1[32], b2[64];
   uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
@@ -474,9 +474,10 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_act_ready[h]);
     };
-    // conv2 drain of one image-row pair: the odd lanes hand W_lo*a_hi to the even lane below (one shuffle per value);
-    // the even lanes add the three terms, pool 2x2 inside the thread, add the bias, apply ReLU, store 4 outputs
-    auto e2_drain = [&](uint32_t n, uint32_t h) {
+    // conv2 drain, first part: TMEM -> registers, accumulator released at once.  Kept per pixel: the even lanes'
+    // W_hi*a_hi + 2^-11 W_hi*a_lo, the odd lanes' 2^-11 W_lo*a_hi (32 values for 2 rows x 16 pixels).
+    float dv[4][8];
+    auto e2_load = [&](uint32_t n, uint32_t h) {
       mbar_wait(&s.bar_d2_full, (2 * n + h) & 1);
       tc_fence_after();
       uint32_t r[4][16];
@@ -489,25 +490,34 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_d2_empty);             // the accumulator may be overwritten (other half's MMAs)
-      if (h == 0 && n > 0) {                                   // the previous sample's bulk copy must be done reading `out`
-        while (ld_acquire_cta(&s.out_free) < (int)n) { }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float lo_or_0 = even ? __uint_as_float(r[k][8 + j]) : 0.f;       // odd lanes: their lo columns are not used
+          dv[k][j] = fmaf(lo_or_0, 1.0f / 2048.0f, __uint_as_float(r[k][j]) * (even ? 1.0f : 1.0f / 2048.0f));
+        }
+    };
+    // second part: the odd lanes hand their term to the even lane below (one shuffle per value); the even lanes pool 2x2
+    // inside the thread, add the bias, apply ReLU and store 4 consecutive outputs of the flatten order
+    auto e2_finish = [&](uint32_t n, uint32_t h) {
+      if (h == 0 && n > 1) {                                   // the bulk copy of sample n-2 must be done reading this buffer
+        while (ld_acquire_cta(&s.out_free) < (int)n - 1) { }
       }
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
         float v0[8], v1[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const float x0 = __shfl_down_sync(0xffffffffu, __uint_as_float(r[2 * g][j]), 1);
-          const float x1 = __shfl_down_sync(0xffffffffu, __uint_as_float(r[2 * g + 1][j]), 1);
-          v0[j] = fmaf(__uint_as_float(r[2 * g][8 + j]) + x0, 1.0f / 2048.0f, __uint_as_float(r[2 * g][j]));
-          v1[j] = fmaf(__uint_as_float(r[2 * g + 1][8 + j]) + x1, 1.0f / 2048.0f, __uint_as_float(r[2 * g + 1][j]));
+          v0[j] = dv[2 * g][j] + __shfl_down_sync(0xffffffffu, dv[2 * g][j], 1);
+          v1[j] = dv[2 * g + 1][j] + __shfl_down_sync(0xffffffffu, dv[2 * g + 1][j], 1);
         }
         float4 o4;
         float* op = &o4.x;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           op[j] = max_nan(max_nan(max_nan(v0[2 * j], v0[2 * j + 1]), max_nan(v1[2 * j], v1[2 * j + 1])) + bias2, 0.f);
-        if (even) *reinterpret_cast<float4*>(&s.out[oc2 * 64 + (4 * h + part) * 8 + 4 * g]) = o4;
+        if (even) *reinterpret_cast<float4*>(&s.out[n & 1][oc2 * 64 + (4 * h + part) * 8 + 4 * g]) = o4;
       }
     };
 
@@ -520,17 +530,15 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     for (int n = 0; n < n_samples; ++n) {
       const bool more = n + 1 < n_samples;
       B2P_TRACE2(2, n, 0, tracer);
-      e2_drain(n, 0);
+      e2_load(n, 0);
+      e2_finish(n, 0);
       B2P_TRACE2(2, n, 1, tracer);
       if (more) e1_read(2 * (n + 1));                          // held in registers: Q2(n,1) still reads the activation
       B2P_TRACE2(1, n, 0, tracer);
-      e2_drain(n, 1);
+      e2_load(n, 1);                                           // Q2(n,1) has completed: the accumulator first ...
       B2P_TRACE2(2, n, 2, tracer);
-      fence_proxy_async();                                     // this thread's writes to `out` -> visible to the copy engine
-      named_bar(2, 16 * 32);                                   // all 4096 outputs are staged
-      if (tracer) st_release_cta(&s.staged, n + 1);
-      if (more) {
-        mbar_wait(&s.bar_act_free, n & 1);                     // Q2(n,1) has completed (it had: its drain is done)
+      if (more) {                                              // ... then the activation rows the next Q2 is waiting for
+        mbar_wait(&s.bar_act_free, n & 1);                     // (passes at once: committed together with d2_full)
         e1_write(0);
         B2P_TRACE2(1, n, 1, tracer);
         e1_read(2 * (n + 1) + 1);
@@ -538,6 +546,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         e1_write(1);
         B2P_TRACE2(1, n, 3, tracer);
       }
+      e2_finish(n, 1);
+      fence_proxy_async();                                     // this thread's writes to `out` -> visible to the copy engine
+      named_bar(2, 16 * 32);                                   // all 4096 outputs are staged
+      if (tracer) st_release_cta(&s.staged, n + 1);
+      B2P_TRACE2(2, n, 3, tracer);
     }
   } else {
     // =========================== publisher (+ ring handshake, ring_hooks.cuh) =========================================
@@ -570,7 +583,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           }
         }
         while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out)),
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out[n & 1])),
                      "r"(64 * 64 * 4) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         cifar_tc::bulk_wait_read();
