@@ -374,7 +374,7 @@ def engine_arm(args):
     except Exception:
         pass
     peak_tf = peaks["bf16_tflops_sustained"]
-    roofline = {"kernel": f"part0_tc (conv1+ReLU+pool+conv2+ReLU+pool), one launch per step = {BATCH} samples",
+    roofline = {"kernel": f"part0_tc2 (conv1+ReLU+pool+conv2+ReLU+pool, both convolutions on tcgen05), one launch per step = {BATCH} samples",
                 "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
                 "traffic": traffic, "peak_source": f"bf16_tflops_sustained of {peaks_kind}",
                 "us_per_launch": us_k0, "launches_timed": KR, "algorithmic_bytes_per_launch": BYTES_PART0 * BATCH,
@@ -398,6 +398,20 @@ def engine_arm(args):
                "sample": f"{r['requests']} requests of {r['batch']} samples through {r['what']} of the "
                          f"2-node localhost gRPC pipeline ({r['total_s']:.1f} s, torch threads {r['torch_threads']})"}
 
+    gpt = None
+    if not args.no_gpt:                                      # BASELINE config 3's model on this one GPU (reported beside the metric)
+        try:
+            rp = import_module("distributed-neural-networks_b200.rank_pipeline")
+            del pipe, parts, dev_pool
+            torch.cuda.empty_cache()
+            sampler2 = ClockSampler(sampler.index)
+            sampler2.start(); sampler2.active.set()
+            gpt = rp.gpt_bench(1, 0, dev, peaks)
+            sampler2.active.clear()
+            gpt["clocks"] = sampler2.finish()
+        except Exception as e:
+            gpt = {"error": f"{type(e).__name__}: {e}"}
+
     line = {
         "metric": METRIC, "value": BATCH * K / (ms_dev * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": ms_dev / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -418,7 +432,7 @@ def engine_arm(args):
         "front_door_grpc": front,
         "roofline_stage1": roofline_stage1,
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-        "torch_eager_gpu": eager,
+        "torch_eager_gpu": eager, "gpt": gpt,
     }
     print(json.dumps(line))
     return 0
@@ -434,6 +448,7 @@ def main():
                     help="tf32x3 (default): tensor-core parity mode, fp32-grade (split-fp16 conv2, 3xTF32 fc1); "
                          "fp32: CUDA-core reference mode; tf32: single-pass fc1")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpt", action="store_true", help="skip the GPT part chain reported under the `gpt` key")
     ap.add_argument("--no-graph", action="store_true", help="launch kernel by kernel instead of replaying CUDA graphs")
     args = ap.parse_args()
     return reference_arm(args) if args.impl == "reference" else engine_arm(args)

@@ -147,7 +147,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else if (!part0_v1())   // both convolutions on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH_PDL_BIT(2, cifar_tc2::part0_tc2, grid, cifar_tc2::kThreads, cifar_tc2::SMEM_BYTES, s, in, st->a1img, st->w2tm,
-                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->trace, span);
+                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->bad_flag, st->trace, span);
   else   // round 1's kernel (conv1 on the CUDA cores), kept for A/B measurements: B2P_PART0_V1=1
   {
     cifar_tc::Conv1Const c1;
@@ -525,6 +525,9 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
     if (rc < 0) { b2p_stage_destroy(st); return rc; }
   }
   if (desc->kind == B2P_CIFAR_PART0) {
+    int rc = dev_alloc(&st->bad_flag, 1);                       // "a value left the split-fp16 range" (cifar_tc2.cuh)
+    if (rc == 0 && cudaMemset(st->bad_flag, 0, sizeof(int)) != cudaSuccess) rc = fail(B2P_ECUDA, "cudaMemset(range flag)");
+    if (rc < 0) { b2p_stage_destroy(st); return rc; }
     // per-device function attribute: set with the stage's device current
     cudaError_t e = cudaFuncSetAttribute(part0_fused_f32, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sizeof(Part0Smem));
@@ -748,6 +751,11 @@ int b2p_stage_check(b2p_stage* st, void* stream) {
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   B2P_CUDA(cudaMemcpyAsync(&flag, st->bad_flag, sizeof(int), cudaMemcpyDeviceToHost, s));
   B2P_CUDA(cudaStreamSynchronize(s));
+  if (flag && st->d.kind == B2P_CIFAR_PART0) {
+    B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));
+    return fail(B2P_ELIMIT, "an input or conv1 output reached the fp16 range limit (|v| >= 65504) of the tensor-core math "
+                            "modes: the affected samples are not finite where the reference's are; use math=fp32 for such data");
+  }
   if (flag) {
     B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));
     return fail(B2P_EINVAL, "index out of range in self: a token id was outside [0, vocab_size=%d)", st->d.vocab_size);

@@ -92,8 +92,8 @@ part0_fused_f32(const float* __restrict__ x,      // [B,3,32,32]
               a10 = fmaf(win[c][kh + 1][kw], w, a10);
               a11 = fmaf(win[c][kh + 1][kw + 1], w, a11);
             }
-        float m = fmaxf(fmaxf(a00, a01), fmaxf(a10, a11));
-        s.a1[oc][py + 1][px + 1] = fmaxf(m, 0.f);      // relu(max) == max(relu)
+        float m = fmax_nan(fmax_nan(a00, a01), fmax_nan(a10, a11));
+        s.a1[oc][py + 1][px + 1] = fmax_nan(m, 0.f);      // relu(max) == max(relu)
       }
     }
     __syncthreads();
@@ -140,8 +140,8 @@ part0_fused_f32(const float* __restrict__ x,      // [B,3,32,32]
       float* o = out + (size_t)b * 4096 + p;
 #pragma unroll
       for (int j = 0; j < 16; ++j) {
-        float m = fmaxf(fmaxf(acc[0][j], acc[1][j]), fmaxf(acc[2][j], acc[3][j]));
-        o[(og * 16 + j) * 64] = fmaxf(m, 0.f);           // 32 lanes -> 128 B contiguous
+        float m = fmax_nan(fmax_nan(acc[0][j], acc[1][j]), fmax_nan(acc[2][j], acc[3][j]));
+        o[(og * 16 + j) * 64] = fmax_nan(m, 0.f);          // 32 lanes -> 128 B contiguous
       }
     }
     __syncthreads();     // s.in / s.a1 are rewritten by the next sample
@@ -244,7 +244,7 @@ fc_tail_f32(const float* __restrict__ ws, int M,
 #pragma unroll
     for (int z = 0; z < SPLITS; ++z) { h.x += p[z].x; h.y += p[z].y; h.z += p[z].z; h.w += p[z].w; }   // fixed order
   }
-  h.x = fmaxf(h.x, 0.f); h.y = fmaxf(h.y, 0.f); h.z = fmaxf(h.z, 0.f); h.w = fmaxf(h.w, 0.f);
+  h.x = fmax_nan(h.x, 0.f); h.y = fmax_nan(h.y, 0.f); h.z = fmax_nan(h.z, 0.f); h.w = fmax_nan(h.w, 0.f);   // nn.ReLU keeps NaN
   __shared__ float part[4][10];
   float l[10];
   float4 w[10];

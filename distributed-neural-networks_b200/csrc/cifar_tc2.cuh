@@ -33,8 +33,10 @@
 //
 // Arithmetic and range are those of round 1's kernel: x ~= hi + lo * 2^-11 with fp16 hi/lo, products exact in the
 // fp32 accumulator, the lo*lo term dropped.  |input| and |conv1 output| must stay below 65504 (fp16 range); beyond
-// it the result is non-finite where the reference's would be finite -- use math="fp32" for such data (b200pipe.h).
-// NaN inputs propagate like torch's ReLU / MaxPool2d (max.NaN), not like fmaxf.
+// it the result is non-finite where the reference's would be finite.  The kernel notices (a per-stage device flag,
+// reported by b2p_stage_check as B2P_ELIMIT) -- use math="fp32" for such data (b200pipe.h).
+// NaN inputs propagate like torch's ReLU / MaxPool2d (max.NaN), not like fmaxf; an infinite input comes out as NaN
+// where the reference keeps +-inf (inf * 0 in the zero-padded pool-window weights, inf - inf in the split).
 #pragma once
 #include "cifar_tc.cuh"
 
@@ -74,7 +76,7 @@ struct Smem {
   uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
       bar_d2_full, bar_d2_empty;
   uint32_t tmem_slot;
-  int staged, out_free;                               // staging hand-offs between the epilogue warps and the publisher
+  int staged, out_free[2];                            // staging hand-offs between the epilogue warps and the publisher (per buffer)
 };
 constexpr int SMEM_BYTES = sizeof(Smem) + 1024;
 static_assert(SMEM_BYTES <= 232448, "shared memory budget of one CTA on sm_100");
@@ -196,7 +198,8 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           const unsigned char* __restrict__ w2tap8,       // pack_conv2_tap8: 8 KB
           const float* __restrict__ b1, const float* __restrict__ b2,
           float* __restrict__ out,                        // [B,4096]
-          int batch, long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..3][sample 0..7][event 0..7], entry 192 = end of set-up
+          int batch, int* __restrict__ range_flag,         // set to 1 when a value left the split-fp16 range (b2p_stage_check)
+          long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..3][sample 0..7][event 0..7], entry 192 = end of set-up
           RingSpan span) {                                // span.data: rows go into handoff-ring slots instead of out
 #define B2P_TRACE2(role, n, ev, cond) \
   do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
@@ -210,7 +213,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
   if (tid < 32) s.b1[tid] = b1[tid];
   if (tid >= 32 && tid < 96) s.b2[tid - 32] = b2[tid - 32];
-  if (tid == 0) { s.staged = 0; s.out_free = 0; }
+  if (tid == 0) { s.staged = 0; s.out_free[0] = 0; s.out_free[1] = 0; }
   if (warp == kMmaWarp) {
     if (lane == 0) {
       mbar_init(&s.bar_w, 1);
@@ -350,6 +353,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       for (int j = 0; j < NLD; ++j) pre[j] = ld_produced(xin + t + kPatchThreads * j);
     }
     uint32_t n = 0;
+    float in_max = 0.f;
     for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
       named_bar(1, kPatchThreads);                           // the previous sample's window reads are done
 #pragma unroll
@@ -383,6 +387,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
               const float2 a = rp[0], bq = rp[1];
               split2(a.x, a.y, hi[2 * r], lo[2 * r]);
               split2(bq.x, bq.y, hi[2 * r + 1], lo[2 * r + 1]);
+              in_max = fmaxf(in_max, fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(bq.x), fabsf(bq.y))));
             }
 #pragma unroll
             for (int half = 0; half < 2; ++half) {           // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
@@ -392,6 +397,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
             }
           }
         }
+        if (in_max >= 65504.0f) *range_flag = 1;             // finite input beyond fp16: hi would be inf (NaN input: not flagged)
         fence_proxy_async();                                 // generic-proxy writes -> async proxy (UMMA)
         __syncwarp();
         if (lane == 0) mbar_arrive(&s.bar_patch_full);
@@ -453,6 +459,8 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           if (up) u[i] = recv; else u[i | k] = recv;
         }
       }
+      if (fmaxf(fmaxf(fmaxf(u[0], u[1]), fmaxf(u[2], u[3])), fmaxf(fmaxf(u[4], u[5]), fmaxf(u[6], u[7]))) >= 65504.0f)
+        *range_flag = 1;                                       // a conv1 output beyond fp16: its hi part is inf
       split2(u[0], u[1], chunk_hi.x, chunk_lo.x);
       split2(u[2], u[3], chunk_hi.y, chunk_lo.y);
       split2(u[4], u[5], chunk_hi.z, chunk_lo.z);
@@ -502,7 +510,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     // inside the thread, add the bias, apply ReLU and store 4 consecutive outputs of the flatten order
     auto e2_finish = [&](uint32_t n, uint32_t h) {
       if (h == 0 && n > 1) {                                   // the bulk copy of sample n-2 must be done reading this buffer
-        while (ld_acquire_cta(&s.out_free) < (int)n - 1) { }
+        while (ld_acquire_cta(&s.out_free[n & 1]) < (int)(n >> 1)) { }
       }
 #pragma unroll
       for (int g = 0; g < 2; ++g) {
@@ -559,10 +567,14 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     // holds the message's first row -- polls the consumer's counter over NVLink and posts what it saw in local memory,
     // the others wait on that local word (sys-scope reads of one remote line serialise).  After the copy the row is
     // counted into the message's ticket; whoever counts the last row publishes the message (one system-scope release).
-    if (lane == 0) {
+    // Two lanes share the work, lane l taking the samples whose staging buffer is l: each sample's chain -- copy, its
+    // completion over NVLink, a gpu-scope fence, the ticket -- takes about as long as a sample's arithmetic, so one
+    // thread doing them back to back set the pace of the whole kernel in ring mode.
+    if (lane < 2) {
       int acquired = -1;
       uint32_t n = 0;
       for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
+        if ((n & 1) != (uint32_t)lane) continue;
         float* dst_row = out + (size_t)b * 4096;
         int msg = 0, slot = 0;
         if (span.data) {
@@ -583,11 +595,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           }
         }
         while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out[n & 1])),
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out[lane])),
                      "r"(64 * 64 * 4) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        cifar_tc::bulk_wait_read();
-        st_release_cta(&s.out_free, (int)n + 1);
+        cifar_tc::bulk_wait_read();                             // the staging buffer has been read
+        st_release_cta(&s.out_free[lane], (int)(n >> 1) + 1);
         if (span.data) {
           cifar_tc::bulk_wait_all();
           __threadfence();

@@ -187,6 +187,13 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// torch's ReLU and MaxPool2d propagate NaN (relu(NaN) = NaN); fmaxf would return the other operand
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+}
+
 // exact (erf) GELU, the nn.GELU() default the oracle pins (oracle/gpt_model.py)
 __device__ __forceinline__ float gelu_erf(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));

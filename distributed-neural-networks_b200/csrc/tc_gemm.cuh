@@ -266,7 +266,7 @@ __device__ __forceinline__ void epilogue_tile(const EpiParams& ep, float* stg, c
     }
     if (ep.act == ACT_RELU) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      for (int j = 0; j < 32; ++j) v[j] = fmax_nan(v[j], 0.f);
     } else if (ep.act == ACT_GELU) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = gelu_erf_fast(v[j]);

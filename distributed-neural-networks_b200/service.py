@@ -28,14 +28,27 @@ from . import wire
 
 
 class NodeServiceImpl(wire.NodeServiceServicer):
-    """``run`` maps the request ndarray to the chain's output ndarray (e.g. ``ChainRunner``)."""
+    """``run`` maps the request ndarray to the chain's output ndarray (e.g. ``ChainRunner``).
 
-    def __init__(self, node_ids: Sequence[str], run: Callable[[np.ndarray], np.ndarray]):
+    Wire generality beyond the reference, all off by default so that a reference client sees the
+    reference's bytes:
+      * request dtype strings ``float16``, ``bfloat16`` (payload = bit patterns), ``float64`` and the integer types are
+        accepted and widened / narrowed to what the chain computes in (``ChainRunner``); the reference would feed such
+        a tensor to its fp32 modules and fail inside torch (node.py:45-53);
+      * ``reply_dtype="same"`` answers in the request's dtype (half the bytes for fp16 / bf16 clients);
+      * ``per_row_argmax=True`` appends `` Per-row: [k0, k1, ...]`` to the last node's status: the reference prints the
+        FLAT arg-max of the whole [B,10] array (node.py:61), which for B > 1 is not a class index."""
+
+    def __init__(self, node_ids: Sequence[str], run: Callable[[np.ndarray], np.ndarray], per_row_argmax: bool = False,
+                 reply_dtype: str = "float32"):
         self.node_ids = list(node_ids)          # this node first, then every downstream node
         self.run = run
+        self.per_row_argmax, self.reply_dtype = per_row_argmax, reply_dtype
 
-    def _status(self, prediction: int) -> str:
+    def _status(self, prediction: int, rows=None) -> str:
         status = f"[{self.node_ids[-1]}] Processing complete. Prediction: {prediction}"
+        if rows is not None:
+            status += f" Per-row: {rows}"
         for nid in reversed(self.node_ids[:-1]):
             status = f"[{nid}] Forwarded. Next node status: {status}"
         return status
@@ -44,9 +57,18 @@ class NodeServiceImpl(wire.NodeServiceServicer):
         me = self.node_ids[0]
         try:
             x = wire.tensor_to_ndarray(request.tensor)                      # node.py:45-47
+            if request.tensor.dtype in ("bfloat16", "torch.bfloat16"):
+                x = wire.bfloat16_bits_to_float32(x)
             y = np.ascontiguousarray(self.run(x))
-            status = self._status(int(np.argmax(y)))                        # node.py:61
-            return wire.TensorResponse(status=status, result_tensor=wire.ndarray_to_tensor(y))
+            rows = [int(k) for k in np.argmax(y.reshape(y.shape[0], -1), axis=1)] if self.per_row_argmax and y.ndim >= 2 else None
+            status = self._status(int(np.argmax(y)), rows)                  # node.py:61
+            if self.reply_dtype == "same" and request.tensor.dtype in ("bfloat16", "torch.bfloat16"):
+                result = wire.bfloat16_tensor(y)
+            elif self.reply_dtype == "same" and np.dtype(request.tensor.dtype).kind == "f":
+                result = wire.ndarray_to_tensor(y.astype(np.dtype(request.tensor.dtype)))
+            else:
+                result = wire.ndarray_to_tensor(y)
+            return wire.TensorResponse(status=status, result_tensor=result)
         except Exception as e:                                              # node.py:96-100
             return wire.TensorResponse(status=f"[{me}] Error: {e}")
 
@@ -70,7 +92,12 @@ class ChainRunner:
     def __call__(self, x: np.ndarray) -> np.ndarray:
         torch, p = self.torch, self.pipe
         if x.dtype != self.in_dtype:
-            raise TypeError(f"expected a {self.in_dtype} tensor, got {x.dtype}")
+            # float16 / float64 / integer payloads: converted once, on the host, to the type the chain
+            # computes in -- exact for fp16 -> fp32 and for token ids; never a silent reinterpretation of bytes
+            if x.dtype.kind in "fiu" and self.in_dtype.kind in "fiu" and not (x.dtype.kind == "f" and self.in_dtype.kind != "f"):
+                x = x.astype(self.in_dtype)
+            else:
+                raise TypeError(f"expected a {self.in_dtype} tensor, got {x.dtype}")
         if tuple(x.shape[1:]) != tuple(p.in_shape):
             raise ValueError(f"expected input [B,{','.join(map(str, p.in_shape))}], got {list(x.shape)}")
         outs = []

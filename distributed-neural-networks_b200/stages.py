@@ -222,6 +222,13 @@ class _CifarPart(EngineStage):
     KEYS: tuple = ()
     WHOLE_BATCH_OK = True       # no per-stage workspace bound: a pipeline on one GPU may run the batch in one call
 
+    def check(self):
+        """Synchronise and raise on deferred device-side range errors (b2p_stage_check): part 0 in a tensor-core math
+        mode met a value beyond the fp16 range its hi/lo split can carry."""
+        self._require_device()
+        stream = torch.cuda.current_stream(self._device).cuda_stream
+        _lib.check(_lib.lib().b2p_stage_check(self._handle, C.c_void_p(stream)))
+
     def __init__(self, original_model=None, math: str = "fp32"):
         super().__init__(math)
         if original_model is not None:          # parts start out sharing the full model's weights

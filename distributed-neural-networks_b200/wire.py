@@ -118,8 +118,31 @@ def ndarray_to_tensor(arr: np.ndarray):
 def tensor_to_ndarray(t) -> np.ndarray:
     """node.py:45-47 / :186-189.  Returns a read-only view over the message's
     bytes (the reference then ``.copy()``s it, node.py:48; the engine instead
-    copies straight into pinned staging memory)."""
-    return np.frombuffer(t.tensor_data, dtype=np.dtype(t.dtype)).reshape(tuple(t.shape))
+    copies straight into pinned staging memory).
+
+    One dtype string beyond what ``np.dtype()`` knows is accepted: ``"bfloat16"`` -- numpy has no
+    such type, so the payload comes back as a ``uint16`` array of bit patterns, ``bfloat16_bits_to_float32`` widens it
+    (``str(torch.bfloat16_tensor.dtype)`` is how such a client would label its bytes)."""
+    name = "uint16" if t.dtype in ("bfloat16", "torch.bfloat16") else t.dtype
+    return np.frombuffer(t.tensor_data, dtype=np.dtype(name)).reshape(tuple(t.shape))
+
+
+def bfloat16_bits_to_float32(bits: np.ndarray) -> np.ndarray:
+    """uint16 bit patterns of bfloat16 values -> float32 (exact: bf16 is the top half of an fp32)."""
+    return (bits.astype(np.uint32) << 16).view(np.float32)
+
+
+def float32_to_bfloat16_bits(x: np.ndarray) -> np.ndarray:
+    """float32 -> bfloat16 bit patterns, round to nearest even (NaN stays NaN)."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+    rounded = (u + 0x7FFF + ((u >> 16) & 1)) >> 16
+    return np.where(np.isnan(x), 0x7FC0, rounded).astype(np.uint16)
+
+
+def bfloat16_tensor(x: np.ndarray):
+    """A ``Tensor`` message carrying ``x`` as bfloat16 (payload = bit patterns, dtype string "bfloat16")."""
+    bits = float32_to_bfloat16_bits(x)
+    return Tensor(tensor_data=bits.tobytes(), shape=list(x.shape), dtype="bfloat16")
 
 
 # --------------------------------------------------------------------------- #

@@ -155,9 +155,16 @@ B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
                       int64_t batch, int64_t seq, void* stream);
 
 /* Synchronising health check: waits for `stream`, then reports (and clears) deferred
- * device-side input errors of earlier forwards -- today: a token id outside
- * [0,vocab_size) seen by a GPT first stage (an IndexError in the reference's
- * nn.Embedding, gpt_model_parts.py:17).  Returns 0 when clean. */
+ * device-side input errors of earlier forwards:
+ *   - a token id outside [0,vocab_size) seen by a GPT first stage (an IndexError in the
+ *     reference's nn.Embedding, gpt_model_parts.py:17): B2P_EINVAL;
+ *   - CIFAR part 0 in a tensor-core math mode: a finite input or conv1 output with
+ *     |v| >= 65504.  Those modes carry values as fp16 hi + lo parts, so such a sample comes
+ *     out non-finite where the reference (cifar_model_parts.py:37-42, fp32) stays finite:
+ *     B2P_ELIMIT; math = B2P_MATH_FP32 has the reference's range.  (Un-normalised 0..255
+ *     images with ordinary weights are far inside the range; NaN inputs propagate to NaN
+ *     outputs as in torch and are not flagged; +-inf inputs give NaN, not flagged.)
+ * Returns 0 when clean. */
 B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 
 /* Developer aid (no reference counterpart): the first call arms a per-stage trace buffer,

@@ -257,3 +257,84 @@ def test_tensor_core_microbatching_bit_exact_and_matches_fp32_path(tc_parts, par
     assert torch.equal(whole, pieces)
     assert (a_tc - a_f32).abs().max().item() <= ACT_TOL      # device-side check at full size
     assert (whole - ref).abs().max().item() <= PROB_TOL
+
+
+# ---- edge semantics (VERDICT r1 "edge semantics differ from torch and are untested") ---------------------------------
+def _tc_parts(cuda_engine, sd, math="tf32x3"):
+    full = cuda_engine.NeuralNetwork()
+    out = []
+    for k in (0, 1):
+        p = cuda_engine.MODEL_PARTS_CLASSES[k](full, math=math).to("cuda:0")
+        p.load_state_dict(sd, strict=False)
+        out.append(p.eval())
+    return out
+
+
+@pytest.mark.parametrize("math", ["fp32", "tf32x3"])
+def test_nan_inputs_propagate_like_torch(cuda_engine, math):
+    """nn.ReLU and nn.MaxPool2d propagate NaN (fmaxf would drop it): a NaN pixel poisons exactly the activations the
+    reference's does, every probability of that sample is NaN, and the other samples of the batch are untouched."""
+    sd = co.init_state_dict(1234)
+    p0, p1 = _tc_parts(cuda_engine, sd, math)
+    x = co.make_input(3, seed=41)
+    x[1, 2, 10, 17] = float("nan")
+    want_act, want = co.part0(x, sd), co.full(x, sd)
+    with torch.no_grad():
+        act = p0(x.cuda())
+        probs = p1(act).cpu()
+    act = act.cpu()
+    assert torch.equal(torch.isnan(act), torch.isnan(want_act))           # same poisoned set (conv2 spreads it 3x3)
+    assert torch.isnan(want_act[1]).any() and not torch.isnan(want_act[[0, 2]]).any()
+    ok = ~torch.isnan(want_act)
+    assert (act[ok] - want_act[ok]).abs().max().item() <= ACT_TOL
+    assert torch.isnan(probs[1]).all() and torch.isnan(want[1]).all()
+    assert (probs[[0, 2]] - want[[0, 2]]).abs().max().item() <= PROB_TOL
+    p0.check()                                                            # NaN is data, not a range error
+
+
+def test_unnormalised_images_stay_inside_the_tensor_core_range(cuda_engine):
+    """Raw 0..255 pixel values (a client that skipped node.py:142-147's Normalize): |conv1 output| stays far below the
+    fp16 limit of the split scheme, results agree with the oracle to the same RELATIVE accuracy."""
+    sd = co.init_state_dict(1234)
+    p0, p1 = _tc_parts(cuda_engine, sd, "tf32x3")
+    g = torch.Generator().manual_seed(3)
+    x = torch.randint(0, 256, (64, 3, 32, 32), generator=g).float()
+    want_act, want = co.part0(x, sd), co.full(x, sd)
+    with torch.no_grad():
+        act = p0(x.cuda())
+        probs = p1(act).cpu()
+    scale = want_act.abs().max().item()
+    assert scale > 50                                                     # the activations really are large
+    assert (act.cpu() - want_act).abs().max().item() <= ACT_TOL * scale
+    assert (probs - want).abs().max().item() <= 1e-4                      # logits are O(100): softmax amplifies 1e-5 relative
+    decided = co.top2_margin(want) > 1e-3
+    assert torch.equal(probs.argmax(1)[decided], want.argmax(1)[decided])
+    p0.check()                                                            # no range error
+
+
+def test_fp16_range_of_the_tensor_core_modes_is_guarded(cuda_engine):
+    """conv1 weights x1000 on 0..255 images: conv1 outputs reach ~1e6, beyond what fp16 hi/lo parts can carry
+    (include/b200pipe.h).  The tensor-core mode flags it (b2p_stage_check -> B2P_ELIMIT) instead of returning garbage
+    silently; the fp32 mode has the reference's range and still agrees with the oracle."""
+    sd = {k: v.clone() for k, v in co.init_state_dict(1234).items()}
+    sd["conv1.weight"] *= 1000.0
+    g = torch.Generator().manual_seed(5)
+    x = torch.randint(0, 256, (8, 3, 32, 32), generator=g).float()
+    want_act = co.part0(x, sd)
+    assert torch.isfinite(want_act).all() and want_act.abs().max() > 65504
+    L = cuda_engine._lib
+    p0_tc = _tc_parts(cuda_engine, sd, "tf32x3")[0]
+    with torch.no_grad():
+        p0_tc(x.cuda())
+    with pytest.raises(L.EngineError) as ei:
+        p0_tc.check()
+    assert ei.value.code == L.ELIMIT and "fp16 range" in str(ei.value)
+    p0_tc.check()                                                         # reported once, then clear
+    with torch.no_grad():
+        ok = p0_tc(co.make_input(8, seed=1).cuda() * 1e-3)                # small inputs: back inside the range
+    p0_tc.check()
+    assert torch.isfinite(ok).all()
+    p0_f32 = _tc_parts(cuda_engine, sd, "fp32")[0]
+    with torch.no_grad():
+        act = p0_f32(x.cuda()).cpu()
+    assert (act - want_act).abs().max().item() <= 2e-5 * want_act.abs().max().item()

@@ -160,3 +160,131 @@ def test_cifar_chain_replays_the_reference_recording(cuda_engine, golden_dir, tm
         ch.close()
     finally:
         server.stop(0)
+
+
+def _gpu_chain(cuda_engine, tmp_path, **servicer_kw):
+    import json
+    import torch
+    from oracle import cifar_oracle as co
+    svc = _svc()
+    sd = co.init_state_dict(1234)
+    pth = tmp_path / "w.pth"
+    torch.save(sd, pth)
+    cfg = {"nodes": [{"id": "node1", "address": "127.0.0.1:0", "part_index": 0, "device": 0},
+                     {"id": "node2", "address": "127.0.0.1:0", "part_index": 1, "device": 0}],
+           "model_weights": str(pth), "num_parts": 2, "return_to_node_id": "node1"}
+    cpath = tmp_path / "config.json"
+    cpath.write_text(json.dumps(cfg))
+    topo = cuda_engine.load_config(str(cpath))
+    servicer, pipe = svc.build_cifar_chain(topo, "node1", math="tf32x3", microbatch=128, max_batch=256)
+    for k, v in servicer_kw.items():
+        setattr(servicer, k, v)
+    return svc, sd, servicer, pipe
+
+
+@pytest.mark.gpu
+def test_concurrent_clients_through_the_batching_front_door_on_the_gpu(cuda_engine, tmp_path):
+    """SURVEY 8f-1 on the real CUDA chain: 32 client threads, each with its own images; whatever batch a request
+    happened to travel in, its reply is the oracle's row for ITS image (|d prob| <= 1e-5, arg-max equal)."""
+    import threading
+    import torch
+    from oracle import cifar_oracle as co
+    svc, sd, servicer, pipe = _gpu_chain(cuda_engine, tmp_path)
+    w = cuda_engine.wire
+    runner = svc.BatchingRunner(svc.ChainRunner(pipe), max_rows=128, max_wait_ms=0.5)
+    batched = svc.NodeServiceImpl(["node1", "node2"], runner)
+    server, port = svc.serve(batched, 0, workers=32)
+    n_clients, per_client = 32, 6
+    xs = co.make_input(n_clients * per_client, seed=77)
+    want = co.full(xs, sd).numpy()
+    errs, got = [], {}
+
+    def client(k):
+        try:
+            ch, stub = _client(cuda_engine, port)
+            for j in range(per_client):
+                i = k * per_client + j
+                rep = stub.SendTensor(w.TensorRequest(request_id=f"c{k}_{j}", tensor=w.ndarray_to_tensor(xs[i:i + 1].numpy())),
+                                      timeout=60)
+                assert rep.HasField("result_tensor"), rep.status
+                got[i] = (w.tensor_to_ndarray(rep.result_tensor).copy(), rep.status)
+            ch.close()
+        except Exception as e:
+            errs.append(e)
+
+    ths = [threading.Thread(target=client, args=(k,)) for k in range(n_clients)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(timeout=120)
+    server.stop(0)
+    runner.close()
+    assert not errs, errs[:3]
+    assert len(got) == n_clients * per_client
+    for i, (probs, status) in got.items():
+        assert probs.shape == (1, 10)
+        assert np.abs(probs[0] - want[i]).max() <= 1e-5, i
+        assert status.endswith(f"Prediction: {int(np.argmax(want[i]))}") or np.sort(want[i])[-1] - np.sort(want[i])[-2] < 1e-5
+    assert max(runner.batches) > 1, "no two requests were ever merged: the batching path was not exercised"
+
+
+@pytest.mark.gpu
+def test_initiate_inference_on_a_png_through_the_gpu_chain(cuda_engine, tmp_path):
+    """node.py:137-200 on the real chain: a PNG goes through the reference's preprocessing, both stages on the GPU and
+    the arg-max; compared with the oracle on the very tensor the preprocessing produced."""
+    import torch
+    from PIL import Image
+    from oracle import cifar_oracle as co
+    svc, sd, servicer, pipe = _gpu_chain(cuda_engine, tmp_path)
+    rng = np.random.default_rng(5)
+    png = tmp_path / "img.png"
+    Image.fromarray(rng.integers(0, 256, (48, 40, 3), dtype=np.uint8), "RGB").save(png)
+    pred, probs, real = svc.initiate_inference(servicer, str(png))
+    assert real is True and probs.shape == (1, 10)
+    x, _ = svc.load_input_image(str(png))
+    want = co.full(x, sd).numpy()
+    assert np.abs(probs - want).max() <= 1e-5
+    assert pred == int(np.argmax(want))
+    # the reference's fallback when the file is missing: a random image, flagged as such (node.py:150-153)
+    pred2, probs2, real2 = svc.initiate_inference(servicer, str(tmp_path / "nope.png"), seed=3)
+    x2, _ = svc.load_input_image(None, seed=3)
+    assert real2 is False and np.abs(probs2 - co.full(x2, sd).numpy()).max() <= 1e-5
+
+
+@pytest.mark.gpu
+def test_request_dtypes_and_per_row_argmax_on_the_gpu(cuda_engine, tmp_path):
+    """float16 / bfloat16 / float64 payloads, replies in the request's dtype on demand, per-row arg-max."""
+    import torch
+    from oracle import cifar_oracle as co
+    svc, sd, servicer, pipe = _gpu_chain(cuda_engine, tmp_path, per_row_argmax=True)
+    w = cuda_engine.wire
+    server, port = svc.serve(servicer, 0)
+    try:
+        ch, stub = _client(cuda_engine, port, big=True)
+        x = co.make_input(5, seed=21).numpy()
+        x16 = x.astype(np.float16)
+        xbf = w.bfloat16_bits_to_float32(w.float32_to_bfloat16_bits(x))
+        cases = [("float32", w.ndarray_to_tensor(x), x), ("float16", w.ndarray_to_tensor(x16), x16.astype(np.float32)),
+                 ("float64", w.ndarray_to_tensor(x.astype(np.float64)), x), ("bfloat16", w.bfloat16_tensor(x), xbf)]
+        for name, tensor, seen in cases:
+            assert tensor.dtype == name
+            rep = stub.SendTensor(w.TensorRequest(request_id=name, tensor=tensor))
+            assert rep.HasField("result_tensor"), rep.status
+            got = w.tensor_to_ndarray(rep.result_tensor)
+            want = co.full(torch.from_numpy(seen), sd).numpy()      # the oracle on exactly the values the payload carries
+            assert got.dtype == np.float32 and np.abs(got - want).max() <= 1e-5, name
+            rows = [int(k) for k in want.argmax(1)]
+            assert rep.status.endswith(f"Prediction: {int(np.argmax(want))} Per-row: {rows}"), rep.status
+        servicer.reply_dtype = "same"
+        rep = stub.SendTensor(w.TensorRequest(request_id="h", tensor=w.ndarray_to_tensor(x16)))
+        assert rep.result_tensor.dtype == "float16" and len(rep.result_tensor.tensor_data) == 5 * 10 * 2
+        rep = stub.SendTensor(w.TensorRequest(request_id="b", tensor=w.bfloat16_tensor(x)))
+        assert rep.result_tensor.dtype == "bfloat16"
+        back = w.bfloat16_bits_to_float32(w.tensor_to_ndarray(rep.result_tensor))
+        assert np.abs(back - co.full(torch.from_numpy(xbf), sd).numpy()).max() <= 4e-3      # bf16 rounding of a probability
+        # an int64 image is converted (it is numbers, not bytes to reinterpret); a string dtype is an error, reported in-band
+        bad = stub.SendTensor(w.TensorRequest(request_id="s", tensor=w.Tensor(tensor_data=b"abcd", shape=[1], dtype="S4")))
+        assert bad.status.startswith("[node1] Error:") and not bad.HasField("result_tensor")
+        ch.close()
+    finally:
+        server.stop(0)

@@ -81,3 +81,19 @@ def test_grpc_loopback(engine):
             assert stub.SendMessage(w.MessageRequest(sender_id="a", message_text="hi")).confirmation_text == "got hi"
     finally:
         server.stop(0)
+
+
+def test_bfloat16_payloads(engine):
+    """bfloat16 travels as bit patterns under the dtype string "bfloat16"; conversion is round-to-nearest-
+    even and agrees with torch's."""
+    import torch
+    w = engine.wire
+    x = np.array([0.0, 1.0, -2.5, 3.14159265, 1e-8, 65504.0, float("inf"), 1.00390625, 1.01171875], np.float32)
+    bits = w.float32_to_bfloat16_bits(x)
+    want = torch.from_numpy(x).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+    assert np.array_equal(bits, want)
+    t = w.bfloat16_tensor(x.reshape(3, 3))
+    assert t.dtype == "bfloat16" and list(t.shape) == [3, 3] and len(t.tensor_data) == 18
+    back = w.bfloat16_bits_to_float32(w.tensor_to_ndarray(t))
+    assert np.array_equal(back.reshape(-1), torch.from_numpy(x).to(torch.bfloat16).float().numpy())
+    assert np.isnan(w.bfloat16_bits_to_float32(w.float32_to_bfloat16_bits(np.array([np.nan], np.float32))))[0]
