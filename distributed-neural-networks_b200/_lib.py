@@ -48,6 +48,8 @@ _PROTOTYPES = {
     "b2p_stage_finalize": (C.c_int, [C.c_void_p]),
     "b2p_stage_reserve": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64]),
     "b2p_stage_set_pdl": (C.c_int, [C.c_void_p, C.c_int]),
+    "b2p_stage_set_aux_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b2p_stage_join": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b2p_ring_set_timeout": (C.c_int, [C.c_int, C.c_double]),
     "b2p_ring_check": (C.c_int, [C.c_int]),
     "b2p_stage_out_elems": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.POINTER(C.c_int64)]),

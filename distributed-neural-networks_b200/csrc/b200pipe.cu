@@ -147,7 +147,7 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
                st->dev(3), out, (int)batch);
   else if (!part0_v1())   // both convolutions on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
     B2P_LAUNCH_PDL_BIT(2, cifar_tc2::part0_tc2, grid, cifar_tc2::kThreads, cifar_tc2::SMEM_BYTES, s, in, st->a1img, st->w2tm,
-                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->bad_flag, st->trace, span);
+                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->bad_flag, st->in_limit, st->trace, span);
   else   // round 1's kernel (conv1 on the CUDA cores), kept for A/B measurements: B2P_PART0_V1=1
   {
     cifar_tc::Conv1Const c1;
@@ -184,16 +184,39 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
   if (st->d.math == B2P_MATH_TF32X3 && fc_fused_enabled()) {
     // fc1 with the activation split inside the kernel (fc_stage_tc.cuh), 32 K slices, then the shared tail
     B2P_TRY(ensure_scratch(&st->fc_ws, &st->fc_ws_bytes, fcs::ws_bytes(batch), 1, s, true, "fc1 split-K"));
+    // Two-stream mode (b2p_stage_set_aux_stream): the tail runs on the stage's second stream behind an event, the next
+    // step's fc1 does not wait for it (the partial sums alternate between two buffers), so on a consumer GPU the
+    // 9 us tail of step s hides behind fc1 of step s+1, which is itself waiting for the producer's messages.
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    const bool two_streams = st->aux && cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusNone;
+    float* ws = st->fc_ws;
+    cudaStream_t tail_stream = s;
+    const int buf = (int)(st->fc_step & 1);
+    if (two_streams) {
+      B2P_TRY(ensure_scratch(&st->fc_ws2, &st->fc_ws2_bytes, fcs::ws_bytes(batch), 1, s, false, "fc1 split-K"));
+      if (buf) ws = st->fc_ws2;
+      if (st->ev_tail_recorded[buf]) B2P_CUDA(cudaStreamWaitEvent(s, st->ev_tail[buf], 0));   // tail(s-2) has read this buffer
+      tail_stream = st->aux;
+    }
     const b2p_weight& w = st->w[0];
-    const int parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, st->fc_ws, batch, s, span);
+    const int parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, ws, batch, s, span);
     if (parts < 0) return parts;
+    if (two_streams) {
+      B2P_CUDA(cudaEventRecord(st->ev_fc1, s));
+      B2P_CUDA(cudaStreamWaitEvent(st->aux, st->ev_fc1, 0));
+    }
     const int tail_grid = (int)batch + (span.data ? 1 : 0);
     if (parts == fcs::NSLICES)
-      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, true>), tail_grid, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, true>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
                      st->dev(3), out, span);
     else
-      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 2, false>), tail_grid, 128, 0, s, st->fc_ws, (int)batch, st->dev(1), st->dev(2),
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 2, false>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
                      st->dev(3), out, span);
+    if (two_streams) {
+      B2P_CUDA(cudaEventRecord(st->ev_tail[buf], st->aux));
+      st->ev_tail_recorded[buf] = true;
+      ++st->fc_step;
+    }
     return 0;
   }
   const int splits = tcm ? FC1_SPLITS_TC : fc1_splits(batch);
@@ -549,7 +572,8 @@ int b2p_stage_destroy(b2p_stage* st) {
   DeviceGuard g(st->d.device);
   for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
   cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
-  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->w2tap8); cudaFree(st->trace); cudaFree(st->fc_ws);
+  cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->w2tap8); cudaFree(st->trace); cudaFree(st->fc_ws); cudaFree(st->fc_ws2);
+  if (st->ev_fc1) { cudaEventDestroy(st->ev_fc1); cudaEventDestroy(st->ev_tail[0]); cudaEventDestroy(st->ev_tail[1]); }
   cudaFree(st->ws_ln); cudaFree(st->ws_qkv); cudaFree(st->ws_att); cudaFree(st->ws_h);
   cudaFree(st->ws_x[0]); cudaFree(st->ws_x[1]); cudaFree(st->ws_logits); cudaFree(st->bad_flag);
   delete st;
@@ -618,6 +642,15 @@ int b2p_stage_finalize(b2p_stage* st) {
       // host copy of the transposed conv1 weights + bias: they travel as a kernel parameter (cifar_tc::Conv1Const)
       B2P_CUDA(cudaMemcpy(st->w1_host, st->w1t, 27 * 32 * sizeof(float), cudaMemcpyDeviceToHost));
       B2P_CUDA(cudaMemcpy(st->w1_host + 27 * 32, st->dev(1), 32 * sizeof(float), cudaMemcpyDeviceToHost));
+      // input magnitude from which on a conv1 output can reach the fp16 limit of the split scheme (cifar_tc2.cuh)
+      float wsum = 0.f, bmax = 0.f;
+      for (int oc = 0; oc < 32; ++oc) {
+        float a = 0.f;
+        for (int k = 0; k < 27; ++k) a += fabsf(st->w1_host[k * 32 + oc]);
+        wsum = std::max(wsum, a);
+        bmax = std::max(bmax, fabsf(st->w1_host[27 * 32 + oc]));
+      }
+      st->in_limit = (wsum > 0.f && bmax < 65504.f) ? std::min(65504.f, (65504.f - bmax) / wsum) : (bmax < 65504.f ? 65504.f : 0.f);
     }
   }
   // math-mode copies of the matrices that feed the tensor cores
@@ -659,6 +692,27 @@ int b2p_stage_reserve(b2p_stage* st, int64_t batch, int64_t seq) {
   if (rows > (1LL << 30)) return fail(B2P_ELIMIT, "batch too large");
   DeviceGuard g(st->d.device);
   return reserve_rows(st, rows);
+}
+
+int b2p_stage_set_aux_stream(b2p_stage* st, void* stream) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  if (st->d.kind != B2P_CIFAR_PART1) return fail(B2P_EINVAL, "set_aux_stream: only the CIFAR part-1 stage has a tail kernel to move");
+  DeviceGuard g(st->d.device);
+  if (stream && !st->ev_fc1) {
+    B2P_CUDA(cudaEventCreateWithFlags(&st->ev_fc1, cudaEventDisableTiming));
+    B2P_CUDA(cudaEventCreateWithFlags(&st->ev_tail[0], cudaEventDisableTiming));
+    B2P_CUDA(cudaEventCreateWithFlags(&st->ev_tail[1], cudaEventDisableTiming));
+  }
+  st->aux = static_cast<cudaStream_t>(stream);
+  return 0;
+}
+
+int b2p_stage_join(b2p_stage* st, void* stream) {
+  if (!st) return fail(B2P_EINVAL, "null stage");
+  DeviceGuard g(st->d.device);
+  for (int b = 0; b < 2; ++b)
+    if (st->ev_tail_recorded[b]) B2P_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), st->ev_tail[b], 0));
+  return 0;
 }
 
 int b2p_stage_set_pdl(b2p_stage* st, int mask) {

@@ -33,8 +33,11 @@
 //
 // Arithmetic and range are those of round 1's kernel: x ~= hi + lo * 2^-11 with fp16 hi/lo, products exact in the
 // fp32 accumulator, the lo*lo term dropped.  |input| and |conv1 output| must stay below 65504 (fp16 range); beyond
-// it the result is non-finite where the reference's would be finite.  The kernel notices (a per-stage device flag,
-// reported by b2p_stage_check as B2P_ELIMIT) -- use math="fp32" for such data (b200pipe.h).
+// it the result is non-finite where the reference's would be finite.  The kernel guards the INPUT (a per-stage device
+// flag, reported by b2p_stage_check as B2P_ELIMIT): every input is compared with the magnitude from which on a conv1
+// output could reach the limit, |x| >= (65504 - max|b1|) / max_oc sum|w1[oc]| -- conservative, never misses an overflow,
+// and costs one max per input pixel (checking the conv1 outputs themselves cost 1.5 us per 1024 samples: the conv1
+// epilogue is on the kernel's critical chain).  Use math="fp32" for such data (b200pipe.h).
 // NaN inputs propagate like torch's ReLU / MaxPool2d (max.NaN), not like fmaxf; an infinite input comes out as NaN
 // where the reference keeps +-inf (inf * 0 in the zero-padded pool-window weights, inf - inf in the split).
 #pragma once
@@ -71,7 +74,7 @@ struct Smem {
   unsigned char a1[2 * PLANE_BYTES];                  // conv1's A operand: [hi | lo][128 rows (oc,dy,dx)][128 B]
   unsigned char w2tap8[cifar_tc::W2_TAP_BYTES];       // conv2 tap 8: 128 rows (2c | 2c+1 = hi | lo of channel c) of 64 B, 64B-swizzled
   float out[2][64 * 64];                              // finished samples in flatten order [channel][h*8+w], double-buffered
-  float in[3][34][34];                                // zero-padded input image
+  uint32_t in[3][34][34];                             // zero-padded input image, every pixel already split: fp16 hi | fp16 lo << 16
   float b1[32], b2[64];
   uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
       bar_d2_full, bar_d2_empty;
@@ -198,7 +201,8 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           const unsigned char* __restrict__ w2tap8,       // pack_conv2_tap8: 8 KB
           const float* __restrict__ b1, const float* __restrict__ b2,
           float* __restrict__ out,                        // [B,4096]
-          int batch, int* __restrict__ range_flag,         // set to 1 when a value left the split-fp16 range (b2p_stage_check)
+          int batch, int* __restrict__ range_flag,         // set to 1 when a value may have left the split-fp16 range (b2p_stage_check)
+          float in_limit,                                  // |input| from which on that can happen: min(65504, (65504 - max|b1|) / max_oc sum|w1[oc]|)
           long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..3][sample 0..7][event 0..7], entry 192 = end of set-up
           RingSpan span) {                                // span.data: rows go into handoff-ring slots instead of out
 #define B2P_TRACE2(role, n, ev, cond) \
@@ -208,9 +212,10 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   // ---- one-time set-up (touches only constant weights: runs before pdl_wait) ----------------------------------
+  if (dbg && tid == 0 && blockIdx.x < 256) dbg[256 + 3 * blockIdx.x] = (long long)global_ns();      // entry
   pdl_trigger();
   for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
-  for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0.f;
+  for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0u;
   if (tid < 32) s.b1[tid] = b1[tid];
   if (tid >= 32 && tid < 96) s.b2[tid - 32] = b2[tid - 32];
   if (tid == 0) { s.staged = 0; s.out_free[0] = 0; s.out_free[1] = 0; }
@@ -266,6 +271,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   tc_fence_after();
   if (dbg && blockIdx.x == 0 && tid == 0) dbg[3 * 64] = clock64();      // end of set-up
   if (warp != kMmaWarp) pdl_wait();   // input readers and output writers: both may touch the previous kernel's data
+  if (dbg && tid == 0 && blockIdx.x < 256) dbg[257 + 3 * blockIdx.x] = (long long)global_ns();      // released by the previous kernel
 
   if (warp == kMmaWarp) {
     // =========================== MMA issuer ========================================================================
@@ -359,8 +365,16 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 #pragma unroll
       for (int j = 0; j < NLD; ++j) {
         const int e = (t + kPatchThreads * j) * 4;
-        float* d = &s.in[e >> 10][((e >> 5) & 31) + 1][(e & 31) + 1];
-        d[0] = pre[j].x; d[1] = pre[j].y; d[2] = pre[j].z; d[3] = pre[j].w;
+        // split ONCE per pixel here (every pixel belongs to four pool windows): the window loop below only moves halves
+        uint32_t* d = &s.in[e >> 10][((e >> 5) & 31) + 1][(e & 31) + 1];
+        uint32_t h01, l01, h23, l23;
+        split2(pre[j].x, pre[j].y, h01, l01);
+        split2(pre[j].z, pre[j].w, h23, l23);
+        d[0] = __byte_perm(h01, l01, 0x5410); d[1] = __byte_perm(h01, l01, 0x7632);
+        d[2] = __byte_perm(h23, l23, 0x5410); d[3] = __byte_perm(h23, l23, 0x7632);
+#ifndef B2P_NO_RANGE_CHECK
+        in_max = fmaxf(in_max, fmaxf(fmaxf(fabsf(pre[j].x), fabsf(pre[j].y)), fmaxf(fabsf(pre[j].z), fabsf(pre[j].w))));   // once per pixel
+#endif
       }
       named_bar(1, kPatchThreads);
       B2P_TRACE2(3, n, 1, t == 0);
@@ -383,11 +397,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
             uint32_t hi[8], lo[8];
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-              const float2* rp = reinterpret_cast<const float2*>(&s.in[c][2 * py + r][2 * pc]);
-              const float2 a = rp[0], bq = rp[1];
-              split2(a.x, a.y, hi[2 * r], lo[2 * r]);
-              split2(bq.x, bq.y, hi[2 * r + 1], lo[2 * r + 1]);
-              in_max = fmaxf(in_max, fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(bq.x), fabsf(bq.y))));
+              const uint2* rp = reinterpret_cast<const uint2*>(&s.in[c][2 * py + r][2 * pc]);
+              const uint2 a = rp[0], bq = rp[1];
+              hi[2 * r] = __byte_perm(a.x, a.y, 0x5410);       lo[2 * r] = __byte_perm(a.x, a.y, 0x7632);
+              hi[2 * r + 1] = __byte_perm(bq.x, bq.y, 0x5410); lo[2 * r + 1] = __byte_perm(bq.x, bq.y, 0x7632);
+
             }
 #pragma unroll
             for (int half = 0; half < 2; ++half) {           // 16-byte chunk 2c + half = window rows 2*half, 2*half+1
@@ -397,7 +411,9 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
             }
           }
         }
-        if (in_max >= 65504.0f) *range_flag = 1;             // finite input beyond fp16: hi would be inf (NaN input: not flagged)
+#ifndef B2P_NO_RANGE_CHECK
+        if (in_max >= in_limit) *range_flag = 1;             // see in_limit above (NaN input: not flagged, it is data)
+#endif
         fence_proxy_async();                                 // generic-proxy writes -> async proxy (UMMA)
         __syncwarp();
         if (lane == 0) mbar_arrive(&s.bar_patch_full);
@@ -459,8 +475,6 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           if (up) u[i] = recv; else u[i | k] = recv;
         }
       }
-      if (fmaxf(fmaxf(fmaxf(u[0], u[1]), fmaxf(u[2], u[3])), fmaxf(fmaxf(u[4], u[5]), fmaxf(u[6], u[7]))) >= 65504.0f)
-        *range_flag = 1;                                       // a conv1 output beyond fp16: its hi part is inf
       split2(u[0], u[1], chunk_hi.x, chunk_lo.x);
       split2(u[2], u[3], chunk_hi.y, chunk_lo.y);
       split2(u[4], u[5], chunk_hi.z, chunk_lo.z);
@@ -620,6 +634,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 
   tc_fence_before();
   __syncthreads();
+  if (dbg && tid == 0 && blockIdx.x < 256) dbg[258 + 3 * blockIdx.x] = (long long)global_ns();      // exit
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 #undef B2P_TRACE2
 }

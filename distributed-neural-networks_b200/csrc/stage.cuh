@@ -38,11 +38,19 @@ struct b2p_stage {
   unsigned char* w2img = nullptr;   // tensor-core modes: smem byte image of conv2's [W_hi ; W_lo] tiles, one per tap (split fp16)
   unsigned char* a1img = nullptr;   // tensor-core modes: conv1 as pool-window GEMM, A tiles hi | lo (cifar_tc2.cuh)
   unsigned char* w2tap8 = nullptr;  // ... and its tap 8 as a shared-memory tile image
+  float in_limit = 65504.f;         // |input| from which on a conv1 output may leave the fp16 range (range guard)
   uint32_t* w2tm = nullptr;         // tensor-core modes: tensor-memory image of conv2's [W_hi ; W_lo], taps 0..7
   long long* trace = nullptr;       // optional kernel timeline buffer (b2p_stage_trace)
   // ---- CIFAR part 1 ----
   float* fc_ws = nullptr;           // split-K partials [splits][M][512]
   size_t fc_ws_bytes = 0;
+  // optional second stream for the tail kernel (b2p_stage_set_aux_stream): fc1 of step s+1 then overlaps the tail of step s
+  cudaStream_t aux = nullptr;
+  float* fc_ws2 = nullptr;          // second partial-sum buffer: steps alternate, so fc1(s+1) never writes what tail(s) reads
+  size_t fc_ws2_bytes = 0;
+  cudaEvent_t ev_fc1 = nullptr, ev_tail[2] = {nullptr, nullptr};
+  bool ev_tail_recorded[2] = {false, false};
+  uint64_t fc_step = 0;
 
   // ---- GPT ----
   std::vector<b2p_gpt_block> blocks;

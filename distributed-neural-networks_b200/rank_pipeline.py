@@ -75,6 +75,7 @@ class CifarRankPipeline:
         self.role, self.dev, self.batch, self.mb = role, device, batch, microbatch
         self.n_mb = (batch + microbatch - 1) // microbatch
         self.seq = 0
+        self.two_streams = False
         self.stream = torch.cuda.Stream(device=device)
         self.copy_stream = torch.cuda.Stream(device=device)
         torch.manual_seed(1234)
@@ -99,6 +100,12 @@ class CifarRankPipeline:
         else:
             self.out_dev = torch.empty((batch, 10), device=device)
             self.out_host = torch.empty((batch, 10)).pin_memory()
+            # consumer GPU: the tail kernel of step s on a second stream, hidden behind fc1 of step s+1 (which spends
+            # its time waiting for the producer's messages); launches stay eager here (two kernels per step)
+            self.aux = torch.cuda.Stream(device=device)
+            if math == "tf32x3" and os.environ.get("B2P_NO_AUX_STREAM") != "1":
+                self.part.set_aux_stream(self.aux.cuda_stream)
+                self.two_streams = True
         self.slots = slots
         self._graphs = {}
         self._warm = set()
@@ -134,6 +141,8 @@ class CifarRankPipeline:
         first visit of a key runs eagerly (warm-up, lazy allocations), the second captures and replays."""
         from . import _lib
         assert self.n_mb % self.slots == 0 or self.slots % self.n_mb == 0
+        if self.two_streams:                           # fork/join across replays cannot live inside one captured step
+            return self.step_device(x)
         key = (x.data_ptr() if x is not None else 0, self.seq % self.slots)
         entry = self._graphs.get(key)
         if entry is None:
@@ -189,8 +198,15 @@ class CifarRankPipeline:
                 self.step_graph(None)
             else:
                 self.step_device(None)
-            with torch.cuda.stream(self.stream):
+            # the result is complete on the stream the tail kernel ran on: copy it out from there, so that the next
+            # step's fc1 (on self.stream) is not ordered behind this step's tail
+            with torch.cuda.stream(self.aux if self.two_streams else self.stream):
                 self.out_host.copy_(self.out_dev, non_blocking=True)
+
+    def join(self):
+        """Make this rank's stream wait for tail kernels still running on the second stream."""
+        if self.two_streams:
+            self.part.join(self.stream.cuda_stream)
 
 
 def bench_main(args) -> int:
@@ -236,6 +252,8 @@ def bench_main(args) -> int:
         e0.record(pipe.stream)
         for i in range(K):
             fn(W + i)
+        if role.active:
+            pipe.join()
         e1.record(pipe.stream)
         torch.cuda.synchronize()
         wall = time.perf_counter() - w0
@@ -244,9 +262,10 @@ def bench_main(args) -> int:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
         return float(t[0]), float(t[1])
 
-    use_graph = not getattr(args, "no_graph", False)
-    step = pipe.step_graph if use_graph else pipe.step_device
-    if role.active and use_graph:                      # capture one graph per input buffer (stage 0) / one (stage 1)
+    use_graph = not getattr(args, "no_graph", False)                 # host-facing path
+    dev_graph = getattr(args, "graph_device_path", False)            # device-resident path: eager launches with PDL by default
+    step = pipe.step_graph if dev_graph else pipe.step_device
+    if role.active and dev_graph:                      # capture one graph per input buffer (stage 0) / one (stage 1)
         for i in range(2 * n_pool + 2):
             step(dev_pool[i % n_pool] if dev_pool else None)
         torch.cuda.synchronize()
@@ -271,6 +290,50 @@ def bench_main(args) -> int:
         _, ms_e2e = timed(lambda i: None)
     sampler.active.clear()
     clocks = sampler.finish()
+    # Who limits the 2-stage pipeline?  Each side timed WITHOUT the other in its way: the ring holds two steps of
+    # messages, so the producer can run two steps while the consumer sits still (no back-pressure), and the consumer
+    # can then run its two steps on messages that are all there already (no waiting).
+    torch.cuda.synchronize()
+    dist.barrier()
+    alone = torch.zeros(2, device=dev)
+    if role.active:
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if role.stage == 0:
+            pe0.record(pipe.stream)
+            for i in range(2):
+                pipe.step_device(dev_pool[i % n_pool])
+            pe1.record(pipe.stream)
+            torch.cuda.synchronize()
+            alone[0] = 1e3 * pe0.elapsed_time(pe1) / 2
+    dist.barrier()
+    if role.active and role.stage == 1:
+        pe0.record(pipe.stream)
+        for i in range(2):
+            pipe.step_device(None)
+        pipe.join()
+        pe1.record(pipe.stream)
+        torch.cuda.synchronize()
+        alone[1] = 1e3 * pe0.elapsed_time(pe1) / 2
+    dist.barrier()
+    dist.all_reduce(alone, op=dist.ReduceOp.MAX)
+    if os.environ.get("B2P_TRACE_RING") and rank == 0:       # developer aid: CTA 0's timeline of the ring-mode stage-0 kernel
+        import ctypes as C
+        from . import _lib
+        buf = (C.c_longlong * 1024)()
+        _lib.check(_lib.lib().b2p_stage_trace(pipe.part._handle, buf, 1024))      # arm
+        for i in range(4):
+            pipe.step_device(dev_pool[i % n_pool])
+        torch.cuda.synchronize()
+        _lib.check(_lib.lib().b2p_stage_trace(pipe.part._handle, buf, 1024))
+        t = list(buf)
+        ent = [t[256 + 3 * i] for i in range(148)]; rel = [t[257 + 3 * i] for i in range(148)]; ext = [t[258 + 3 * i] for i in range(148)]
+        e0 = min(ent)
+        us = lambda v: round((v - e0) / 1e3, 1)
+        print(f"ring trace (last launch) entry min/max {us(min(ent))}/{us(max(ent))} released min/max {us(min(rel))}/{us(max(rel))} "
+              f"exit min/median/max {us(min(ext))}/{us(sorted(ext)[74])}/{us(max(ext))} us; CTA0 {us(ent[0])} {us(rel[0])} {us(ext[0])}", file=sys.stderr)
+        for n in range(7):
+            row = {r: [t[(r * 8 + n) * 8 + e] - t[192] for e in range(8) if t[(r * 8 + n) * 8 + e]] for r in range(4)}
+            print(f"ring trace n={n} mma={row[0]} e1={row[1]} e2={row[2]}", file=sys.stderr)
     lt = torch.tensor([float(launches)], device=dev)
     dist.all_reduce(lt)
     checksum = float(pipe.out_host.sum()) if role.active and role.stage == 1 else 0.0
@@ -340,12 +403,19 @@ def bench_main(args) -> int:
             "config": {"workload": WORKLOAD, "batch": BATCH, "microbatch": MICROBATCH, "stages": 2,
                        "placement": f"{replicas} pipeline(s) of 2 stages, stage k on GPU 2r+k; activations stored by the "
                                     "stage-0 kernel directly into a peer-memory ring on the stage-1 GPU (NVLink)",
-                       "math": args.math, "launch": "cuda_graph_per_step_per_rank" if use_graph else "per_kernel",
+                       "math": args.math,
+                       "launch": ("cuda_graph_per_step_per_rank" if dev_graph else "one_call_per_rank_per_step_with_programmatic_dependent_launch") +
+                                 " (device path); " + ("cuda_graph_per_step_per_rank" if use_graph else "per_kernel") + " (host-facing path)",
                        "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
                     "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0]),
                     "max_abs_diff_vs_single_gpu_path": float(mt[0])},
             "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None, "gpt": gpt,
+            "stage_times": {"stage0_us_ring": float(alone[0]), "stage1_us_fed": float(alone[1]), "step_us": 1e3 * ms_dev / K,
+                            "stage0_busy_frac": float(alone[0]) / (1e3 * ms_dev / K), "stage1_busy_frac": float(alone[1]) / (1e3 * ms_dev / K),
+                            "what": "per 1024-sample step: the stage-0 kernel storing into the peer ring with no back-pressure "
+                                    "(two steps into free slots), the stage-1 kernels on messages already delivered, and the "
+                                    "steady-state step of the pipeline; max over replicas"},
         }
         sys.stdout.flush()
         os.write(real_stdout, (json.dumps(line) + "\n").encode())

@@ -191,6 +191,14 @@ class EngineStage(nn.Module):
         self._require_device()
         return _lib.lib().b2p_stage_set_pdl(self._handle, mask)
 
+    def set_aux_stream(self, stream: int | None):
+        """CIFAR part 1: run the tail kernel on a second stream (b2p_stage_set_aux_stream); ``join`` before reading."""
+        self._require_device()
+        _lib.check(_lib.lib().b2p_stage_set_aux_stream(self._handle, C.c_void_p(stream) if stream else None))
+
+    def join(self, stream: int):
+        _lib.check(_lib.lib().b2p_stage_join(self._handle, C.c_void_p(stream)))
+
     # raw-pointer entry for the pipeline scheduler (no tensor allocation, no checks)
     def forward_ptr(self, in_ptr: int, out_ptr: int, batch: int, seq: int, stream: int):
         _lib.check(_lib.lib().b2p_stage_forward(

@@ -140,6 +140,17 @@ B2P_API int b2p_stage_finalize(b2p_stage* st);
 B2P_API int b2p_stage_reserve(b2p_stage* st, int64_t batch, int64_t seq);
 B2P_API int b2p_stage_set_pdl(b2p_stage* st, int mask);
 
+/* CIFAR part 1 only, no reference counterpart (the reference has one forward per request, node.py:52-53): give the
+ * stage a second stream for its tail kernel (bias + ReLU + fc2 + softmax over fc1's partial sums).  forward then
+ * launches fc1 on the caller's stream and the tail on `aux_stream` behind an event, alternating between two
+ * partial-sum buffers, so fc1 of the next forward does not wait for this forward's tail: on the consumer GPU of a
+ * 2-stage pipeline, where fc1 spends its time waiting for the producer's messages, the tail of step s hides behind
+ * fc1 of step s+1.  The OUTPUT is then complete on `aux_stream`, not on the caller's stream: call b2p_stage_join
+ * before anything on another stream reads it.  Ignored while the caller's stream is being captured.  NULL turns it off. */
+B2P_API int b2p_stage_set_aux_stream(b2p_stage* st, void* aux_stream);
+/* Make `stream` wait for every tail kernel this stage has enqueued on its aux stream so far. */
+B2P_API int b2p_stage_join(b2p_stage* st, void* stream);
+
 /* Output element count for a given input geometry (host helper). */
 B2P_API int b2p_stage_out_elems(b2p_stage* st, int64_t batch, int64_t seq, int64_t* elems);
 
@@ -158,12 +169,15 @@ B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
  * device-side input errors of earlier forwards:
  *   - a token id outside [0,vocab_size) seen by a GPT first stage (an IndexError in the
  *     reference's nn.Embedding, gpt_model_parts.py:17): B2P_EINVAL;
- *   - CIFAR part 0 in a tensor-core math mode: a finite input or conv1 output with
- *     |v| >= 65504.  Those modes carry values as fp16 hi + lo parts, so such a sample comes
- *     out non-finite where the reference (cifar_model_parts.py:37-42, fp32) stays finite:
- *     B2P_ELIMIT; math = B2P_MATH_FP32 has the reference's range.  (Un-normalised 0..255
- *     images with ordinary weights are far inside the range; NaN inputs propagate to NaN
- *     outputs as in torch and are not flagged; +-inf inputs give NaN, not flagged.)
+ *   - CIFAR part 0 in a tensor-core math mode: those modes carry inputs and conv1 outputs
+ *     as fp16 hi + lo parts, so a value with |v| >= 65504 comes out non-finite where the
+ *     reference (cifar_model_parts.py:37-42, fp32) stays finite.  The guard is on the
+ *     input: B2P_ELIMIT when some |x| >= (65504 - max|conv1.bias|) / max_oc sum|conv1.weight[oc]|,
+ *     the magnitude from which on a conv1 output CAN reach the limit (conservative: it never
+ *     misses an overflow, it may flag a batch whose outputs happened to stay below).
+ *     math = B2P_MATH_FP32 has the reference's range.  (Un-normalised 0..255 images with
+ *     ordinary weights are far inside the range; NaN inputs propagate to NaN outputs as in
+ *     torch and are not flagged; +-inf inputs give NaN.)
  * Returns 0 when clean. */
 B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 

@@ -22,6 +22,10 @@ names = {0: ["iter", "act_ready0", "d2_empty(h0)", "Q2h0_issued", "C1(n+1,h0)_is
          2: ["loop_start", "drain(h0)_done", "d2(h1)_loaded", "staged", "-", "-", "-", "-"],
          3: ["-", "image_staged", "patch_empty(h0)", "patches(h0)", "patch_empty(h1)", "patches(h1)", "-", "-"]}
 print("cycles relative to end of set-up (CTA 0), batch", batch)
+ent = [t[256 + 3 * i] for i in range(148)]; rel = [t[257 + 3 * i] for i in range(148)]; ext = [t[258 + 3 * i] for i in range(148)]
+e0 = min(ent)
+us = lambda v: round((v - e0) / 1e3, 1)
+print(f"per-CTA (us after the first entry): entry max {us(max(ent))}, released min/max {us(min(rel))}/{us(max(rel))}, exit min/median/max {us(min(ext))}/{us(sorted(ext)[74])}/{us(max(ext))}")
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for bsz in (128, 1024):
     xb = x[:bsz].contiguous()

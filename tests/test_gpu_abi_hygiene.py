@@ -100,3 +100,28 @@ def test_ring_wait_gives_up_with_a_record_instead_of_trapping(cuda_engine):
     t = torch.arange(1024, device="cuda:0").float()
     assert float(t.sum()) == 1023 * 1024 / 2
     ring.close()
+
+
+def test_tail_kernel_on_a_second_stream(cuda_engine):
+    """b2p_stage_set_aux_stream: fc1 on the caller's stream, the tail on a second stream behind an event, partial sums in
+    alternating buffers.  Back-to-back forwards into separate outputs must each equal the single-stream result bit for
+    bit (same kernels, same association), and b2p_stage_join is what makes them visible to the caller's stream."""
+    sd, p1 = _part1(cuda_engine, "tf32x3")
+    dev = torch.device("cuda", 0)
+    xs = [torch.rand(b, 4096, device=dev) for b in (1024, 1024, 300, 1024, 7)]
+    with torch.no_grad():
+        want = [p1(x).clone() for x in xs]                       # single-stream results
+    main, aux = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    torch.cuda.synchronize()
+    p1.set_aux_stream(aux.cuda_stream)
+    outs = [torch.full((x.shape[0], 10), float("nan"), device=dev) for x in xs]
+    for x, out in zip(xs, outs):                                 # enqueued without any host synchronisation in between
+        p1.forward_ptr(x.data_ptr(), out.data_ptr(), x.shape[0], 0, main.cuda_stream)
+    p1.join(main.cuda_stream)
+    main.synchronize()
+    for got, w, x in zip(outs, want, xs):
+        assert torch.equal(got, w)
+    assert (outs[2].cpu() - co.part1(xs[2].cpu(), sd)).abs().max().item() <= 1e-5
+    p1.set_aux_stream(None)                                      # back to one stream
+    with torch.no_grad():
+        assert torch.equal(p1(xs[4]), want[4])
