@@ -101,6 +101,43 @@ __device__ __forceinline__ void umma_ss_f16_scale11(uint32_t tmem_d, uint64_t de
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(z)
       : "memory");
 }
+// The MMA warp runs its loop with all 32 lanes in uniform control flow and predicates the tensor-core instructions on
+// `lead` (non-zero in one lane): descriptors and addresses then live in uniform registers.  Under `if (lane == 0)` every
+// operand of every UTCHMMA / UTCBAR went through an ELECT / R2UR.BROADCAST / BRA.U.ANY loop -- about 14 dependent
+// instructions per MMA, which made the ISSUE of an 81-cycle MMA take ~80 cycles and every barrier hand-over 150-350.
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred;
+}
+__device__ __forceinline__ void umma_ss_p(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate, uint32_t lead) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
+      : "memory");
+}
+__device__ __forceinline__ void umma_ts_p(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate, uint32_t lead) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
+      : "memory");
+}
+// D = A*B + D * 2^-11   (scale-input-d; checked on the device by scripts/micro/mma_probe.cu)
+__device__ __forceinline__ void umma_ss_scale11_p(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t lead) {
+  const uint32_t z = 0;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, 1, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%4, %4, %4, %4}, p, 11;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(z), "r"(lead)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_p(uint64_t* bar, uint32_t lead) {   // implies fence::before_thread_sync
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
+               "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)), "r"(lead)
+               : "memory");
+}
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
@@ -209,7 +246,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // warp index: uniform for the compiler
 
   // ---- one-time set-up (touches only constant weights: runs before pdl_wait) ----------------------------------
   if (dbg && tid == 0 && blockIdx.x < 256) dbg[256 + 3 * blockIdx.x] = (long long)global_ns();      // entry
@@ -275,7 +312,9 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 
   if (warp == kMmaWarp) {
     // =========================== MMA issuer ========================================================================
-    if (lane == 0) {
+    {
+      const uint32_t lead = elect_one();
+      const uint32_t tmem_base = __shfl_sync(0xffffffffu, s.tmem_slot, 0);     // warp-uniform for the compiler
       mbar_wait(&s.bar_w, 0);
       constexpr uint32_t idesc128 = make_idesc_f16(128, 128), idesc256 = make_idesc_f16(128, 256);
       const uint64_t d_act = make_desc_sw64(smem_u32(s.act));
@@ -289,18 +328,22 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       // conv1 of half `k1 & 1` of sample k1 >> 1: 9 MMAs, lo terms first, the first hi*hi one scales them by 2^-11
       auto issue_c1 = [&](uint32_t k1) {
         mbar_wait(&s.bar_patch_full, k1 & 1);
+        B2P_TRACE2(1, (k1 >> 1) - 1, 4, lead && (k1 & 1) && k1 > 1);
         mbar_wait(&s.bar_d1_empty, (k1 & 1) ^ 1);
+        B2P_TRACE2(1, (k1 >> 1) - 1, 5, lead && (k1 & 1) && k1 > 1);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          umma<0>(t_d1, d_alo + 2 * c, d_phi + 2 * c, idesc128, c != 0);
-          umma<0>(t_d1, d_ahi + 2 * c, d_plo + 2 * c, idesc128, 1u);
+        for (int c = 0; c < 3; ++c) {                          // A = patches (M = pixels), B = weights (N = (oc,dy,dx))
+          umma_ss_p(t_d1, d_phi + 2 * c, d_alo + 2 * c, idesc128, c != 0, lead);
+          umma_ss_p(t_d1, d_plo + 2 * c, d_ahi + 2 * c, idesc128, 1u, lead);
         }
-        umma_ss_f16_scale11(t_d1, d_ahi, d_phi, idesc128);
-        umma<0>(t_d1, d_ahi + 2, d_phi + 2, idesc128, 1u);
-        umma<0>(t_d1, d_ahi + 4, d_phi + 4, idesc128, 1u);
-        umma_commit(&s.bar_d1_full);
-        umma_commit(&s.bar_patch_empty);
+        umma_ss_scale11_p(t_d1, d_phi, d_ahi, idesc128, lead);
+        umma_ss_p(t_d1, d_phi + 2, d_ahi + 2, idesc128, 1u, lead);
+        umma_ss_p(t_d1, d_phi + 4, d_ahi + 4, idesc128, 1u, lead);
+        B2P_TRACE2(1, (k1 >> 1) - 1, 6, lead && (k1 & 1) && k1 > 1);
+        umma_commit_p(&s.bar_d1_full, lead);
+        B2P_TRACE2(1, (k1 >> 1) - 1, 7, lead && (k1 & 1) && k1 > 1);
+        umma_commit_p(&s.bar_patch_empty, lead);
       };
       // conv2 of image rows 8h..8h+7 of sample n: 18 MMAs of N = 256 (128 pixels x hi|lo).  Tap row kh reads activation
       // rows 8h+kh-1 .. 8h+kh+6, so of the upper half only kh = 2 touches row 8, the first row conv1's SECOND half
@@ -309,10 +352,10 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         const uint32_t k2 = 2 * n + h;
         if (h == 0) {
           mbar_wait(&s.bar_act_ready[0], n & 1);
-          B2P_TRACE2(0, n, 1, true);
+          B2P_TRACE2(0, n, 1, lead);
         }
         mbar_wait(&s.bar_d2_empty, (k2 & 1) ^ 1);
-        B2P_TRACE2(0, n, h ? 5 : 2, true);
+        B2P_TRACE2(0, n, h ? 5 : 2, lead);
         tc_fence_after();
         const uint64_t d_half = d_act + ((h * 8 * ACT_ROW_BYTES) >> 4);
 #pragma unroll
@@ -325,25 +368,25 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 #pragma unroll
           for (int ks = 0; ks < 2; ++ks) {
             const uint64_t db = d_half + ((kw * ACT_COPY_BYTES + kh * ACT_ROW_BYTES + ks * 32) >> 4);
-            if (tap < 8) umma_ts_f16(t_d2, t_a2 + tap * 16 + ks * 8, db, idesc256, (tap | ks) != 0);
-            else umma<0>(t_d2, d_w8 + 2 * ks, db, idesc256, 1u);
+            if (tap < 8) umma_ts_p(t_d2, t_a2 + tap * 16 + ks * 8, db, idesc256, (tap | ks) != 0, lead);
+            else umma_ss_p(t_d2, d_w8 + 2 * ks, db, idesc256, 1u, lead);
           }
         }
-        umma_commit(&s.bar_d2_full);
-        if (h == 1) umma_commit(&s.bar_act_free);
+        umma_commit_p(&s.bar_d2_full, lead);
+        if (h == 1) umma_commit_p(&s.bar_act_free, lead);
       };
 
       if (n_samples > 0) { issue_c1(0); issue_c1(1); }
       for (int n = 0; n < n_samples; ++n) {
-        B2P_TRACE2(0, n, 0, true);
+        B2P_TRACE2(0, n, 0, lead);
         issue_q2(n, 0);
-        B2P_TRACE2(0, n, 3, true);
+        B2P_TRACE2(0, n, 3, lead);
         if (n + 1 < n_samples) issue_c1(2 * (n + 1));
-        B2P_TRACE2(0, n, 4, true);
+        B2P_TRACE2(0, n, 4, lead);
         issue_q2(n, 1);
-        B2P_TRACE2(0, n, 6, true);
+        B2P_TRACE2(0, n, 6, lead);
         if (n + 1 < n_samples) issue_c1(2 * (n + 1) + 1);
-        B2P_TRACE2(0, n, 7, true);
+        B2P_TRACE2(0, n, 7, lead);
       }
     }
     __syncwarp();
@@ -433,14 +476,13 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     const int oc2 = 16 * q + (lane >> 1);
     const float bias2 = s.b2[oc2];
     const uint32_t t_row2 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D2 + 64 * part;
-    // ---- E1 geometry: lane = (channel 8q + o, window position d), columns 32*part .. +31 = pooled rows 8h+2*part, +1
-    const int o = lane >> 2, d = lane & 3;
-    const float bias1 = s.b1[8 * q + o];
+    // ---- E1 geometry: lane = pooled pixel 32q + lane of the half (pooled rows 8h+2q, +1), columns 32*part .. +31 =
+    //      channels 8*part .. +7, the four window positions of a channel side by side: pooling stays inside the thread
     const uint32_t t_row1 = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + TM_D1 + 32 * part;
     const bool tracer = warp == kE1Warp0 && lane == 0;
 
     uint4 chunk_hi, chunk_lo;                                  // E1 result held between read and write
-    // conv1 epilogue, first part: TMEM -> pooled, biased, rectified, transposed, split
+    // conv1 epilogue, first part: TMEM -> pooled, biased, rectified, split (this pixel's channels 8*part .. +7)
     auto e1_read = [&](uint32_t k1) {
       mbar_wait(&s.bar_d1_full, k1 & 1);
       tc_fence_after();
@@ -450,30 +492,15 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&s.bar_d1_empty);           // the accumulator may be overwritten (next half's MMAs)
-      float m1[16];
-#pragma unroll
-      for (int j = 0; j < 16; ++j) {                         // dx partner: keep column 2j + (d&1), hand over the other
-        const float a = __uint_as_float(v[2 * j]), c2 = __uint_as_float(v[2 * j + 1]);
-        const float recv = __shfl_xor_sync(0xffffffffu, (d & 1) ? a : c2, 1);
-        m1[j] = max_nan((d & 1) ? c2 : a, recv);
-      }
+      const float4 ba = *reinterpret_cast<const float4*>(&s.b1[8 * part]);
+      const float4 bb = *reinterpret_cast<const float4*>(&s.b1[8 * part + 4]);
+      const float bias[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
       float u[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {                          // dy partner: keep m1[2i + (d>>1)]  ->  column 4i + d
-        const float recv = __shfl_xor_sync(0xffffffffu, (d & 2) ? m1[2 * i] : m1[2 * i + 1], 2);
-        const float m = max_nan((d & 2) ? m1[2 * i + 1] : m1[2 * i], recv);
-        u[i] = max_nan(m + bias1, 0.f);                      // max(a)+b == max(a+b); ReLU
-      }
-      // 8x8 transpose over (channel lane o, register i): afterwards lane (o', d) holds pixel column 4o'+d, channels 8q+i
-#pragma unroll
-      for (int k = 1; k < 8; k <<= 1) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          if (i & k) continue;
-          const bool up = (o & k) != 0;
-          const float recv = __shfl_xor_sync(0xffffffffu, up ? u[i] : u[i | k], 4 * k);
-          if (up) u[i] = recv; else u[i | k] = recv;
-        }
+      for (int j = 0; j < 8; ++j) {                          // max(a)+b == max(a+b); ReLU
+        const float m = max_nan(max_nan(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1])),
+                                max_nan(__uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])));
+        u[j] = max_nan(m + bias[j], 0.f);
       }
       split2(u[0], u[1], chunk_hi.x, chunk_lo.x);
       split2(u[2], u[3], chunk_hi.y, chunk_lo.y);
@@ -482,13 +509,13 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     };
     // conv1 epilogue, second part: this lane's pixel (16-byte hi and lo chunk of its 8 channels) into the three copies
     auto e1_write = [&](uint32_t h) {
-      const int y = 8 * h + 2 * part + (lane >> 4), xc = lane & 15;
+      const int y = 8 * h + 2 * q + (lane >> 4), xc = lane & 15;
 #pragma unroll
       for (int kw = 0; kw < 3; ++kw) {
         const int xs = xc - kw + 1;                            // its column in copy kw (copy kw holds pixel (y, x+kw-1) at x)
         if (xs < 0 || xs > 15) continue;
         unsigned char* dst = s.act + kw * ACT_COPY_BYTES + ((y + 1) * 2 + (xs >> 3)) * 1024 + (xs & 7) * 64 +
-                             ((q ^ ((xs & 7) >> 1)) * 16);
+                             ((part ^ ((xs & 7) >> 1)) * 16);
         *reinterpret_cast<uint4*>(dst) = chunk_hi;
         *reinterpret_cast<uint4*>(dst + 512) = chunk_lo;
       }
@@ -499,7 +526,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     // conv2 drain, first part: TMEM -> registers, accumulator released at once.  Kept per pixel: the even lanes'
     // W_hi*a_hi + 2^-11 W_hi*a_lo, the odd lanes' 2^-11 W_lo*a_hi (32 values for 2 rows x 16 pixels).
     float dv[4][8];
-    auto e2_load = [&](uint32_t n, uint32_t h) {
+    auto e2_load = [&](uint32_t n, uint32_t h, bool rows67) {
       mbar_wait(&s.bar_d2_full, (2 * n + h) & 1);
       tc_fence_after();
       uint32_t r[4][16];
@@ -508,6 +535,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         cifar_tc::tmem_ld16(t_row2 + 16 * g, r[2 * g]);            // row y:   hi x8 | lo x8   (left / right 8 pixels)
         cifar_tc::tmem_ld16(t_row2 + 32 + 16 * g, r[2 * g + 1]);   // row y+1
       }
+      if (rows67) e1_write(0);                                 // Q2(n,1) has completed: rows 6, 7 go out while the loads fly
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
@@ -552,17 +580,21 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     for (int n = 0; n < n_samples; ++n) {
       const bool more = n + 1 < n_samples;
       B2P_TRACE2(2, n, 0, tracer);
-      e2_load(n, 0);
+      e2_load(n, 0, false);
       e2_finish(n, 0);
       B2P_TRACE2(2, n, 1, tracer);
-      if (more) e1_read(2 * (n + 1));                          // held in registers: Q2(n,1) still reads the activation
-      B2P_TRACE2(1, n, 0, tracer);
-      e2_load(n, 1);                                           // Q2(n,1) has completed: the accumulator first ...
-      B2P_TRACE2(2, n, 2, tracer);
-      if (more) {                                              // ... then the activation rows the next Q2 is waiting for
-        mbar_wait(&s.bar_act_free, n & 1);                     // (passes at once: committed together with d2_full)
-        e1_write(0);
+      if (more) {
+        e1_read(2 * (n + 1));
+        B2P_TRACE2(1, n, 0, tracer);
+        // Q2(n,0) has completed and Q2(n,1) reads rows 7..16: rows 0..5 of the next sample can be written now, only
+        // the warps holding rows 6, 7 (lane quarter 3) wait for Q2(n,1) -- inside the second drain
+        if (q != 3) e1_write(0);
         B2P_TRACE2(1, n, 1, tracer);
+      }
+      e2_load(n, 1, more && q == 3);                           // Q2(n,1) has completed: the accumulator first
+      B2P_TRACE2(2, n, 2, tracer);
+      if (more) {
+        mbar_wait(&s.bar_act_free, n & 1);                     // (passes at once: committed together with d2_full)
         e1_read(2 * (n + 1) + 1);
         B2P_TRACE2(1, n, 2, tracer);
         e1_write(1);

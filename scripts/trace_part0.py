@@ -18,7 +18,7 @@ L.check(L.lib().b2p_stage_trace(p._handle, buf, 1024))
 t = list(buf)
 t0 = t[192]
 names = {0: ["iter", "act_ready0", "d2_empty(h0)", "Q2h0_issued", "C1(n+1,h0)_issued", "d2_empty(h1)", "Q2h1_issued", "C1(n+1,h1)_issued"],
-         1: ["e1_read(n+1,h0)_done", "e1_write(h0)_done", "e1_read(n+1,h1)_done", "e1_write(h1)_done", "-", "-", "-", "-"],
+         1: ["e1_read(n+1,h0)_done", "e1_write(h0)_done", "e1_read(n+1,h1)_done", "e1_write(h1)_done", "mma:C1h1_patch_full", "mma:C1h1_d1_empty", "mma:C1h1_mmas_issued", "mma:C1h1_commit1", ],
          2: ["loop_start", "drain(h0)_done", "d2(h1)_loaded", "staged", "-", "-", "-", "-"],
          3: ["-", "image_staged", "patch_empty(h0)", "patches(h0)", "patch_empty(h1)", "patches(h1)", "-", "-"]}
 print("cycles relative to end of set-up (CTA 0), batch", batch)
