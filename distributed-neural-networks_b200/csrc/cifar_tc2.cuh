@@ -67,6 +67,7 @@ constexpr int ACT_COPY_BYTES = 17 * ACT_ROW_BYTES;    // rows -1..15; the zero r
 constexpr int ACT_BYTES = (3 * 17 + 1) * ACT_ROW_BYTES;   // 106 496
 constexpr int PLANE_BYTES = 128 * 128;                // a 128-row operand tile with 128-byte rows
 constexpr int W2T_WORDS = 128;                        // tensor-memory image of conv2's weights: 32-bit words per row
+constexpr int W2T_BYTES = 128 * W2T_WORDS * 4;        // 65 536
 
 struct Smem {
   unsigned char act[ACT_BYTES];                       // conv2's B operand: 3 x-shifted copies, hi/lo interleaved by 8 pixels
@@ -76,7 +77,7 @@ struct Smem {
   float out[2][64 * 64];                              // finished samples in flatten order [channel][h*8+w], double-buffered
   uint32_t in[3][34][34];                             // zero-padded input image, every pixel already split: fp16 hi | fp16 lo << 16
   float b1[32], b2[64];
-  uint64_t bar_w, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
+  uint64_t bar_w, bar_w2t, bar_patch_full, bar_patch_empty, bar_d1_full, bar_d1_empty, bar_act_ready[2], bar_act_free,
       bar_d2_full, bar_d2_empty;
   uint32_t tmem_slot;
   int staged, out_free[2];                            // staging hand-offs between the epilogue warps and the publisher (per buffer)
@@ -101,22 +102,8 @@ __device__ __forceinline__ void umma_ss_f16_scale11(uint32_t tmem_d, uint64_t de
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(z)
       : "memory");
 }
-// The MMA warp runs its loop with all 32 lanes in uniform control flow and predicates the tensor-core instructions on
-// `lead` (non-zero in one lane): descriptors and addresses then live in uniform registers.  Under `if (lane == 0)` every
-// operand of every UTCHMMA / UTCBAR went through an ELECT / R2UR.BROADCAST / BRA.U.ANY loop -- about 14 dependent
-// instructions per MMA, which made the ISSUE of an 81-cycle MMA take ~80 cycles and every barrier hand-over 150-350.
-__device__ __forceinline__ uint32_t elect_one() {
-  uint32_t pred;
-  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-  return pred;
-}
-__device__ __forceinline__ void umma_ss_p(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate, uint32_t lead) {
-  asm volatile(
-      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
-      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
-      : "memory");
-}
+// tensor-core instructions issued from warp-uniform code (tc_gemm.cuh: elect_one, umma_p, umma_commit_p), plus the
+// two forms only this kernel uses: A from tensor memory, and scale-input-d
 __device__ __forceinline__ void umma_ts_p(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate, uint32_t lead) {
   asm volatile(
       "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
@@ -132,11 +119,6 @@ __device__ __forceinline__ void umma_ss_scale11_p(uint32_t tmem_d, uint64_t desc
       "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%4, %4, %4, %4}, p, 11;\n\t}"
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(z), "r"(lead)
       : "memory");
-}
-__device__ __forceinline__ void umma_commit_p(uint64_t* bar, uint32_t lead) {   // implies fence::before_thread_sync
-  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
-               "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)), "r"(lead)
-               : "memory");
 }
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
   asm volatile(
@@ -180,7 +162,7 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
 // ---- one-off weight repacks (b2p_stage_finalize) -----------------------------------------------------------------
 // conv2.weight [64,32,3,3] -> the tensor-memory image of A for taps 0..7: row r = hi part (r even) or lo part (r odd)
 // of channel r/2, 32-bit word tap*16 + ks*8 + j = input channels ks*16 + 2j | 2j+1 (low | high half): exactly what
-// tcgen05.mma reads as A[r][k] from lane r, column j of a K=16 step.
+// tcgen05.mma reads as A[r][k] from lane r, column j of a K=16 step (column = word index).
 __global__ void pack_conv2_tmem(const float* __restrict__ w2, uint32_t* __restrict__ img) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= 128 * W2T_WORDS) return;
@@ -194,7 +176,9 @@ __global__ void pack_conv2_tmem(const float* __restrict__ w2, uint32_t* __restri
     const uint32_t p = split_pack(w2[((oc * 32 + ic) * 3 + kh) * 3 + kw]);
     v |= ((r & 1) ? (p >> 16) : (p & 0xffffu)) << (16 * e);
   }
-  img[i] = v;
+  // stored chunk-major -- 16-byte chunk j of row r at uint4 index j * 128 + r -- so that the kernel, which stages the
+  // image in shared memory with one bulk copy, reads a row's chunk per thread without bank conflicts
+  img[((word >> 2) * 128 + r) * 4 + (word & 3)] = v;
 }
 // ... and tap 8 (kh = kw = 2) as the byte image of its shared-memory tile: the same 128 rows, 64 B (32 input channels)
 // each, 64B-swizzled K-major (16-byte chunk c of row r at chunk c ^ ((r >> 1) & 3)).
@@ -250,8 +234,10 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 
   // ---- one-time set-up (touches only constant weights: runs before pdl_wait) ----------------------------------
   if (dbg && tid == 0 && blockIdx.x < 256) dbg[256 + 3 * blockIdx.x] = (long long)global_ns();      // entry
+  if (dbg && tid == 0 && blockIdx.x == 0) dbg[710] = clock64();
   pdl_trigger();
-  for (int i = tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
+  // (the first 64 KB of `act` first serve as the landing zone of conv2's tensor-memory image, zeroed after the fill)
+  for (int i = W2T_BYTES / 16 + tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < 3 * 34 * 34; i += kThreads) (&s.in[0][0][0])[i] = 0u;
   if (tid < 32) s.b1[tid] = b1[tid];
   if (tid >= 32 && tid < 96) s.b2[tid - 32] = b2[tid - 32];
@@ -268,7 +254,16 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
       mbar_init(&s.bar_act_free, 1);
       mbar_init(&s.bar_d2_full, 1);
       mbar_init(&s.bar_d2_empty, kEpiWarps);
+      mbar_init(&s.bar_w2t, 1);
       fence_barrier_init();
+      // constant weights, requested first thing: conv2's tensor-memory image into the (not yet used) activation buffer,
+      // conv1's A tiles and conv2's tap 8 to their places
+      mbar_expect_tx(&s.bar_w2t, W2T_BYTES);
+      bulk_g2s(s.act, w2t, W2T_BYTES, &s.bar_w2t);
+      mbar_expect_tx(&s.bar_w, 2 * PLANE_BYTES + cifar_tc::W2_TAP_BYTES);
+      bulk_g2s(s.a1, a1img, PLANE_BYTES, &s.bar_w);
+      bulk_g2s(s.a1 + PLANE_BYTES, a1img + PLANE_BYTES, PLANE_BYTES, &s.bar_w);
+      bulk_g2s(s.w2tap8, w2tap8, cifar_tc::W2_TAP_BYTES, &s.bar_w);
     }
     __syncwarp();
     tmem_alloc(&s.tmem_slot, 512);
@@ -279,36 +274,46 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = s.tmem_slot;
-  if (warp == kMmaWarp && lane == 0) {                     // conv1's A tiles and conv2's tap 8 -> shared memory
-    mbar_expect_tx(&s.bar_w, 2 * PLANE_BYTES + cifar_tc::W2_TAP_BYTES);
-    bulk_g2s(s.a1, a1img, PLANE_BYTES, &s.bar_w);
-    bulk_g2s(s.a1 + PLANE_BYTES, a1img + PLANE_BYTES, PLANE_BYTES, &s.bar_w);
-    bulk_g2s(s.w2tap8, w2tap8, cifar_tc::W2_TAP_BYTES, &s.bar_w);
-  }
-  // (Requesting these 512 bytes per thread at the top of the kernel, to hide their latency behind the rest of the
-  //  set-up, was measured SLOWER by 3.9 us per launch: 64 more live registers in the prologue change the allocation of
-  //  the whole kernel, which runs at its 80-register limit.)
-  if (tid < 128) {                                         // conv2's A, taps 0..7 -> tensor memory: thread = row = lane
-    const uint4* src = reinterpret_cast<const uint4*>(w2t + (size_t)tid * W2T_WORDS);
-    const uint32_t row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + TM_A2;
+  // The conv1 patch producers need nothing of what follows (tensor memory, weights): they go straight to the first
+  // image, whose load, split and first patches (~3 k cycles) then overlap the rest of the set-up.
+  if (warp >= kPubWarp) {
+    if (warp >= kE1Warp0 && warp < kE1Warp0 + 4) {           // conv2's A, taps 0..7 -> tensor memory: thread = row = lane
+      // The image arrives in shared memory by ONE bulk copy issued at the top of the kernel (pack_conv2_tmem stores it
+      // chunk-major).  Reading it from global memory here -- four rounds of eight dependent 16-byte loads -- took four
+      // L2 round trips, 6 k cycles of every launch.  (Sixteen warps filling 32 columns each in one round was slower
+      // still, +1.5 us per launch: 32 more live registers on the epilogue warps' path change the allocation of the
+      // whole kernel.)
+      mbar_wait(&s.bar_w2t, 0);
+      const uint4* src = reinterpret_cast<const uint4*>(s.act) + 32 * (warp & 3) + lane;
+      const uint32_t row = tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + TM_A2;
 #pragma unroll 1
-    for (int i = 0; i < 4; ++i) {
-      uint32_t v[32];
+      for (int i = 0; i < 4; ++i) {
+        uint32_t v[32];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const uint4 w = __ldg(src + i * 8 + j);
-        v[4 * j] = w.x; v[4 * j + 1] = w.y; v[4 * j + 2] = w.z; v[4 * j + 3] = w.w;
+        for (int j = 0; j < 8; ++j) {
+          const uint4 w = src[(i * 8 + j) * 128];
+          v[4 * j] = w.x; v[4 * j + 1] = w.y; v[4 * j + 2] = w.z; v[4 * j + 3] = w.w;
+        }
+        tmem_st32(row + 32 * i, v);
       }
-      tmem_st32(row + 32 * i, v);
+      tmem_st_wait();
     }
-    tmem_st_wait();
+    named_bar(3, kThreads - kPatchThreads);                  // the landing zone has been read: zero it (activation halo)
+    for (int i = tid - kPatchThreads; i < W2T_BYTES / 16; i += kThreads - kPatchThreads)
+      reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async();               // the zeroed activation halo must be visible to the tensor core
+    tc_fence_before();
+    named_bar(3, kThreads - kPatchThreads);
+    tc_fence_after();
+    if (dbg && blockIdx.x == 0 && tid == kPubWarp * 32) dbg[3 * 64] = clock64();      // end of set-up
   }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  if (dbg && blockIdx.x == 0 && tid == 0) dbg[3 * 64] = clock64();      // end of set-up
   if (warp != kMmaWarp) pdl_wait();   // input readers and output writers: both may touch the previous kernel's data
   if (dbg && tid == 0 && blockIdx.x < 256) dbg[257 + 3 * blockIdx.x] = (long long)global_ns();      // released by the previous kernel
+  if (dbg && tid == 0 && blockIdx.x == 0) {
+    dbg[711] = clock64();
+    const unsigned long long k = atomicAdd(reinterpret_cast<unsigned long long*>(dbg + 719), 1ull);   // launches seen by this trace buffer
+    dbg[720 + (k & 15)] = (long long)global_ns();            // CTA 0 released, exit: per launch (ring of 16), for back-to-back periods
+  }
 
   if (warp == kMmaWarp) {
     // =========================== MMA issuer ========================================================================
@@ -334,12 +339,12 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < 3; ++c) {                          // A = patches (M = pixels), B = weights (N = (oc,dy,dx))
-          umma_ss_p(t_d1, d_phi + 2 * c, d_alo + 2 * c, idesc128, c != 0, lead);
-          umma_ss_p(t_d1, d_plo + 2 * c, d_ahi + 2 * c, idesc128, 1u, lead);
+          umma_p<0>(t_d1, d_phi + 2 * c, d_alo + 2 * c, idesc128, c != 0, lead);
+          umma_p<0>(t_d1, d_plo + 2 * c, d_ahi + 2 * c, idesc128, 1u, lead);
         }
         umma_ss_scale11_p(t_d1, d_phi, d_ahi, idesc128, lead);
-        umma_ss_p(t_d1, d_phi + 2, d_ahi + 2, idesc128, 1u, lead);
-        umma_ss_p(t_d1, d_phi + 4, d_ahi + 4, idesc128, 1u, lead);
+        umma_p<0>(t_d1, d_phi + 2, d_ahi + 2, idesc128, 1u, lead);
+        umma_p<0>(t_d1, d_phi + 4, d_ahi + 4, idesc128, 1u, lead);
         B2P_TRACE2(1, (k1 >> 1) - 1, 6, lead && (k1 & 1) && k1 > 1);
         umma_commit_p(&s.bar_d1_full, lead);
         B2P_TRACE2(1, (k1 >> 1) - 1, 7, lead && (k1 & 1) && k1 > 1);
@@ -369,7 +374,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           for (int ks = 0; ks < 2; ++ks) {
             const uint64_t db = d_half + ((kw * ACT_COPY_BYTES + kh * ACT_ROW_BYTES + ks * 32) >> 4);
             if (tap < 8) umma_ts_p(t_d2, t_a2 + tap * 16 + ks * 8, db, idesc256, (tap | ks) != 0, lead);
-            else umma_ss_p(t_d2, d_w8 + 2 * ks, db, idesc256, 1u, lead);
+            else umma_p<0>(t_d2, d_w8 + 2 * ks, db, idesc256, 1u, lead);
           }
         }
         umma_commit_p(&s.bar_d2_full, lead);
@@ -666,7 +671,13 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
 
   tc_fence_before();
   __syncthreads();
-  if (dbg && tid == 0 && blockIdx.x < 256) dbg[258 + 3 * blockIdx.x] = (long long)global_ns();      // exit
+  if (dbg && tid == kMmaWarp * 32 && blockIdx.x < 256) {     // exit (stamped by a thread that has work until the end)
+    dbg[258 + 3 * blockIdx.x] = (long long)global_ns();
+    if (blockIdx.x == 0) {
+      dbg[712] = clock64();
+      dbg[736 + ((dbg[719] - 1) & 15)] = (long long)global_ns();
+    }
+  }
   if (warp == kMmaWarp) tmem_dealloc(tmem_base, 512);
 #undef B2P_TRACE2
 }

@@ -88,7 +88,7 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
   uint64_t* tmem_empty = tmem_full + ACC;    // [ACC] epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + ACC);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;      // warp-uniform for the compiler
   const int m_tiles = (M + BM - 1) / BM;
   const int num_items = ZI * NTILES * m_tiles;
 
@@ -164,31 +164,32 @@ fc1_x3_splitk(const __grid_constant__ CUtensorMap tmap_x,       // x [M,4096] fp
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // all 32 lanes in uniform control flow, the tensor-core instructions predicated on elect.sync (tc_gemm.cuh)
     constexpr uint32_t idesc = make_idesc(1, BM, BN);
+    const uint32_t lead = elect_one();
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t tiles_u = __shfl_sync(0xffffffffu, smem_u32(tiles), 0);
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_items; item += gridDim.x)
     for (int sl = 0; sl < GROUP; ++sl) {             // one accumulator stage per K slice of the item
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * BN;
+      const uint32_t tmem_d = tmem_u + acc * BN;
       for (int kb = 0; kb < KBLOCKS; ++kb) {
         mbar_wait(&full[stage], phase);
         mbar_wait(&conv[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t base = smem_u32(tiles + stage * STAGE_BYTES);
-          const uint64_t xa = make_desc_sw128(base), xl = make_desc_sw128(base + PLANE);
-          const uint64_t wh = make_desc_sw128(base + 2 * PLANE), wl = make_desc_sw128(base + 3 * PLANE);
+        const uint32_t base = tiles_u + stage * STAGE_BYTES;
+        const uint64_t xa = make_desc_sw128(base), xl = make_desc_sw128(base + PLANE);
+        const uint64_t wh = make_desc_sw128(base + 2 * PLANE), wl = make_desc_sw128(base + 3 * PLANE);
 #pragma unroll
-          for (int k = 0; k < KB / 8; ++k) {              // tf32 k-step = 8 elements = 32 B = +2 in the descriptor
-            umma<1>(tmem_d, xl + 2 * k, wh + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);      // small terms first
-            umma<1>(tmem_d, xa + 2 * k, wl + 2 * k, idesc, 1u);
-            umma<1>(tmem_d, xa + 2 * k, wh + 2 * k, idesc, 1u);
-          }
-          umma_commit(&empty[stage]);
-          if (kb == KBLOCKS - 1) umma_commit(&tmem_full[acc]);
+        for (int k = 0; k < KB / 8; ++k) {              // tf32 k-step = 8 elements = 32 B = +2 in the descriptor
+          umma_p<1>(tmem_d, xl + 2 * k, wh + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u, lead);      // small terms first
+          umma_p<1>(tmem_d, xa + 2 * k, wl + 2 * k, idesc, 1u, lead);
+          umma_p<1>(tmem_d, xa + 2 * k, wh + 2 * k, idesc, 1u, lead);
         }
-        __syncwarp();
+        umma_commit_p(&empty[stage], lead);
+        if (kb == KBLOCKS - 1) umma_commit_p(&tmem_full[acc], lead);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
       if (++acc == ACC) { acc = 0; acc_phase ^= 1; }

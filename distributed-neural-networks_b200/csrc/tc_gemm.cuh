@@ -132,6 +132,40 @@ __device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t desc_a, uint64_t 
         : "memory");
   }
 }
+// ---- single-thread tensor-core instructions from warp-uniform code --------------------------------------------------
+// tcgen05.mma / tcgen05.commit are issued by one thread.  Written as `if (lane == 0) { ... }` the compiler sees a
+// divergent region, keeps every descriptor in vector registers and wraps EVERY such instruction in an
+// ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~14 dependent instructions): issuing an 81-cycle MMA then takes ~80 cycles
+// and a barrier hand-over 150-350 (measured in part0_tc2 with clock64 stamps).  The issuing warp therefore runs its loop
+// with all 32 lanes (warp index and tensor-memory base made warp-uniform with __shfl_sync(.., 0)) and predicates the
+// instruction itself on elect.sync: operands stay in uniform registers, UTCHMMAs issue back to back.
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred;
+}
+template <int KIND>
+__device__ __forceinline__ void umma_p(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                       uint32_t accumulate, uint32_t lead) {
+  if (KIND == 0) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void umma_commit_p(uint64_t* bar, uint32_t lead) {   // implies fence::before_thread_sync
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t"
+               "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+               ::"r"(smem_u32(bar)), "r"(lead) : "memory");
+}
 // 32 lanes x 32 consecutive 32-bit columns: thread t of the warp gets TMEM lane
 // (lane_base + t), columns col .. col+31.
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {

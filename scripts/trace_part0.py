@@ -13,7 +13,11 @@ batch = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 x = torch.randn(batch, 3, 32, 32, device=dev)
 p(x)                                   # warm
 L.check(L.lib().b2p_stage_trace(p._handle, buf, 1024))     # arm
-p(x); torch.cuda.synchronize()
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 1      # > 1: the stamps are those of the last of `reps` back-to-back launches
+o = torch.empty(batch, 4096, device=dev)
+for _ in range(reps):
+    p.forward_ptr(x.data_ptr(), o.data_ptr(), batch, 0, torch.cuda.current_stream().cuda_stream)
+torch.cuda.synchronize()
 L.check(L.lib().b2p_stage_trace(p._handle, buf, 1024))
 t = list(buf)
 t0 = t[192]
@@ -26,6 +30,17 @@ ent = [t[256 + 3 * i] for i in range(148)]; rel = [t[257 + 3 * i] for i in range
 e0 = min(ent)
 us = lambda v: round((v - e0) / 1e3, 1)
 print(f"per-CTA (us after the first entry): entry max {us(max(ent))}, released min/max {us(min(rel))}/{us(max(rel))}, exit min/median/max {us(min(ext))}/{us(sorted(ext)[74])}/{us(max(ext))}")
+print(f"CTA 0 (cycles relative to end of set-up): entry {t[710] - t0}, released {t[711] - t0}, exit {t[712] - t0}; ns: entry {us(ent[0])}, released {us(rel[0])}, exit {us(ext[0])} us")
+nl = t[719]
+if nl > 1:
+    rel_k = [t[720 + (k & 15)] for k in range(max(0, nl - 16), nl)]
+    ext_k = [t[736 + (k & 15)] for k in range(max(0, nl - 16), nl)]
+    print("CTA 0 over the traced launches: release-to-release", [round((b - a) / 1e3, 1) for a, b in zip(rel_k, rel_k[1:])],
+          "us; release-to-exit", [round((e - r) / 1e3, 1) for r, e in zip(rel_k, ext_k)], "us; exit-to-next-release",
+          [round((r - e) / 1e3, 1) for e, r in zip(ext_k, rel_k[1:])], "us")
+if nl > 1:
+    print("raw ns (CTA 0, minus first entry): entry", ent[0] - e0, "released", rel[0] - e0, "exit", ext[0] - e0, "| ring: released",
+          [v - e0 for v in rel_k[-3:]], "exit", [v - e0 for v in ext_k[-3:]])
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 for bsz in (128, 1024):
     xb = x[:bsz].contiguous()
