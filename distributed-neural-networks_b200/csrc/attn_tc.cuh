@@ -80,7 +80,7 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
                     __nv_bfloat16* __restrict__ y, int T, int C) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;     // warp index: uniform for the compiler
   const int pair = gridDim.x - 1 - blockIdx.x;          // heavy (late) query tiles first
   const int h = blockIdx.y, b = blockIdx.z;
   const int q0 = pair * (QW * BQ);
@@ -135,11 +135,14 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc_s = idesc_bf16(BQ, BKV, false);
     constexpr uint32_t idesc_o = idesc_bf16(BQ, HD, true);
+    // all 32 lanes in uniform control flow, the tensor-core instructions predicated on elect.sync (tc_gemm.cuh, elect_one)
+    const uint32_t lead = elect_one();
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
     auto issue_s = [&](int w, int st) {                  // S_w = Q_w K^T  (4 MMAs, K = 64)
       const uint64_t dq = make_desc_sw128(smem_u32(s.q[w])), dk = make_desc_sw128(smem_u32(s.k[st]));
 #pragma unroll
-      for (int k = 0; k < HD / 16; ++k) umma<0>(tmem_base + w * 128, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-      umma_commit(&s.s_full[w]);
+      for (int k = 0; k < HD / 16; ++k) umma_p<0>(tmem_u + w * 128, dq + 2 * k, dk + 2 * k, idesc_s, k != 0, lead);
+      umma_commit_p(&s.s_full[w], lead);
     };
     auto issue_pv = [&](int w, int st) {                 // O_w = P_w V  (8 MMAs, 16 keys each)
       const uint64_t dv = make_desc_sw128(smem_u32(s.v[st]));
@@ -147,18 +150,16 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
       for (int k = 0; k < BKV / 16; ++k) {
         // A = P: 64-key atom (k>>2), +32 B per 16 keys inside it; B = V (MN-major): +16 key rows = 2048 B
         const uint64_t dp = make_desc_sw128(smem_u32(s.p[w]) + (k >> 2) * P_ATOM_BYTES) + 2 * (k & 3);
-        umma<0>(tmem_base + 256 + w * 64, dp, dv + 128 * k, idesc_o, k != 0);
+        umma_p<0>(tmem_u + 256 + w * 64, dp, dv + 128 * k, idesc_o, k != 0, lead);
       }
-      umma_commit(&s.o_full[w]);
+      umma_commit_p(&s.o_full[w], lead);
     };
     mbar_wait(&s.q_full, 0);
     if (n_kv > 0) {
       mbar_wait(&s.kv_full[0], 0);
       tc_fence_after();
-      if (lane == 0)
-        for (int w = 0; w < QW; ++w)
-          if (last[w] >= 0) issue_s(w, 0);
-      __syncwarp();
+      for (int w = 0; w < QW; ++w)
+        if (last[w] >= 0) issue_s(w, 0);
     }
     uint32_t stage = 0, phase = 0;
     for (int j = 0; j < n_kv; ++j) {
@@ -171,13 +172,11 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
           mbar_wait(&s.p_full[w], j & 1);                // P_w(j) written; S_w and O_w(j-1) already consumed
           tc_fence_after();
           ATTN_TRACE(0, j, w * 4 + 1, lane == 0);
-          if (lane == 0) issue_pv(w, stage);
-          __syncwarp();
+          issue_pv(w, stage);
           ATTN_TRACE(0, j, w * 4 + 2, lane == 0);
         }
         if (w == QW - 1) {                               // both PVs of this stage are in flight
-          if (lane == 0) umma_commit(&s.kv_empty[stage]);
-          __syncwarp();
+          umma_commit_p(&s.kv_empty[stage], lead);
         }
         if (j + 1 <= last[w]) {                          // start the next score tile of this query tile right away
           if (!next_ready) {
@@ -185,8 +184,7 @@ attention_causal_tc(const __grid_constant__ CUtensorMap tmap_q,     // box [64 c
             tc_fence_after();
             next_ready = true;
           }
-          if (lane == 0) issue_s(w, nstage);
-          __syncwarp();
+          issue_s(w, nstage);
           ATTN_TRACE(0, j, w * 4 + 3, lane == 0);
         }
       }

@@ -403,7 +403,7 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   uint64_t* tmem_empty = tmem_full + 2;          // [2]       epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;     // warp index: uniform for the compiler
   const int tiles_m = (M + Cfg::BM - 1) / Cfg::BM, tiles_n = (N + BN - 1) / BN;
   const int num_tiles = tiles_m * tiles_n * splits;        // work items: (output tile, K slice)
   const int total_kb = (K + Cfg::BK - 1) / Cfg::BK;
@@ -451,36 +451,37 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // all 32 lanes in uniform control flow, the tensor-core instructions predicated on elect.sync (see elect_one above)
     constexpr uint32_t idesc = make_idesc(KIND, Cfg::BM, BN);
+    const uint32_t lead = elect_one();
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t tiles_u = __shfl_sync(0xffffffffu, smem_u32(tiles), 0);
     uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       const int z = item % splits;
       const int kb0 = z * kb_per_split, num_kb = min(total_kb, kb0 + kb_per_split) - kb0;
       mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * BN;
+      const uint32_t tmem_d = tmem_u + acc * BN;
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_addr = smem_u32(tiles + stage * Cfg::STAGE_BYTES);
-          const uint64_t da = make_desc_sw128(a_addr), db = make_desc_sw128(a_addr + Cfg::A_BYTES);
+        const uint32_t a_addr = tiles_u + stage * Cfg::STAGE_BYTES;
+        const uint64_t da = make_desc_sw128(a_addr), db = make_desc_sw128(a_addr + Cfg::A_BYTES);
 #pragma unroll
-          for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k) {  // +32 B along K inside the swizzle row = +2 (>>4)
-            if (Cfg::SPLIT) {
-              const uint64_t da_lo = make_desc_sw128(a_addr + Cfg::A_PLANE);
-              const uint64_t db_lo = make_desc_sw128(a_addr + Cfg::A_BYTES + Cfg::B_PLANE);
-              umma<KIND>(tmem_d, da_lo + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);   // small terms first
-              umma<KIND>(tmem_d, da + 2 * k, db_lo + 2 * k, idesc, 1u);
-              umma<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, 1u);
-            } else {
-              umma<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
+        for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k) {  // +32 B along K inside the swizzle row = +2 (>>4)
+          if (Cfg::SPLIT) {
+            const uint64_t da_lo = make_desc_sw128(a_addr + Cfg::A_PLANE);
+            const uint64_t db_lo = make_desc_sw128(a_addr + Cfg::A_BYTES + Cfg::B_PLANE);
+            umma_p<KIND>(tmem_d, da_lo + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u, lead);   // small terms first
+            umma_p<KIND>(tmem_d, da + 2 * k, db_lo + 2 * k, idesc, 1u, lead);
+            umma_p<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, 1u, lead);
+          } else {
+            umma_p<KIND>(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u, lead);
           }
-          umma_commit(&empty[stage]);                        // smem slot free once these MMAs retire
-          if (kb == num_kb - 1) umma_commit(&tmem_full[acc]);
         }
-        __syncwarp();
+        umma_commit_p(&empty[stage], lead);                  // smem slot free once these MMAs retire
+        if (kb == num_kb - 1) umma_commit_p(&tmem_full[acc], lead);
         if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }

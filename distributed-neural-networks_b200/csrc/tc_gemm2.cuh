@@ -68,6 +68,21 @@ __device__ __forceinline__ void umma_pair_bf16(uint32_t tmem_d, uint64_t desc_a,
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// the same two, issued from warp-uniform code and predicated on elect.sync (tc_gemm.cuh, elect_one)
+__device__ __forceinline__ void umma_pair_bf16_p(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                 uint32_t accumulate, uint32_t lead) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(lead)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_p(uint64_t* bar, uint32_t lead) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t"
+               "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}"
+               ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3)), "r"(lead)
+               : "memory");
+}
 __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {     // arrives on `bar` in BOTH CTAs of the pair
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
@@ -108,7 +123,7 @@ linear_tc_pair(const __grid_constant__ CUtensorMap tmap_a,      // box [64 K, 12
   uint64_t* tmem_empty = tmem_full + 2;          // [2]       (used in the leader)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;     // warp index: uniform for the compiler
   const uint32_t rank = cluster_ctarank();       // 0 = leader
   const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
   const int tiles_m = (M + Cfg::BM_PAIR - 1) / Cfg::BM_PAIR, tiles_n = (N + BN - 1) / BN;
@@ -155,24 +170,24 @@ linear_tc_pair(const __grid_constant__ CUtensorMap tmap_a,      // box [64 K, 12
     // ===================== MMA issuer (leader only) =====================
     if (rank == 0) {
       constexpr uint32_t idesc = make_idesc(0, Cfg::BM_PAIR, BN);
+      const uint32_t lead = elect_one();
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t tiles_u = __shfl_sync(0xffffffffu, smem_u32(tiles), 0);
       uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
       for (int tile = pair; tile < num_tiles; tile += n_pairs) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * BN;
+        const uint32_t tmem_d = tmem_u + acc * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t a_addr = smem_u32(tiles + stage * Cfg::STAGE_BYTES);
-            const uint64_t da = make_desc_sw128(a_addr), db = make_desc_sw128(a_addr + Cfg::A_BYTES);
+          const uint32_t a_addr = tiles_u + stage * Cfg::STAGE_BYTES;
+          const uint64_t da = make_desc_sw128(a_addr), db = make_desc_sw128(a_addr + Cfg::A_BYTES);
 #pragma unroll
-            for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k)
-              umma_pair_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-            umma_commit_pair(&empty[stage]);                       // frees the slot in both CTAs
-            if (kb == num_kb - 1) umma_commit_pair(&tmem_full[acc]);
-          }
-          __syncwarp();
+          for (int k = 0; k < Cfg::BK / Cfg::UMMA_K; ++k)
+            umma_pair_bf16_p(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u, lead);
+          umma_commit_pair_p(&empty[stage], lead);                 // frees the slot in both CTAs
+          if (kb == num_kb - 1) umma_commit_pair_p(&tmem_full[acc], lead);
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
