@@ -146,8 +146,14 @@ int cifar_part0_forward(b2p_stage* st, const float* in, float* out, int64_t batc
     B2P_LAUNCH(part0_fused_f32, grid, 256, sizeof(Part0Smem), s, in, st->w1t, st->dev(1), st->w2t,
                st->dev(3), out, (int)batch);
   else if (!part0_v1())   // both convolutions on the tensor cores (split-fp16, fp32-grade) in every tensor-core math mode
+  {
+    // ring mode with bit 2 of the stage's PDL mask: consecutive steps use different slots and the input is not the
+    // preceding kernel's output, so the kernel need not wait for that kernel (b200pipe.h, b2p_stage_set_pdl)
+    const int no_wait = (span.data && pdl_call_mask() >= 0 && (pdl_call_mask() & 4) && pdl_enabled(2) &&
+                         2 * ceil_div(batch, span.rows_per_msg) <= span.slots) ? 1 : 0;   // (this launch and the next never share a slot)
     B2P_LAUNCH_PDL_BIT(2, cifar_tc2::part0_tc2, grid, cifar_tc2::kThreads, cifar_tc2::SMEM_BYTES, s, in, st->a1img, st->w2tm,
-                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->bad_flag, st->in_limit, st->trace, span);
+                       st->w2tap8, st->dev(1), st->dev(3), out, (int)batch, st->bad_flag, st->in_limit, st->trace, span, no_wait);
+  }
   else   // round 1's kernel (conv1 on the CUDA cores), kept for A/B measurements: B2P_PART0_V1=1
   {
     cifar_tc::Conv1Const c1;
@@ -718,7 +724,7 @@ int b2p_stage_join(b2p_stage* st, void* stream) {
 int b2p_stage_set_pdl(b2p_stage* st, int mask) {
   if (!st) return fail(B2P_EINVAL, "null stage");
   const int prev = st->pdl_mask;
-  st->pdl_mask = mask < 0 ? -1 : (mask & 3);
+  st->pdl_mask = mask < 0 ? -1 : (mask & 7);
   return prev < 0 ? pdl_switch().load() : prev;
 }
 

@@ -54,8 +54,10 @@ using cifar_tc::named_bar;
 
 constexpr int kPatchWarp0 = 0, kPatchThreads = 64;
 constexpr int kPubWarp = 2, kMmaWarp = 3;
+constexpr int kPubLanes = 4;                          // lanes of the publisher warp that send samples (power of two)
 constexpr int kE1Warp0 = 4, kEpiWarps = 16;           // epilogue warps 4..19
-constexpr int kThreads = 20 * 32;                     // 640 threads: 96 registers each (at 736 threads the 80-register limit decided everything)
+constexpr int kThreads = 20 * 32;                     // 640 threads: 96 registers each (at 736 threads the 80-register limit decided everything;
+                                                      // a 21st warp is accounted as four: 80 registers again)
 
 // tensor-memory map (512 columns)
 constexpr uint32_t TM_A2 = 0;                         // conv2 weights, taps 0..7: 8 taps x 2 K-steps x 8 columns
@@ -225,16 +227,20 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
           int batch, int* __restrict__ range_flag,         // set to 1 when a value may have left the split-fp16 range (b2p_stage_check)
           float in_limit,                                  // |input| from which on that can happen: min(65504, (65504 - max|b1|) / max_oc sum|w1[oc]|)
           long long* __restrict__ dbg,         // dbg: optional clock64 trace of CTA 0, [role 0..3][sample 0..7][event 0..7], entry 192 = end of set-up
-          RingSpan span) {                                // span.data: rows go into handoff-ring slots instead of out
+          RingSpan span,                                  // span.data: rows go into handoff-ring slots instead of out
+          int no_wait) {                                  // ring mode only: do not wait for the preceding kernel of the stream (b2p_stage_set_pdl bit 2)
+#ifndef B2P_TRACE_CTA
+#define B2P_TRACE_CTA 0          // the CTA whose clock64 timeline b2p_stage_trace records (developer builds: -DB2P_TRACE_CTA=8 ...)
+#endif
 #define B2P_TRACE2(role, n, ev, cond) \
-  do { if (dbg && blockIdx.x == 0 && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
+  do { if (dbg && blockIdx.x == B2P_TRACE_CTA && (n) < 8 && (cond)) dbg[((role) * 8 + (n)) * 8 + (ev)] = clock64(); } while (0)
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   Smem& s = *reinterpret_cast<Smem*>(smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u));
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // warp index: uniform for the compiler
 
   // ---- one-time set-up (touches only constant weights: runs before pdl_wait) ----------------------------------
   if (dbg && tid == 0 && blockIdx.x < 256) dbg[256 + 3 * blockIdx.x] = (long long)global_ns();      // entry
-  if (dbg && tid == 0 && blockIdx.x == 0) dbg[710] = clock64();
+  if (dbg && tid == 0 && blockIdx.x == B2P_TRACE_CTA) dbg[710] = clock64();
   pdl_trigger();
   // (the first 64 KB of `act` first serve as the landing zone of conv2's tensor-memory image, zeroed after the fill)
   for (int i = W2T_BYTES / 16 + tid; i < ACT_BYTES / 16; i += kThreads) reinterpret_cast<uint4*>(s.act)[i] = make_uint4(0, 0, 0, 0);
@@ -305,11 +311,16 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     tc_fence_before();
     named_bar(3, kThreads - kPatchThreads);
     tc_fence_after();
-    if (dbg && blockIdx.x == 0 && tid == kPubWarp * 32) dbg[3 * 64] = clock64();      // end of set-up
+    if (dbg && blockIdx.x == B2P_TRACE_CTA && tid == kPubWarp * 32) dbg[3 * 64] = clock64();      // end of set-up
   }
-  if (warp != kMmaWarp) pdl_wait();   // input readers and output writers: both may touch the previous kernel's data
+  // input readers and output writers: both may touch the previous kernel's data.  Not so in ring mode when the caller
+  // says the input is not that kernel's output (no_wait): consecutive steps write different ring slots, at most two
+  // consecutive grids are resident (grids dispatch in order), and the slots' counters were last written two steps ago.
+  // The previous step's stragglers -- the CTAs that publish its last messages, 5-8 us of fences -- and the flush of its
+  // peer writes then overlap this step's first samples instead of standing between the steps (52 -> 4x us per step).
+  if (warp != kMmaWarp && !no_wait) pdl_wait();
   if (dbg && tid == 0 && blockIdx.x < 256) dbg[257 + 3 * blockIdx.x] = (long long)global_ns();      // released by the previous kernel
-  if (dbg && tid == 0 && blockIdx.x == 0) {
+  if (dbg && tid == 0 && blockIdx.x == B2P_TRACE_CTA) {
     dbg[711] = clock64();
     const unsigned long long k = atomicAdd(reinterpret_cast<unsigned long long*>(dbg + 719), 1ull);   // launches seen by this trace buffer
     dbg[720 + (k & 15)] = (long long)global_ns();            // CTA 0 released, exit: per launch (ring of 16), for back-to-back periods
@@ -621,47 +632,84 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     // Two lanes share the work, lane l taking the samples whose staging buffer is l: each sample's chain -- copy, its
     // completion over NVLink, a gpu-scope fence, the ticket -- takes about as long as a sample's arithmetic, so one
     // thread doing them back to back set the pace of the whole kernel in ring mode.
-    if (lane < 2) {
-      int acquired = -1;
+    // Slot handshake with the consumer GPU, done for the WHOLE step before the first copy: at kernel start the consumer
+    // has normally released every slot this step will use (the ring holds two steps), so the NVLink round trip of the
+    // poll and the system-scope fence behind it (2.5 us and more with peer traffic outstanding) pass while the first
+    // sample is still being computed.  The message this CTA leads (it holds the message's first row; at most one, 148
+    // CTAs > 128 rows) is polled first and the value posted for the other CTAs, then the CTA waits for what the other
+    // leaders posted.  (Acquiring per sample inside the copy loop stalled a leader's lane for 5-8 us per message and
+    // everybody else behind it; a third lane of this warp running ahead was starved by its spinning siblings.)
+    if (span.data) {
+      if (lane == 0) {
+        for (int b = blockIdx.x; b < batch; b += gridDim.x) {
+          const int msg = b / span.rows_per_msg;
+          if (b != msg * span.rows_per_msg) continue;
+          const int slot = span_slot(span, msg);
+          const unsigned long long k = ld_count(span.count + slot);      // messages already published into this slot
+          if (k > 0) {
+            spin_until_ge_remote(span.released + slot, k);
+            st_release_gpu(span.acq_seen + slot, k);
+          }
+        }
+        int acquired = -1;
+        for (int b = blockIdx.x; b < batch; b += gridDim.x) {
+          const int msg = b / span.rows_per_msg;
+          if (msg == acquired) continue;
+          const int slot = span_slot(span, msg);
+          const unsigned long long k = ld_count(span.count + slot);
+          if (k > 0 && b != msg * span.rows_per_msg)
+            while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
+          acquired = msg;
+        }
+      }
+      __syncwarp();
+    }
+    // Four lanes take the samples in turn (sample n: lane n & 3, staging buffer n & 1).  In ring mode a sample's chain
+    // after the copy -- gpu-scope fence + ticket 1-3.4 us, and for whoever counts a message's last row another fence and
+    // the system-scope release, 3-6.6 us with peer traffic outstanding -- is longer than a sample's arithmetic; with two
+    // lanes the CTA that published one message fell behind, was last again for the next one, and ended the kernel 10 us
+    // after the others (two CTAs published all eight messages of a step).
+    if (lane < kPubLanes) {
       uint32_t n = 0;
       for (int b = blockIdx.x; b < batch; b += gridDim.x, ++n) {
-        if ((n & 1) != (uint32_t)lane) continue;
+        if ((n & (kPubLanes - 1)) != (uint32_t)lane) continue;
         float* dst_row = out + (size_t)b * 4096;
         int msg = 0, slot = 0;
         if (span.data) {
           msg = b / span.rows_per_msg;
           slot = span_slot(span, msg);
           dst_row = reinterpret_cast<float*>(span.data + (size_t)slot * span.slot_bytes) + (size_t)(b - msg * span.rows_per_msg) * 4096;
-          if (msg != acquired) {
-            const unsigned long long k = ld_count(span.count + slot);    // messages already published into this slot
-            if (k > 0) {
-              if (b == msg * span.rows_per_msg) {
-                spin_until_ge_remote(span.released + slot, k);
-                st_release_gpu(span.acq_seen + slot, k);
-              } else {
-                while (ld_acquire_gpu(span.acq_seen + slot) < k) __nanosleep(64);
-              }
-            }
-            acquired = msg;
-          }
         }
+        B2P_TRACE2(2, n, 4, true);                              // slot acquired
         while (ld_acquire_cta(&s.staged) <= (int)n) __nanosleep(32);
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out[lane])),
+        B2P_TRACE2(2, n, 5, true);                              // sample staged
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_row), "r"(smem_u32(s.out[n & 1])),
                      "r"(64 * 64 * 4) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         cifar_tc::bulk_wait_read();                             // the staging buffer has been read
-        st_release_cta(&s.out_free[lane], (int)(n >> 1) + 1);
+        st_release_cta(&s.out_free[n & 1], (int)(n >> 1) + 1);
+        B2P_TRACE2(2, n, 6, true);                              // staging buffer read
         if (span.data) {
-          cifar_tc::bulk_wait_all();
+          const long long tq0 = dbg ? clock64() : 0;
+          cifar_tc::bulk_wait_all();                            // the row has arrived at the consumer
+          const long long tq1 = dbg ? clock64() : 0;
           __threadfence();
           const int rows = min(span.rows_per_msg, batch - msg * span.rows_per_msg);
           if (atomicAdd(span.tickets + slot, 1) == rows - 1) {
+            const long long tq2 = dbg ? clock64() : 0;
             span.tickets[slot] = 0;                             // ready for the slot's next message
             __threadfence();
             const unsigned long long k = ld_count(span.count + slot) + 1;
             span.count[slot] = k;
             st_release_sys(span.published + slot, k);
+            if (dbg && msg < 8) {                               // developer trace: who published message msg, and what it cost
+              dbg[760 + 4 * msg] = blockIdx.x * 16 + n;
+              dbg[761 + 4 * msg] = tq1 - tq0;                   // copy completion
+              dbg[762 + 4 * msg] = tq2 - tq1;                   // gpu-scope fence + ticket
+              dbg[763 + 4 * msg] = clock64() - tq2;             // fence + system-scope release
+            }
           }
+          B2P_TRACE2(2, n, 7, true);                            // row counted (and the message published, if it was the last)
         }
       }
       cifar_tc::bulk_wait_all();
@@ -673,7 +721,7 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
   __syncthreads();
   if (dbg && tid == kMmaWarp * 32 && blockIdx.x < 256) {     // exit (stamped by a thread that has work until the end)
     dbg[258 + 3 * blockIdx.x] = (long long)global_ns();
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == B2P_TRACE_CTA) {
       dbg[712] = clock64();
       dbg[736 + ((dbg[719] - 1) & 15)] = (long long)global_ns();
     }

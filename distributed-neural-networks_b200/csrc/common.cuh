@@ -113,11 +113,12 @@ inline int& pdl_call_mask() {
 }
 struct PdlScope {
   int prev;
-  explicit PdlScope(int mask) : prev(pdl_call_mask()) { if (mask >= 0) pdl_call_mask() = mask & 3; }
+  explicit PdlScope(int mask) : prev(pdl_call_mask()) { if (mask >= 0) pdl_call_mask() = mask & 7; }
   ~PdlScope() { pdl_call_mask() = prev; }
 };
 // bit 0: the light kernel chains (GEMMs, LayerNorm, attention, fc tail, splits); bit 1: the CIFAR part-0
-// kernel, whose CTAs each take a whole SM's shared memory while they wait.
+// kernel, whose CTAs each take a whole SM's shared memory while they wait; bit 2 (per stage only, b2p_stage_set_pdl):
+// the CIFAR part-0 kernel in ring mode does not wait for the preceding kernel of its stream at all (b200pipe.h).
 inline bool pdl_enabled(int bit = 1) {
   const int call = pdl_call_mask();
   return ((call >= 0 ? call : pdl_switch().load(std::memory_order_relaxed)) & bit) != 0;

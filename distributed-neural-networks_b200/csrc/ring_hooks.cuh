@@ -32,7 +32,7 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
 }
 __device__ __forceinline__ unsigned long long ld_count(const unsigned long long* p) {      // written by an earlier kernel
   unsigned long long v;
-  asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");     // (never from a stale L1 line)
   return v;
 }
 __device__ __forceinline__ uint64_t hook_ns() {

@@ -69,7 +69,10 @@ class CifarRankPipeline:
     ACT_BYTES = 4096 * 4            # per sample, the reference's fp32 [B,4096] handoff tensor
 
     def __init__(self, role: RankRole, device: torch.device, math: str, batch: int, microbatch: int,
-                 slots: int = 16, group=None):     # two steps of slots: the producer runs a step ahead of the consumer
+                 slots: int = 32, group=None):     # four steps of slots (64 MiB on the consumer GPU): the stage-0 kernels of
+                                                   # consecutive steps overlap (b2p_stage_set_pdl bit 2) and the consumer
+                                                   # releases a step's slots only at the end of its step; with two steps of
+                                                   # slots the producer waited for them (22.5 vs 26.0 M samples/s on 2 GPUs)
         import dnn_b200 as engine
         from .handoff import Ring
         self.role, self.dev, self.batch, self.mb = role, device, batch, microbatch
@@ -94,6 +97,10 @@ class CifarRankPipeline:
         if role.active and role.stage == 0:
             self.ring = Ring.open(handles[role.next_rank], device.index, slots, slot_bytes)
         if role.stage == 0:
+            # bit 2: the ring-mode kernel of step k+1 does not wait for step k's kernel -- its input is a resident buffer
+            # or an H2D copy ordered by an event, never the preceding kernel's output (b200pipe.h, b2p_stage_set_pdl)
+            if os.environ.get("B2P_RING_WAIT") != "1":
+                self.part.set_pdl(7)
             self.x_dev = [torch.empty((batch, 3, 32, 32), device=device) for _ in range(2)]
             self._x_free = [None, None]
             self._flip = 0
@@ -229,7 +236,7 @@ def bench_main(args) -> int:
     dist.init_process_group("nccl", device_id=dev)
     roles = plan(world, 2)
     role = roles[rank]
-    pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH)
+    pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH, slots=int(os.environ.get("B2P_RING_SLOTS", "32")))
     replicas = world // 2
     W, K = max(args.warmup, 3), args.steps
     n_pool = 16
@@ -296,24 +303,25 @@ def bench_main(args) -> int:
     torch.cuda.synchronize()
     dist.barrier()
     alone = torch.zeros(2, device=dev)
+    n_alone = max(2, pipe.slots // (BATCH // MICROBATCH)) if role.active else 2      # as many steps as the ring holds
     if role.active:
         pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         if role.stage == 0:
             pe0.record(pipe.stream)
-            for i in range(2):
+            for i in range(n_alone):
                 pipe.step_device(dev_pool[i % n_pool])
             pe1.record(pipe.stream)
             torch.cuda.synchronize()
-            alone[0] = 1e3 * pe0.elapsed_time(pe1) / 2
+            alone[0] = 1e3 * pe0.elapsed_time(pe1) / n_alone
     dist.barrier()
     if role.active and role.stage == 1:
         pe0.record(pipe.stream)
-        for i in range(2):
+        for i in range(n_alone):
             pipe.step_device(None)
         pipe.join()
         pe1.record(pipe.stream)
         torch.cuda.synchronize()
-        alone[1] = 1e3 * pe0.elapsed_time(pe1) / 2
+        alone[1] = 1e3 * pe0.elapsed_time(pe1) / n_alone
     dist.barrier()
     dist.all_reduce(alone, op=dist.ReduceOp.MAX)
     if os.environ.get("B2P_TRACE_RING") and rank == 0:       # developer aid: CTA 0's timeline of the ring-mode stage-0 kernel

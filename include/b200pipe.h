@@ -107,7 +107,15 @@ B2P_API int64_t     b2p_launch_count(void);
  * GPU on two streams.  Default 3.  Returns the previous mask.
  * b2p_set_pdl sets the process-wide DEFAULT; b2p_stage_set_pdl sets it for one stage (mask < 0:
  * back to the default) and is what a scheduler should use -- two pipelines, or two threads, in
- * one process then never see each other's setting. */
+ * one process then never see each other's setting.
+ * b2p_stage_set_pdl only, bit 2 (value 4), CIFAR part 0 writing into a handoff ring
+ * (b2p_stage_forward_ring_span): the kernel does not wait for the kernel that precedes it in the
+ * stream at all.  Consecutive steps write different ring slots, so step k+1's first samples are
+ * computed while step k's last messages are still being published (5-8 us of fences per step
+ * otherwise stand between two steps: 18 -> 26 M samples/s on two GPUs).  The caller promises that
+ * the stage's INPUT is not written by that preceding kernel (a resident buffer, or a copy ordered
+ * by an event -- not a kernel of the same stream); the library applies the bit only when the
+ * launch uses at most half of the ring's slots (this step and the next never share a slot). */
 B2P_API int b2p_set_pdl(int mask);
 
 /* ---- stage lifecycle (seam 1; node.py:300-317) ------------------------------- */

@@ -116,6 +116,23 @@ def test_forward_ring_handshake_inside_the_stage_kernels(cuda_engine, math):
             assert torch.equal(ob[:300], p1(p0(xb[:300]))), f"100-row messages, step {step}"
     with pytest.raises(L.EngineError, match="fewer slots"):
         p0.forward_ring(xb.data_ptr(), None, 1000, 0, None, prod8, 0, s, 64)
+    if math == "tf32x3":
+        # PDL mask bit 2: the stage-0 kernels of consecutive steps do not wait for each other (different slots, resident
+        # inputs).  Three producer steps back to back into a 32-slot ring, then the three consumer steps: same bits.
+        ring32 = Ring.create(0, slots=32, slot_bytes=128 * 4096 * 4)
+        prod32 = ring32.open_local(0)
+        xs3 = [co.make_input(1024, seed=90 + i).cuda() for i in range(3)]
+        prev = p0.set_pdl(7)
+        for rep in range(2):                                 # second round: the slots' counters are no longer zero
+            for i, x3 in enumerate(xs3):
+                p0.forward_ring(x3.data_ptr(), None, 1024, 0, None, prod32, 24 * rep + 8 * i, s, 128)
+            for i, x3 in enumerate(xs3):
+                ob3 = torch.empty(1024, 10, device="cuda:0")
+                p1.forward_ring(None, ob3.data_ptr(), 1024, 0, ring32, None, 24 * rep + 8 * i, s, 128)
+                torch.cuda.synchronize()
+                with torch.no_grad():
+                    assert torch.equal(ob3, p1(p0(x3))), f"no-wait ring mode, round {rep}, step {i}"
+        p0.set_pdl(prev)
     # wrong side / oversize / missing operands are refused before anything is enqueued
     with pytest.raises(L.EngineError, match="consumer side"):
         p1.forward_ring(None, outs[0].data_ptr(), 1, 0, prod, None, 0, s)
