@@ -205,18 +205,32 @@ int cifar_part1_forward(b2p_stage* st, const float* in, float* out, int64_t batc
       tail_stream = st->aux;
     }
     const b2p_weight& w = st->w[0];
-    const int parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, ws, batch, s, span);
-    if (parts < 0) return parts;
+    static const bool tf32_fc1 = [] { const char* e = getenv("B2P_FC1_TF32"); return e && e[0] == '1'; }();   // A/B: round 1's 3xTF32 kernel
+    int parts = 0, per_item = 0;
+    if (!tf32_fc1 && w.packed16) {
+      const __half* w16 = static_cast<const __half*>(w.packed16);
+      per_item = fcs::launch_fc1_f16x3_splitk(in, w16, w16 + w.elems(), ws, batch, st->bad_flag, s, span);
+      if (per_item < 0) return per_item;
+    } else {
+      parts = fcs::launch_fc1_x3_splitk(in, static_cast<const float*>(w.packed), w.packed_lo, ws, batch, s, span);
+      if (parts < 0) return parts;
+    }
     if (two_streams) {
       B2P_CUDA(cudaEventRecord(st->ev_fc1, s));
       B2P_CUDA(cudaStreamWaitEvent(st->aux, st->ev_fc1, 0));
     }
     const int tail_grid = (int)batch + (span.data ? 1 : 0);
-    if (parts == fcs::NSLICES)
-      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, true>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
+    if (per_item == 1)
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, 4>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
+                     st->dev(3), out, span);
+    else if (per_item == 4)
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 4, 1>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
+                     st->dev(3), out, span);
+    else if (parts == fcs::NSLICES)
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES, 2>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
                      st->dev(3), out, span);
     else
-      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 2, false>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
+      B2P_LAUNCH_PDL((fc_tail_f32<fcs::NSLICES / 2, 1>), tail_grid, 128, 0, tail_stream, ws, (int)batch, st->dev(1), st->dev(2),
                      st->dev(3), out, span);
     if (two_streams) {
       B2P_CUDA(cudaEventRecord(st->ev_tail[buf], st->aux));
@@ -553,6 +567,11 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
     int rc = alloc_gpt_workspace(st);
     if (rc < 0) { b2p_stage_destroy(st); return rc; }
   }
+  if (desc->kind == B2P_CIFAR_PART1) {
+    int rc = dev_alloc(&st->bad_flag, 1);                       // "a value left the split-fp16 range" (fc_stage_tc.cuh)
+    if (rc == 0 && cudaMemset(st->bad_flag, 0, sizeof(int)) != cudaSuccess) rc = fail(B2P_ECUDA, "cudaMemset(range flag)");
+    if (rc < 0) { b2p_stage_destroy(st); return rc; }
+  }
   if (desc->kind == B2P_CIFAR_PART0) {
     int rc = dev_alloc(&st->bad_flag, 1);                       // "a value left the split-fp16 range" (cifar_tc2.cuh)
     if (rc == 0 && cudaMemset(st->bad_flag, 0, sizeof(int)) != cudaSuccess) rc = fail(B2P_ECUDA, "cudaMemset(range flag)");
@@ -576,7 +595,7 @@ int b2p_stage_create(b2p_stage** out, const b2p_stage_desc* desc) {
 int b2p_stage_destroy(b2p_stage* st) {
   if (!st) return 0;
   DeviceGuard g(st->d.device);
-  for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); }
+  for (auto& w : st->w) { cudaFree(w.dev); cudaFree(w.packed); cudaFree(w.packed_lo); cudaFree(w.packed16); }
   cudaFree(st->ws_split); cudaFree(st->amax_val); cudaFree(st->amax_idx);
   cudaFree(st->kv_k); cudaFree(st->kv_v); cudaFree(st->w1t); cudaFree(st->w2t); cudaFree(st->w2img); cudaFree(st->a1img); cudaFree(st->w2tm); cudaFree(st->w2tap8); cudaFree(st->trace); cudaFree(st->fc_ws); cudaFree(st->fc_ws2);
   if (st->ev_fc1) { cudaEventDestroy(st->ev_fc1); cudaEventDestroy(st->ev_tail[0]); cudaEventDestroy(st->ev_tail[1]); }
@@ -674,6 +693,11 @@ int b2p_stage_finalize(b2p_stage* st) {
       if (!w.packed) B2P_CUDA(cudaMalloc(&w.packed, n * sizeof(float)));
       if (!w.packed_lo) B2P_CUDA(cudaMalloc((void**)&w.packed_lo, n * sizeof(float)));
       B2P_LAUNCH(split_tf32, elementwise_grid(n), 256, 0, 0, w.dev, static_cast<float*>(w.packed), w.packed_lo, n);
+      if (st->d.kind == B2P_CIFAR_PART1) {       // fc1 runs in split fp16 (fc_stage_tc.cuh): hi plane | lo plane
+        if (!w.packed16) B2P_CUDA(cudaMalloc(&w.packed16, 2 * n * sizeof(__half)));
+        B2P_LAUNCH(fcs::split_f16_planes, elementwise_grid(n), 256, 0, 0, w.dev, static_cast<__half*>(w.packed16),
+                   static_cast<__half*>(w.packed16) + n, n, st->bad_flag);
+      }
     }
   }
   // batch-dependent scratch, so that no forward up to these sizes ever allocates (b2p_stage_reserve raises them)
@@ -815,6 +839,11 @@ int b2p_stage_check(b2p_stage* st, void* stream) {
     B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));
     return fail(B2P_ELIMIT, "an input or conv1 output reached the fp16 range limit (|v| >= 65504) of the tensor-core math "
                             "modes: the affected samples are not finite where the reference's are; use math=fp32 for such data");
+  }
+  if (flag && st->d.kind == B2P_CIFAR_PART1) {
+    B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));
+    return fail(B2P_ELIMIT, "an activation or fc1 weight reached the fp16 range limit (|v| >= 65504) of the tensor-core math "
+                            "mode: the affected rows are not finite where the reference's are; use math=fp32 for such data");
   }
   if (flag) {
     B2P_CUDA(cudaMemsetAsync(st->bad_flag, 0, sizeof(int), s));

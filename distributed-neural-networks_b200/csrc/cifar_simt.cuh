@@ -207,9 +207,10 @@ fc1_splitk_f32(const float* __restrict__ x,     // [M,4096]
 //   out[m] = softmax(l)                    cifar_model_parts.py:55-57
 // ---------------------------------------------------------------------------------
 // SPLITS is compile-time so the partial-sum loads are all in flight together (they were a serial chain).
-// PAIRS: the partials are added two by two first ((p0+p1), (p2+p3), ...), the association the fc1 kernel of
-// fc_stage_tc.cuh uses when it sums pairs of K slices itself -- so 32 unpaired and 16 paired partials give the same bits.
-template <int SPLITS, bool PAIRS = false>
+// GROUP: the partials are first added in groups of GROUP, left to right (((p0+p1)+p2)+p3, ...), the association the fc1
+// kernels of fc_stage_tc.cuh use when they sum the K slices of an item themselves -- so 32 single-slice partials with
+// GROUP = 4 and 8 four-slice partials with GROUP = 1 give the same bits (GROUP = 2: the 3xTF32 kernel's slice pairs).
+template <int SPLITS, int GROUP = 1>
 __global__ void __launch_bounds__(128)
 fc_tail_f32(const float* __restrict__ ws, int M,
             const float* __restrict__ b1,
@@ -235,14 +236,12 @@ fc_tail_f32(const float* __restrict__ ws, int M,
 #pragma unroll
   for (int z = 0; z < SPLITS; ++z)      // plain loads, NOT __ldg: ws was written by the previous kernel, and the compiler
     p[z] = ld_produced(reinterpret_cast<const float4*>(ws + ((size_t)z * M + m) * FC1_N) + tid);   // may hoist ld.global.nc above pdl_wait()
-  if (PAIRS) {
 #pragma unroll
-    for (int z = 0; z < SPLITS; z += 2) {
-      h.x += p[z].x + p[z + 1].x; h.y += p[z].y + p[z + 1].y; h.z += p[z].z + p[z + 1].z; h.w += p[z].w + p[z + 1].w;
-    }
-  } else {
+  for (int z = 0; z < SPLITS; z += GROUP) {      // fixed order
+    float4 g = p[z];
 #pragma unroll
-    for (int z = 0; z < SPLITS; ++z) { h.x += p[z].x; h.y += p[z].y; h.z += p[z].z; h.w += p[z].w; }   // fixed order
+    for (int i = 1; i < GROUP; ++i) { g.x += p[z + i].x; g.y += p[z + i].y; g.z += p[z + i].z; g.w += p[z + i].w; }
+    h.x += g.x; h.y += g.y; h.z += g.z; h.w += g.w;
   }
   h.x = fmax_nan(h.x, 0.f); h.y = fmax_nan(h.y, 0.f); h.z = fmax_nan(h.z, 0.f); h.w = fmax_nan(h.w, 0.f);   // nn.ReLU keeps NaN
   __shared__ float part[4][10];

@@ -14,6 +14,7 @@ struct b2p_weight {
   float* dev = nullptr;             // fp32 copy in the original layout
   void* packed = nullptr;           // math-mode copy: bf16 (BF16) or tf32 hi plane (TF32X3)
   float* packed_lo = nullptr;       // TF32X3: lo plane
+  void* packed16 = nullptr;         // CIFAR fc1.weight, TF32X3: fp16 hi plane | fp16 lo plane (x 2^11), back to back (fc_stage_tc.cuh)
   size_t elems() const {
     size_t n = 1;
     for (auto d : shape) n *= (size_t)d;
