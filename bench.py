@@ -384,9 +384,16 @@ def engine_arm(args):
 
     # stage 1 is the memory-side kernel: fc1's weights once per launch + the [1024,4096] activation in
     bytes_p1 = 512 * 4096 * 4 + 10 * 512 * 4 + BATCH * (4096 + 10) * 4
-    roofline_stage1 = {"kernel": f"part 1 (fc1_x3_splitk + fc_tail), one launch each per step = {BATCH} rows",
+    traffic1 = None
+    try:                                                     # dram bytes per launch from the committed ncu capture
+        t1 = json.load(open(os.path.join(ROOT, "profiles", "part1_traffic.json")))
+        if t1.get("rows_per_launch") == BATCH:
+            traffic1 = t1["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    roofline_stage1 = {"kernel": f"part 1 (fc1_f16x3_splitk + fc_tail), one launch each per step = {BATCH} rows",
                        "bound": "hbm", "achieved": bytes_p1 / (us_k1 * 1e-6) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                       "frac": bytes_p1 / (us_k1 * 1e-6) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                       "frac": bytes_p1 / (us_k1 * 1e-6) / 1e9 / peaks["hbm_gbs"], "traffic": traffic1,
                        "us_per_launch": us_k1, "algorithmic_bytes_per_launch": bytes_p1,
                        "tensor_view": {"achieved_tflops": FLOP_PART1 * BATCH / (us_k1 * 1e-6) / 1e12,
                                        "note": "fp32-grade 3xTF32: three tensor-core products per algorithmic FLOP"}}

@@ -534,7 +534,7 @@ def gpt_flop_per_token(cfg, seq: int) -> float:
     return cfg.n_layer * (24 * cfg.n_embd ** 2 + 2 * seq * cfg.n_embd) + 2 * cfg.n_embd * cfg.vocab_size
 
 
-def gpt_bench(world: int, rank: int, dev: torch.device, peaks: dict, steps: int = 3, group=None) -> dict | None:
+def gpt_bench(world: int, rank: int, dev: torch.device, peaks: dict, steps: int = 8, group=None) -> dict | None:
     """Tokens/s of the GPT part chain over `world` GPUs, one CUDA-graph launch per rank per batch, timed on the device
     (max over ranks), plus a correctness bit: the greedy ids the LAST rank produced for the last microbatch, compared
     with the same tokens through a single-GPU chain of the same parts built on that rank (`ids_equal_single_gpu`)."""

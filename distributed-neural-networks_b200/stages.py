@@ -231,8 +231,8 @@ class _CifarPart(EngineStage):
     WHOLE_BATCH_OK = True       # no per-stage workspace bound: a pipeline on one GPU may run the batch in one call
 
     def check(self):
-        """Synchronise and raise on deferred device-side range errors (b2p_stage_check): part 0 in a tensor-core math
-        mode met a value beyond the fp16 range its hi/lo split can carry."""
+        """Synchronise and raise on deferred device-side range errors (b2p_stage_check): a part in a tensor-core math
+        mode met a value (input, conv1 output, fc1 activation or weight) beyond the fp16 range its hi/lo split can carry."""
         self._require_device()
         stream = torch.cuda.current_stream(self._device).cuda_stream
         _lib.check(_lib.lib().b2p_stage_check(self._handle, C.c_void_p(stream)))

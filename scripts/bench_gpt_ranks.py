@@ -41,27 +41,29 @@ pipe = rp.GptRankPipeline(role, dev, model, a.math, a.microbatch, a.seq, ranges=
 n_mb = a.batch // a.microbatch
 g = torch.Generator().manual_seed(0)
 idx = torch.randint(0, cfg.vocab_size, (a.batch, a.seq), generator=g).to(dev) if rank == 0 else None
-for _ in range(2):
-    pipe.step(idx, n_mb, a.head)
-torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record(pipe.stream)
-for _ in range(a.steps):
-    pipe.step(idx, n_mb, a.head)
-e1.record(pipe.stream)
-torch.cuda.synchronize(); dist.barrier()
-t = torch.tensor([e0.elapsed_time(e1)], device=dev)
-dist.all_reduce(t, op=dist.ReduceOp.MAX)
-ms = float(t[0]) / a.steps
-if rank == 0:
-    tokens = a.batch * a.seq
-    C_, L_, V_ = cfg.n_embd, cfg.n_layer, cfg.vocab_size
-    flop_tok = L_ * (24 * C_ * C_ + 2 * a.seq * C_) + 2 * C_ * V_
-    peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
-    tf = flop_tok * tokens / (ms * 1e-3) / 1e12
-    print(json.dumps({"workload": f"gpt2-{a.model} {world} stages B={a.batch} T={a.seq} microbatch={a.microbatch} seq head={a.head}",
-                      "ranges": ranges or "even", "math": a.math, "n_gpus": world, "ms_per_batch": ms,
-                      "tokens_per_s": tokens / (ms * 1e-3), "model_tflops_total": tf,
-                      "frac_of_sustained_bf16_peak_per_gpu": tf / world / peaks["bf16_tflops_sustained"]}), flush=True)
+peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+for mode in ("eager launches with programmatic dependent launch", "one CUDA graph per rank per batch"):
+    step = pipe.step if mode.startswith("eager") else pipe.step_graph
+    for _ in range(3):
+        step(idx, n_mb, a.head)
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(pipe.stream)
+    for _ in range(a.steps):
+        step(idx, n_mb, a.head)
+    e1.record(pipe.stream)
+    torch.cuda.synchronize(); dist.barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t[0]) / a.steps
+    if rank == 0:
+        tokens = a.batch * a.seq
+        C_, L_, V_ = cfg.n_embd, cfg.n_layer, cfg.vocab_size
+        flop_tok = L_ * (24 * C_ * C_ + 2 * a.seq * C_) + 2 * C_ * V_
+        tf = flop_tok * tokens / (ms * 1e-3) / 1e12
+        print(json.dumps({"workload": f"gpt2-{a.model} {world} stages B={a.batch} T={a.seq} microbatch={a.microbatch} seq head={a.head}",
+                          "launch": mode, "steps": a.steps, "ranges": ranges or "even", "math": a.math, "n_gpus": world, "ms_per_batch": ms,
+                          "tokens_per_s": tokens / (ms * 1e-3), "model_tflops_total": tf,
+                          "frac_of_sustained_bf16_peak_per_gpu": tf / world / peaks["bf16_tflops_sustained"]}), flush=True)
 dist.barrier()
 dist.destroy_process_group()

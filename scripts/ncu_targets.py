@@ -1,5 +1,5 @@
 """The two dominant CIFAR kernels at the bench's launch shape (one launch per 1024-sample step), for ncu:
-3 warm-up launches of each stage, then 2 more of each (the ones to capture: -k regex:"part0_tc|fc1_x3_splitk" -s 6 -c 4)."""
+3 warm-up launches of each stage, then 2 more of each (the ones to capture: -k regex:"part0_tc2|fc1_f16x3_splitk|fc_tail_f32" -s 9 -c 6)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch

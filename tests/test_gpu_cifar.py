@@ -338,3 +338,33 @@ def test_fp16_range_of_the_tensor_core_modes_is_guarded(cuda_engine):
     with torch.no_grad():
         act = p0_f32(x.cuda()).cpu()
     assert (act - want_act).abs().max().item() <= 2e-5 * want_act.abs().max().item()
+
+
+def test_fp16_range_of_the_tensor_core_fc1_is_guarded(cuda_engine):
+    """Part 1 in tf32x3 runs fc1 in split fp16 (fc_stage_tc.cuh): an activation at or beyond 65504 cannot be carried by
+    the fp16 hi/lo parts.  The stage flags it (b2p_stage_check -> B2P_ELIMIT); large but representable activations
+    (the 0..255-image case, O(1000)) keep the oracle's relative accuracy; fp32 mode has the reference's range."""
+    sd = co.init_state_dict(1234)
+    L = cuda_engine._lib
+    p1 = _tc_parts(cuda_engine, sd, "tf32x3")[1]
+    x = co.part0(co.make_input(130, seed=77), sd)
+    big = x * 2000.0                                                     # activations up to a few thousand
+    want = co.part1(big, sd)
+    with torch.no_grad():
+        probs = p1(big.cuda()).cpu()
+    p1.check()                                                           # inside the range: no error
+    decided = co.top2_margin(want) > 1e-3
+    assert torch.equal(probs.argmax(1)[decided], want.argmax(1)[decided])
+    assert (probs - want).abs().max().item() <= 1e-3                     # logits are O(1000): softmax amplifies 1e-7 relative
+    x2 = x.clone()
+    x2[5, 100] = 70000.0
+    with torch.no_grad():
+        p1(x2.cuda())
+    with pytest.raises(L.EngineError) as ei:
+        p1.check()
+    assert ei.value.code == L.ELIMIT and "fp16 range" in str(ei.value)
+    p1.check()                                                           # reported once, then clear
+    p1_f32 = _tc_parts(cuda_engine, sd, "fp32")[1]
+    with torch.no_grad():
+        got = p1_f32(x2.cuda()).cpu()
+    assert (got - co.part1(x2, sd)).abs().max().item() <= PROB_TOL
