@@ -396,7 +396,7 @@ def engine_arm(args):
                        "frac": bytes_p1 / (us_k1 * 1e-6) / 1e9 / peaks["hbm_gbs"], "traffic": traffic1,
                        "us_per_launch": us_k1, "algorithmic_bytes_per_launch": bytes_p1,
                        "tensor_view": {"achieved_tflops": FLOP_PART1 * BATCH / (us_k1 * 1e-6) / 1e12,
-                                       "note": "fp32-grade 3xTF32: three tensor-core products per algorithmic FLOP"}}
+                                       "note": "fp32-grade split fp16: three tensor-core products per algorithmic FLOP"}}
 
     cpu = None
     if not args.no_cpu_baseline:

@@ -69,7 +69,7 @@ class CifarRankPipeline:
     ACT_BYTES = 4096 * 4            # per sample, the reference's fp32 [B,4096] handoff tensor
 
     def __init__(self, role: RankRole, device: torch.device, math: str, batch: int, microbatch: int,
-                 slots: int = 32, group=None):     # four steps of slots (64 MiB on the consumer GPU): the stage-0 kernels of
+                 slots: int = 32, group=None, input_via_device: int | None = None):     # four steps of slots (64 MiB on the consumer GPU): the stage-0 kernels of
                                                    # consecutive steps overlap (b2p_stage_set_pdl bit 2) and the consumer
                                                    # releases a step's slots only at the end of its step; with two steps of
                                                    # slots the producer waited for them (22.5 vs 26.0 M samples/s on 2 GPUs)
@@ -104,6 +104,21 @@ class CifarRankPipeline:
             self.x_dev = [torch.empty((batch, 3, 32, 32), device=device) for _ in range(2)]
             self._x_free = [None, None]
             self._flip = 0
+            # Host-facing path: the input link is the limit (12.6 MB per step over one PCIe x16 = 4.4 M samples/s), and
+            # the stage-1 GPU of the pipeline has a host link of its own that carries 40 KB of results per step.  The
+            # second half of every batch therefore enters through THAT GPU (pinned host -> its memory) and crosses to
+            # this one over NVLink (6 MiB: 26 us) -- measured 110 GB/s for the two links together against 55 GB/s.
+            self.via = None
+            if input_via_device is not None and input_via_device != device.index:
+                self.via = torch.device("cuda", input_via_device)
+                self.half = (self.n_mb // 2) * microbatch
+                self.hop_stream = torch.cuda.Stream(device=device)
+                self._split_events = [tuple(torch.cuda.Event() for _ in range(3)) for _ in range(2)]
+                self._xd_hi = [xd[self.half:] for xd in self.x_dev]
+                self._hi_views = {}
+                with torch.cuda.device(self.via):
+                    self.via_stream = torch.cuda.Stream(device=self.via)
+                    self.x_via = [torch.empty((batch - self.half, 3, 32, 32), device=self.via) for _ in range(2)]
         else:
             self.out_dev = torch.empty((batch, 10), device=device)
             self.out_host = torch.empty((batch, 10)).pin_memory()
@@ -180,13 +195,31 @@ class CifarRankPipeline:
             if self._x_free[flip] is not None:
                 self.copy_stream.wait_event(self._x_free[flip])
             ready = []
-            with torch.cuda.stream(self.copy_stream):
-                if graph:
+            if graph and self.via is not None and 0 < self.half < self.batch:
+                arrived, own, ev = self._split_events[flip]                # (events are re-recorded every step)
+                if self._x_free[flip] is not None:
+                    self.via_stream.wait_event(self._x_free[flip])         # the hop that read this staging buffer is long done
+                    self.hop_stream.wait_event(self._x_free[flip])
+                with torch.cuda.stream(self.via_stream):                   # the stage-1 GPU's host link
+                    self.x_via[flip].copy_(self._x_host_hi(x_host), non_blocking=True)
+                    arrived.record(self.via_stream)
+                with torch.cuda.stream(self.copy_stream):                  # this GPU's host link
+                    xd[:self.half].copy_(x_host[:self.half], non_blocking=True)
+                    own.record(self.copy_stream)
+                with torch.cuda.stream(self.hop_stream):                   # its own stream: this GPU's host link never waits for the hop
+                    self.hop_stream.wait_event(arrived)
+                    self._xd_hi[flip].copy_(self.x_via[flip], non_blocking=True)   # stage-1 GPU -> this GPU over NVLink
+                    self.hop_stream.wait_event(own)
+                    ev.record(self.hop_stream)
+                ready.append(ev)
+            elif graph:
+                with torch.cuda.stream(self.copy_stream):
                     xd.copy_(x_host, non_blocking=True)
                     ev = torch.cuda.Event()
                     ev.record(self.copy_stream)
                     ready.append(ev)
-                else:
+            else:
+                with torch.cuda.stream(self.copy_stream):
                     for lo in range(0, self.batch, self.mb):
                         xd[lo:lo + self.mb].copy_(x_host[lo:lo + self.mb], non_blocking=True)
                         ev = torch.cuda.Event()
@@ -209,6 +242,13 @@ class CifarRankPipeline:
             # step's fc1 (on self.stream) is not ordered behind this step's tail
             with torch.cuda.stream(self.aux if self.two_streams else self.stream):
                 self.out_host.copy_(self.out_dev, non_blocking=True)
+
+    def _x_host_hi(self, x_host: torch.Tensor) -> torch.Tensor:
+        """Second half of a pinned host batch (the view is cached: host buffers recur)."""
+        v = self._hi_views.get(x_host.data_ptr())
+        if v is None:
+            v = self._hi_views[x_host.data_ptr()] = x_host[self.half:]
+        return v
 
     def join(self):
         """Make this rank's stream wait for tail kernels still running on the second stream."""
@@ -236,7 +276,11 @@ def bench_main(args) -> int:
     dist.init_process_group("nccl", device_id=dev)
     roles = plan(world, 2)
     role = roles[rank]
-    pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH, slots=int(os.environ.get("B2P_RING_SLOTS", "32")))
+    via = None
+    if role.active and role.stage == 0 and os.environ.get("B2P_SPLIT_H2D", "1") != "0":
+        via = dev.index + (role.next_rank - rank)            # one node: the stage-1 GPU of this pipeline
+    pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH, slots=int(os.environ.get("B2P_RING_SLOTS", "32")),
+                             input_via_device=via)
     replicas = world // 2
     W, K = max(args.warmup, 3), args.steps
     n_pool = 16
@@ -417,6 +461,8 @@ def bench_main(args) -> int:
                        "l2_policy": f"inputs rotate over {n_pool} distinct batches = 201 MB > 126 MB L2"},
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
                     "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0]),
+                    "input_path": ("half of every batch over the stage-0 GPU's host link, half over the stage-1 GPU's and on over NVLink"
+                                   if os.environ.get("B2P_SPLIT_H2D", "1") != "0" else "all over the stage-0 GPU's host link"),
                     "max_abs_diff_vs_single_gpu_path": float(mt[0])},
             "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None, "gpt": gpt,
             "stage_times": {"stage0_us_ring": float(alone[0]), "stage1_us_fed": float(alone[1]), "step_us": 1e3 * ms_dev / K,
