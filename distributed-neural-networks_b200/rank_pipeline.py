@@ -276,8 +276,14 @@ def bench_main(args) -> int:
     dist.init_process_group("nccl", device_id=dev)
     roles = plan(world, 2)
     role = roles[rank]
+    # Host-facing path: a pipeline's input may enter over both of its GPUs' host links (CifarRankPipeline).  Worth it while
+    # the links are the limit: 2 pipelines (4 GPUs) 8.8 -> 13.2 M samples/s; with 4 pipelines all eight links together
+    # ask the host for more than its memory system delivers (~200 GB/s measured: 15.1 M split against 17.2 M over the
+    # four stage-0 links alone), so from 3 pipelines up the input stays on the stage-0 links.  B2P_SPLIT_H2D=0/1 forces it.
     via = None
-    if role.active and role.stage == 0 and os.environ.get("B2P_SPLIT_H2D", "1") != "0":
+    split_env = os.environ.get("B2P_SPLIT_H2D", "")
+    split_h2d = (split_env == "1") or (split_env != "0" and world // 2 <= 2)
+    if role.active and role.stage == 0 and split_h2d:
         via = dev.index + (role.next_rank - rank)            # one node: the stage-1 GPU of this pipeline
     pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH, slots=int(os.environ.get("B2P_RING_SLOTS", "32")),
                              input_via_device=via)
@@ -462,7 +468,7 @@ def bench_main(args) -> int:
             "e2e": {"value": total / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": BATCH * 3 * 32 * 32 * 4 * replicas,
                     "d2h_bytes_per_step": BATCH * 10 * 4 * replicas, "ms_per_step": ms_e2e / K, "result_checksum": float(ct[0]),
                     "input_path": ("half of every batch over the stage-0 GPU's host link, half over the stage-1 GPU's and on over NVLink"
-                                   if os.environ.get("B2P_SPLIT_H2D", "1") != "0" else "all over the stage-0 GPU's host link"),
+                                   if split_h2d else "all over the stage-0 GPU's host link"),
                     "max_abs_diff_vs_single_gpu_path": float(mt[0])},
             "gpu_launches": int(lt[0]), "clocks": clocks, "roofline": roofline, "cpu_baseline": None, "gpt": gpt,
             "stage_times": {"stage0_us_ring": float(alone[0]), "stage1_us_fed": float(alone[1]), "step_us": 1e3 * ms_dev / K,
