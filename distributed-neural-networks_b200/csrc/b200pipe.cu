@@ -176,7 +176,7 @@ constexpr int FC1_SPLITS_TC = 16;
 
 int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
                  bool out_bf16, int M, int N, int K, cudaStream_t s, int splits = 1, int64_t split_stride = 0,
-                 float* amax_val = nullptr, int* amax_idx = nullptr, int amax_slots = 0);
+                 float* amax_val = nullptr, int* amax_idx = nullptr, int amax_slots = 0, int amax_bn = 128);
 
 // B2P_FC_FUSED=0 keeps the three-kernel path (split, split-K linear, tail) for A/B measurements
 bool fc_fused_enabled() {
@@ -284,7 +284,7 @@ int split_activation(b2p_stage* st, const float* A, size_t n, cudaStream_t s) {
 // where the producer wrote it as bf16; `out` is fp32 unless out_bf16.
 int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, const float* res, void* out,
                  bool out_bf16, int M, int N, int K, cudaStream_t s, int splits, int64_t split_stride,
-                 float* amax_val, int* amax_idx, int amax_slots) {
+                 float* amax_val, int* amax_idx, int amax_slots, int amax_bn) {
   const float* bias = st->dev(bidx);
   const b2p_weight& w = st->w[widx];
   tc::EpiParams ep{bias, res, out, N, N, out_bf16 ? 1 : 0, act, split_stride, amax_val, amax_idx, amax_slots};
@@ -293,7 +293,7 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
     case B2P_MATH_FP32:
       return linear(act, static_cast<const float*>(A), w.dev, bias, res, static_cast<float*>(out), M, N, K, s);
     case B2P_MATH_TF32:
-      rc = tc::linear_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
+      rc = tc::linear_dispatch(1, A, nullptr, K, w.dev, nullptr, K, ep, M, N, K, splits, amax_val ? amax_bn : 0, s);
       break;
     case B2P_MATH_TF32X3:
       B2P_TRY(split_activation(st, static_cast<const float*>(A), (size_t)M * K, s));
@@ -301,7 +301,7 @@ int stage_linear(b2p_stage* st, int act, const void* A, int widx, int bidx, cons
                                   ep, M, N, K, splits, 0, s);
       break;
     case B2P_MATH_BF16:
-      rc = tc::linear_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, amax_val ? 128 : 0, s);
+      rc = tc::linear_dispatch(0, A, nullptr, K, w.packed, nullptr, K, ep, M, N, K, splits, amax_val ? amax_bn : 0, s);
       break;
     default:
       return fail(B2P_EINVAL, "unknown math mode %d", st->d.math);
@@ -490,10 +490,15 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
   if (!ids_out) return stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, out, false, M, V, C, s);
   if (st->d.math != B2P_MATH_FP32) {
     // tensor-core modes: arg-max fused into the LM-head epilogue, logits never materialised
-    const int slots = 2 * ceil_div(V, 128);              // the head runs with 128-wide tiles here
+    // tile width of the head: 256 wide (half the shared-memory traffic per MMA, N = 256 MMAs at the tensor pipe's rate)
+    // whenever such tiles still fill the GPU, else 128; two partial results (column halves) per tile and row
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, st->d.device);
+    const int head_bn = (st->d.math != B2P_MATH_TF32X3 && (int64_t)ceil_div(M, 128) * ceil_div(V, 256) >= sms) ? 256 : 128;
+    const int slots = 2 * ceil_div(V, head_bn);
     B2P_TRY(reserve_amax(st, (size_t)M * slots, s, true));
     B2P_TRY(stage_linear(st, EPI_NONE, st->ws_ln, st->head, -1, nullptr, st->amax_val /*unused*/, false, M, V, C, s, 1, 0,
-                         st->amax_val, st->amax_idx, slots));
+                         st->amax_val, st->amax_idx, slots, head_bn));      // (the CTA-pair kernel measured the same: 2.75 vs 2.77 M tokens/s)
     B2P_LAUNCH_PDL(argmax_partials, ceil_div((int64_t)M * 32, 256), 256, 0, s, st->amax_val, st->amax_idx, ids_out, M, slots);
     return 0;
   }
