@@ -58,6 +58,7 @@ _PROTOTYPES = {
     "b2p_stage_kv_reset": (C.c_int, [C.c_void_p, C.c_int64]),
     "b2p_stage_forward_kv": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
                                        C.c_void_p]),
+    "b2p_stage_forward_kv_at": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "b2p_debug_attn_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "b2p_debug_fc_trace": (C.c_int, [C.POINTER(C.c_longlong), C.c_int]),
     "b2p_stage_check": (C.c_int, [C.c_void_p, C.c_void_p]),

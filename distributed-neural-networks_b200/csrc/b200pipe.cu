@@ -351,7 +351,8 @@ int layernorm(b2p_stage* st, const float* x, int gi, int bi, void* y, int M, int
 // output) are written as bf16 by their producers.
 // pos0 < 0: plain forward.  pos0 >= 0: the rows are positions pos0 .. pos0+T-1 of their sequences; their keys and values
 // go into the stage's KV cache, and a single new position (T == 1, pos0 > 0) attends to the cache instead of recomputing.
-int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s, int pos0 = -1) {
+int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cudaStream_t s, int pos0 = -1,
+               const int* pos_dev = nullptr) {      // pos_dev: one new position per sequence, its index in device memory (pos0 > 0 then only says "decode")
   const int C = st->d.n_embd, H = st->d.n_head, M = B * T;
   const bool bf = st->d.math == B2P_MATH_BF16;
   const float* cur = x;
@@ -371,17 +372,17 @@ int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cu
       const int64_t n = (int64_t)M * H * 16;
       if (bf)
         B2P_LAUNCH_PDL(kv::kv_append<__nv_bfloat16>, ceil_div(n, 256), 256, 0, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
-                       kc, vc, B, T, C, H, Tmax, pos0);
+                       kc, vc, B, T, C, H, Tmax, pos0, pos_dev);
       else
-        B2P_LAUNCH_PDL(kv::kv_append<float>, ceil_div(n, 256), 256, 0, s, st->ws_qkv, kc, vc, B, T, C, H, Tmax, pos0);
+        B2P_LAUNCH_PDL(kv::kv_append<float>, ceil_div(n, 256), 256, 0, s, st->ws_qkv, kc, vc, B, T, C, H, Tmax, pos0, pos_dev);
       if (decode) {
         const size_t smem = ((size_t)Tmax + 64 + 128) * sizeof(float);
         dim3 dgrid(H, B);
         if (bf)
           B2P_LAUNCH_PDL(kv::attention_decode<__nv_bfloat16>, dgrid, 128, smem, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
-                         kc, vc, reinterpret_cast<__nv_bfloat16*>(st->ws_att), C, H, Tmax, pos0);
+                         kc, vc, reinterpret_cast<__nv_bfloat16*>(st->ws_att), C, H, Tmax, pos0, pos_dev);
         else
-          B2P_LAUNCH_PDL(kv::attention_decode<float>, dgrid, 128, smem, s, st->ws_qkv, kc, vc, st->ws_att, C, H, Tmax, pos0);
+          B2P_LAUNCH_PDL(kv::attention_decode<float>, dgrid, 128, smem, s, st->ws_qkv, kc, vc, st->ws_att, C, H, Tmax, pos0, pos_dev);
       }
     }
     if (decode) {
@@ -456,7 +457,7 @@ int reserve_rows(b2p_stage* st, int64_t rows) {
 }
 
 int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t seq, cudaStream_t s,
-                int64_t* ids_out, int pos0 = -1) {
+                int64_t* ids_out, int pos0 = -1, const int* pos_dev = nullptr) {
   B2P_TRY(check_gpt_geometry(st, batch, seq));
   if (pos0 >= 0) {
     if (!st->blocks.empty() && (!st->kv_k || batch > st->kv_batch))
@@ -474,16 +475,16 @@ int gpt_forward(b2p_stage* st, const void* in, void* out, int64_t batch, int64_t
     // (with its own output) only after reading it for the last time.
     float* emb = st->blocks.empty() ? static_cast<float*>(out) : st->ws_x[1];
     B2P_LAUNCH(embed_f32, ceil_div((int64_t)M * 32, 256), 256, 0, s, static_cast<const int64_t*>(in),
-               st->dev(st->wte), st->dev(st->wpe), emb, M, T, C, V, st->bad_flag, pos0 > 0 ? pos0 : 0);
+               st->dev(st->wte), st->dev(st->wpe), emb, M, T, C, V, st->bad_flag, pos0 > 0 ? pos0 : 0, pos_dev, st->d.block_size);
     if (st->blocks.empty()) return 0;
-    return gpt_blocks(st, emb, static_cast<float*>(out), B, T, s, pos0);
+    return gpt_blocks(st, emb, static_cast<float*>(out), B, T, s, pos0, pos_dev);
   }
-  if (st->d.kind == B2P_GPT_MIDDLE) return gpt_blocks(st, x, static_cast<float*>(out), B, T, s, pos0);
+  if (st->d.kind == B2P_GPT_MIDDLE) return gpt_blocks(st, x, static_cast<float*>(out), B, T, s, pos0, pos_dev);
 
   // final: blocks -> ln_f -> lm_head                          gpt_model_parts.py:44-50
   const float* hx = x;
   if (!st->blocks.empty()) {
-    B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s, pos0));    // ws_att is free after the last block's proj
+    B2P_TRY(gpt_blocks(st, x, st->ws_att, B, T, s, pos0, pos_dev));    // ws_att is free after the last block's proj
     hx = st->ws_att;
   }
   B2P_TRY(layernorm(st, hx, st->lnf_w, st->lnf_b, st->ws_ln, M, C, s));
@@ -887,6 +888,19 @@ int b2p_stage_forward_kv(b2p_stage* st, const void* in_dev, void* out_dev, int64
   DeviceGuard g(st->d.device);
   PdlScope pdl(st->pdl_mask);
   return gpt_forward(st, in_dev, out_dev, batch, seq, static_cast<cudaStream_t>(stream), ids_dev, (int)pos0);
+}
+
+int b2p_stage_forward_kv_at(b2p_stage* st, const void* in_dev, void* out_dev, int64_t* ids_dev, int64_t batch,
+                            const int32_t* pos_dev, void* stream) {
+  if (!st || !in_dev || !pos_dev) return fail(B2P_EINVAL, "null argument");
+  if (st->d.kind < B2P_GPT_FIRST) return fail(B2P_EINVAL, "forward_kv_at: only GPT stages keep a key/value cache");
+  if (!st->finalized) return fail(B2P_ESTATE, "stage_forward called before stage_finalize");
+  if (st->d.kind == B2P_GPT_FINAL ? (!out_dev && !ids_dev) : !out_dev) return fail(B2P_EINVAL, "forward_kv_at: no output");
+  if (ids_dev && st->d.kind != B2P_GPT_FINAL) return fail(B2P_EINVAL, "forward_kv_at: greedy ids come from the final stage");
+  DeviceGuard g(st->d.device);
+  PdlScope pdl(st->pdl_mask);
+  // pos0 = 1 only selects the decode path; the kernels read the position from pos_dev
+  return gpt_forward(st, in_dev, out_dev, batch, 1, static_cast<cudaStream_t>(stream), ids_dev, 1, reinterpret_cast<const int*>(pos_dev));
 }
 
 int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t* ids_dev, int64_t batch, int64_t seq,

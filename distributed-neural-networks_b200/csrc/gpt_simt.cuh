@@ -19,9 +19,11 @@ namespace b2p {
 __global__ void __launch_bounds__(256)
 embed_f32(const int64_t* __restrict__ idx, const float* __restrict__ wte,
           const float* __restrict__ wpe, float* __restrict__ out,
-          int M, int T, int C, int V, int* __restrict__ bad_flag, int pos0) {      // pos0: position of column 0 (KV-cache decoding)
+          int M, int T, int C, int V, int* __restrict__ bad_flag, int pos0,        // pos0: position of column 0 (KV-cache decoding)
+          const int* pos_dev, int pos_limit) {      // pos_dev != null: the position comes from device memory (clamped below pos_limit)
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= M) return;
+  if (pos_dev) pos0 = min(max(*pos_dev, 0), pos_limit - T);
   long long tok = idx[warp];
   if (tok < 0 || tok >= V) {
     if (lane == 0) atomicExch(bad_flag, 1);

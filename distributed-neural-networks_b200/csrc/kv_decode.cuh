@@ -26,12 +26,13 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 kv_append(const T* qkv, float* kc, float* vc,      // no __restrict__: qkv comes from the previous kernel (PDL), plain loads stay behind the wait
           int B, int Tn, int C, int H,
-          int Tmax, int pos0) {
+          int Tmax, int pos0, const int* pos_dev) {      // pos_dev != null: the position comes from device memory (CUDA-graph decoding)
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t total = (int64_t)B * Tn * H * 16;
   pdl_trigger();
   pdl_wait();
-  if (i >= total) return;
+  if (pos_dev) pos0 = ld_produced(pos_dev);
+  if (i >= total || pos0 < 0 || pos0 + Tn > Tmax) return;      // (a position beyond the cache: nothing is stored)
   const int d4 = (int)(i % 16), h = (int)((i / 16) % H);
   const int64_t row = i / (16 * H);
   const int b = (int)(row / Tn), t = (int)(row % Tn);
@@ -50,14 +51,15 @@ kv_append(const T* qkv, float* kc, float* vc,      // no __restrict__: qkv comes
 //   pass 3: threads (half, d): half of the keys each, one output dim -- coalesced 256-byte reads of the value rows
 template <typename T>
 __global__ void __launch_bounds__(128)
-attention_decode(const T* qkv, const float* kc, const float* vc, T* y, int C, int H, int Tmax, int pos) {
+attention_decode(const T* qkv, const float* kc, const float* vc, T* y, int C, int H, int Tmax, int pos, const int* pos_dev) {
   extern __shared__ float sc[];                       // [Tmax] scores, then 64 q values, then scratch
   float* q = sc + Tmax;
   float* red = q + 64;                                 // [128]
   const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
-  const int n = pos + 1;
   pdl_trigger();
   pdl_wait();
+  if (pos_dev) pos = ld_produced(pos_dev);             // CUDA-graph decoding: the position lives in device memory
+  const int n = min(max(pos, 0), Tmax - 1) + 1;
   if (tid < 64) q[tid] = to_f32(qkv[(int64_t)b * 3 * C + h * 64 + tid]) * 0.125f;       // 1/sqrt(64), exact
   __syncthreads();
   const float* kb = kc + ((int64_t)b * H + h) * Tmax * 64;

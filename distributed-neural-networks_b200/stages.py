@@ -387,6 +387,20 @@ class _GptPart(EngineStage):
                                                    C.c_void_p(stream)))
         return out
 
+    def forward_kv_at(self, x, pos_t: torch.Tensor, out: torch.Tensor, want_ids: bool = False):
+        """One new position per sequence at the position stored in ``pos_t`` (int32 scalar tensor on this device), read
+        by the kernels when they run (b2p_stage_forward_kv_at): no launch carries a step-dependent argument, so a decode
+        step can live in a CUDA graph.  ``x``: [B,1] ids or [B,1,C] hidden states; ``out``: preallocated [B,1] int64
+        (``want_ids``, final part) or [B,1,C] / [B,1,V] fp32."""
+        self._require_device()
+        self._finalize()
+        assert pos_t.dtype == torch.int32 and pos_t.device == self._device and x.is_contiguous() and out.is_contiguous()
+        stream = torch.cuda.current_stream(self._device).cuda_stream
+        args = (None, C.c_void_p(out.data_ptr())) if want_ids else (C.c_void_p(out.data_ptr()), None)
+        _lib.check(_lib.lib().b2p_stage_forward_kv_at(self._handle, C.c_void_p(x.data_ptr()), args[0], args[1], x.shape[0],
+                                                      C.c_void_p(pos_t.data_ptr()), C.c_void_p(stream)))
+        return out
+
     def _full_keys(self):
         return list(self._shape_table)
 
@@ -518,13 +532,16 @@ class ModelPartFinal_GPT(_GptPart):
 
 
 @torch.no_grad()
-def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True):
+def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True, graph: bool = False):
     """Greedy decoding through a chain of GPT parts: the arg-max of the LAST position is appended, the
     head never materialises [B,T,V].  The reference only ever does one full-sequence forward
     (gpt_model_parts.py:44-50).  With ``kv_cache`` the prompt is run once (prefill) and every further token costs one
     position per stage (keys / values of earlier positions are kept per block, csrc/kv_decode.cuh); positions are
     absolute, so once the context would exceed block_size the loop falls back to what the public nanoGPT ``generate``
-    does: re-run the chain on the context cropped to block_size.  idx: int64 [B,T0]; returns [B,T0+new]."""
+    does: re-run the chain on the context cropped to block_size.  ``graph`` (parts on one GPU): the decode step -- every
+    stage, the feedback of the new token and the advance of the position, which lives in device memory -- is captured
+    once in a CUDA graph and replayed per token (a step is ~110 launches for 12 blocks; the graph frees the host thread,
+    the step time itself is set by the kernels' fixed latencies).  idx: int64 [B,T0]; returns [B,T0+new]."""
     block_size = parts[0].config.block_size
     idx = idx.to(parts[0]._device)
 
@@ -546,6 +563,10 @@ def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True):
         nxt = chain(idx, 0)                                   # prefill
         idx = torch.cat([idx, nxt], dim=1)
         done = 1
+        n_graph = min(max_new_tokens - done, block_size - idx.shape[1] + 1)
+        if graph and n_graph > 1 and len({p._device for p in parts}) == 1:
+            idx = torch.cat([idx, _decode_steps_graph(parts, nxt, idx.shape[1] - 1, n_graph)], dim=1)
+            done += n_graph
         while done < max_new_tokens and idx.shape[1] <= block_size:
             nxt = chain(idx[:, -1:], idx.shape[1] - 1)        # the token just appended sits at position len-1
             idx = torch.cat([idx, nxt], dim=1)
@@ -554,6 +575,44 @@ def greedy_generate(parts, idx, max_new_tokens: int, kv_cache: bool = True):
         x = idx if idx.shape[1] <= block_size else idx[:, -block_size:]
         idx = torch.cat([idx, chain(x)], dim=1)
     return idx
+
+
+def _decode_steps_graph(parts, tok, pos: int, n: int):
+    """n decode steps as n replays of ONE CUDA graph: tok [B,1] is the token at position ``pos`` (already appended to the
+    context); returns the n following tokens [B,n]."""
+    dev = parts[0]._device
+    b = tok.shape[0]
+    cfg = parts[0].config
+    tok = tok.to(dev).contiguous().clone()
+    pos_t = torch.tensor([pos], dtype=torch.int32, device=dev)
+    hid = [torch.empty((b, 1, cfg.n_embd), dtype=torch.float32, device=dev) for _ in parts[:-1]]
+    ids = torch.empty((b, 1), dtype=torch.int64, device=dev)
+    gen = torch.zeros((b, n), dtype=torch.int64, device=dev)
+
+    def stages():
+        x = tok
+        for k, p in enumerate(parts):
+            lastp = k == len(parts) - 1
+            x = p.forward_kv_at(x, pos_t, ids if lastp else hid[k], want_ids=lastp)
+
+    def advance():
+        gen.index_copy_(1, (pos_t - pos).to(torch.int64), ids)      # column = steps done so far, computed on the device
+        tok.copy_(ids)
+        pos_t.add_(1)
+
+    stages()                                                  # warm-up outside the capture (idempotent: same token, same position)
+    torch.cuda.synchronize(dev)
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            stages()
+            advance()
+        for _ in range(n):
+            g.replay()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    return gen
 
 
 # node.py:29-32

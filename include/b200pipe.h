@@ -220,6 +220,16 @@ B2P_API int b2p_stage_forward_argmax(b2p_stage* st, const void* in_dev, int64_t*
 B2P_API int b2p_stage_kv_reset(b2p_stage* st, int64_t batch);
 B2P_API int b2p_stage_forward_kv(b2p_stage* st, const void* in_dev, void* out_dev, int64_t* ids_dev, int64_t batch,
                                  int64_t seq, int64_t pos0, void* stream);
+/* The decode step with the position in DEVICE memory (int32, the same for every sequence): one new position per
+ * sequence at *pos_dev, read by the kernels when they run.  No launch then carries a step-dependent argument, so a whole
+ * decode step through every stage (about 110 kernels for 12 blocks) can be captured ONCE in a CUDA graph and replayed
+ * per token -- one launch per token from a host thread that has better things to do; the caller advances *pos_dev (and
+ * feeds the new token back) inside the same graph.  (The step itself is bound by the fixed latency of its small kernels,
+ * not by their launches: 1.03 ms per position either way for GPT-2 small, B = 8.)  Requires the prefill through b2p_stage_forward_kv(pos0 = 0).  A position at or beyond
+ * block_size stores nothing and attends to the last cached position (the caller bounds the number of replays).
+ * No counterpart in the reference (gpt_model_parts.py:13-50 runs one full-sequence forward). */
+B2P_API int b2p_stage_forward_kv_at(b2p_stage* st, const void* in_dev, void* out_dev, int64_t* ids_dev, int64_t batch,
+                            const int32_t* pos_dev, void* stream);
 
 /* ---- dense contraction building block (tcgen05 tensor cores) ------------------------
  *   out[m,n] = act( sum_k A[m,k] * W[n,k] + bias[n] ) + res[m,n]

@@ -251,6 +251,31 @@ def test_greedy_generation_matches_the_oracle(cuda_engine, math, kv_cache):
     assert len(set(want[0, 5:].tolist())) > 5                 # a real sequence, not one token repeated
 
 
+@pytest.mark.parametrize("math", ["fp32", "tf32x3", "bf16"])
+def test_graph_decoding_equals_eager_kv_decoding(cuda_engine, math):
+    """b2p_stage_forward_kv_at: the decode step with its position in device memory, captured once in a CUDA graph and
+    replayed per token (stages.greedy_generate(graph=True)), yields exactly the token ids of the eager KV-cache loop --
+    same kernels, same arithmetic -- including the run past block_size, where both fall back to the cropped context."""
+    cfg = cuda_engine.GPTConfig(block_size=48, vocab_size=211, n_layer=3, n_head=2, n_embd=128)
+    sd = gpt_oracle.init_state_dict(gpt_model.GPTConfig(block_size=48, vocab_size=211, n_layer=3, n_head=2, n_embd=128), seed=13)
+    g = torch.Generator().manual_seed(6)
+    for k in sd:
+        if k.endswith("weight") and "ln_" not in k and "wte" not in k and "wpe" not in k and "lm_head" not in k:
+            sd[k] = sd[k] * 12
+        if k.endswith("bias") or "ln_" in k:
+            sd[k] = sd[k] + 0.1 * torch.randn(sd[k].shape, generator=g)
+    model = cuda_engine.GPT(cfg)
+    model.load_state_dict(sd)
+    parts = [p.to("cuda:0").eval() for p in cuda_engine.gpt_parts_for(model, 2, math=math, max_tokens=4 * 48)]
+    prompt = gpt_oracle.make_tokens(4, 9, cfg.vocab_size, seed=3)
+    for new in (1, 2, 30, 45):                            # 45: 9 + 45 > block_size, the tail runs on the cropped context
+        eager = cuda_engine.greedy_generate(parts, prompt, new, kv_cache=True).cpu()
+        graph = cuda_engine.greedy_generate(parts, prompt, new, kv_cache=True, graph=True).cpu()
+        assert graph.shape == (4, 9 + new)
+        assert torch.equal(graph, eager), f"{math}, {new} new tokens"
+    assert len(set(eager[0, 9:].tolist())) > 5                # a real sequence, not one token repeated
+
+
 @pytest.mark.parametrize("math,tol", [("fp32", LOGIT_TOL), ("tf32x3", LOGIT_TOL), ("bf16", 3e-2)])
 def test_kv_cache_steps_equal_the_full_forward(cuda_engine, math, tol):
     """forward_kv: the prefill returns what forward returns, and every cached single-position step returns the last
