@@ -717,12 +717,11 @@ part0_tc2(const float* __restrict__ x,                    // [B,3,32,32]
     __syncwarp();
   }
 
-  // no_wait: the wait skipped at the top happens here, where it costs nothing (the preceding kernel finished long ago):
-  // this grid then still COMPLETES after it, so whatever waits for this grid is ordered behind it as well.
-  // (Tried on ONE GPU too -- alternating activation buffers, the next step's stage-0 kernel not waiting for the tail kernel
-  //  of this one: no gain, 67.8 us per step either way; the tail's 1024 small CTAs hold every SM's registers until they
-  //  have drained, and a slim persistent tail that would leave room took 18 us instead of 7.)
-  if (no_wait && tid == 0) pdl_wait();
+  // (no_wait: executing the skipped griddepcontrol.wait HERE, so that the grid at least completes after its predecessor,
+  //  was measured to cost the whole gain -- 49.9 against 39.3 us per step on two GPUs -- and nothing on the producer GPU
+  //  needs that order.  Tried on ONE GPU too -- alternating activation buffers, the next step's stage-0 kernel not waiting
+  //  for the tail kernel of this one: no gain, 67.8 us per step either way; the tail's 1024 small CTAs hold every SM's
+  //  registers until they have drained, and a slim persistent tail that would leave room took 18 us instead of 7.)
   tc_fence_before();
   __syncthreads();
   if (dbg && tid == kMmaWarp * 32 && blockIdx.x < 256) {     // exit (stamped by a thread that has work until the end)

@@ -501,6 +501,16 @@ class GptRankPipeline:
         self.stream = torch.cuda.Stream(device=device)
         parts = engine.gpt_parts_for(model, role.stages, math=math, max_tokens=mb_seqs * seq, ranges=ranges)
         self.part = parts[role.stage].to(device).eval()
+        # Two lanes (B2P_GPT_LANES=2): a second instance of the stage (own workspaces, own copy of the weights) on a second
+        # stream takes every other microbatch, so the kernels of microbatch i+1 fill the SMs that the last wave of
+        # microbatch i's kernels leaves idle (2048-token GEMMs are 1.3 to 2 waves of tiles on 148 SMs).
+        self.lanes = max(1, min(2, int(os.environ.get("B2P_GPT_LANES", "2"))))
+        self.parts_l = [self.part]
+        self.streams_l = [self.stream]
+        if self.lanes == 2:
+            parts2 = engine.gpt_parts_for(model, role.stages, math=math, max_tokens=mb_seqs * seq, ranges=ranges)
+            self.parts_l.append(parts2[role.stage].to(device).eval())
+            self.streams_l.append(torch.cuda.Stream(device=device))
         slot_bytes = mb_seqs * seq * cfg.n_embd * 4
         self.ring_in = self.ring_out = None
         mine = None
@@ -513,31 +523,39 @@ class GptRankPipeline:
         self.seq_no = 0
         self.is_last = role.next_rank is None
         if self.is_last:
-            self.ids = torch.empty((mb_seqs, seq), dtype=torch.int64, device=device)
+            self.ids_l = [torch.empty((mb_seqs, seq), dtype=torch.int64, device=device) for _ in range(self.lanes)]
+            self.ids = self.ids_l[0]          # the ids of the microbatch processed last
             self.logits = None
 
     def step(self, idx_batch: torch.Tensor | None, n_microbatches: int, head: str = "ids"):
         """One batch = n_microbatches microbatches of mb_seqs sequences through this rank's stage."""
         import ctypes as C
         from . import _lib
-        s = self.stream.cuda_stream
+        if self.lanes == 2:
+            assert n_microbatches % 2 == 0 and (head == "ids" or not self.is_last)
+            self.streams_l[1].wait_stream(self.stream)           # fork (also inside a graph capture)
         for i in range(n_microbatches):
+            lane = self.seq_no % self.lanes                      # a ring slot always sees the same lane (slots are even)
+            part, s = self.parts_l[lane], self.streams_l[lane].cuda_stream
             src = self.ring_in.recv(self.seq_no, s) if self.ring_in else idx_batch[i * self.mb:].data_ptr()
             if not self.is_last:
                 dst = self.ring_out.acquire(self.seq_no, s)
-                self.part.forward_ptr(src, dst, self.mb, self.seq_len, s)
+                part.forward_ptr(src, dst, self.mb, self.seq_len, s)
                 self.ring_out.publish(self.seq_no, s)
             elif head == "ids":
-                _lib.check(_lib.lib().b2p_stage_forward_argmax(self.part._handle, C.c_void_p(src),
+                self.ids = self.ids_l[lane]
+                _lib.check(_lib.lib().b2p_stage_forward_argmax(part._handle, C.c_void_p(src),
                                                                C.c_void_p(self.ids.data_ptr()), self.mb, self.seq_len,
                                                                C.c_void_p(s)))
             else:
                 if self.logits is None:
                     self.logits = torch.empty((self.mb, self.seq_len, self.cfg.vocab_size), device=self.dev)
-                self.part.forward_ptr(src, self.logits.data_ptr(), self.mb, self.seq_len, s)
+                part.forward_ptr(src, self.logits.data_ptr(), self.mb, self.seq_len, s)
             if self.ring_in:
                 self.ring_in.release(self.seq_no, s)
             self.seq_no += 1
+        if self.lanes == 2:
+            self.stream.wait_stream(self.streams_l[1])           # join
 
     def step_graph(self, idx_batch: torch.Tensor | None, n_microbatches: int, head: str = "ids"):
         """``step`` as ONE CUDA-graph launch per rank.  The ring counters live in device memory, so no launch carries a
