@@ -623,18 +623,29 @@ def gpt_bench(world: int, rank: int, dev: torch.device, peaks: dict, steps: int 
     if world == 1:
         import ctypes as C
         from . import _lib
-        first, final = [p.to(dev).eval() for p in engine.gpt_parts_for(model, 1, math=w["math"], max_tokens=mb * seq)]
+        # two lanes, as in GptRankPipeline: a second instance of the chain on a second stream takes every other
+        # microbatch, so its kernels fill the SMs the last wave of the other lane's kernels leaves idle
+        lanes = max(1, min(2, int(os.environ.get("B2P_GPT_LANES", "2")))) if n_mb % 2 == 0 else 1
+        chains = [[p.to(dev).eval() for p in engine.gpt_parts_for(model, 1, math=w["math"], max_tokens=mb * seq)]
+                  for _ in range(lanes)]
+        first, final = chains[0]
         idx = idx_host.to(dev)
-        hidden = torch.empty(mb, seq, cfg.n_embd, device=dev)
+        hiddens = [torch.empty(mb, seq, cfg.n_embd, device=dev) for _ in range(lanes)]
         ids = torch.empty(batch, seq, dtype=torch.int64, device=dev)
         stream = torch.cuda.Stream(device=dev)
-        s = stream.cuda_stream
+        streams = [stream] + [torch.cuda.Stream(device=dev) for _ in range(lanes - 1)]
 
         def step():
-            for lo in range(0, batch, mb):
-                first.forward_ptr(idx[lo:].data_ptr(), hidden.data_ptr(), mb, seq, s)
-                _lib.check(_lib.lib().b2p_stage_forward_argmax(final._handle, C.c_void_p(hidden.data_ptr()),
+            for st in streams[1:]:
+                st.wait_stream(stream)                           # fork (also inside the graph capture)
+            for i, lo in enumerate(range(0, batch, mb)):
+                lane = i % lanes
+                s = streams[lane].cuda_stream
+                chains[lane][0].forward_ptr(idx[lo:].data_ptr(), hiddens[lane].data_ptr(), mb, seq, s)
+                _lib.check(_lib.lib().b2p_stage_forward_argmax(chains[lane][1]._handle, C.c_void_p(hiddens[lane].data_ptr()),
                                                                C.c_void_p(ids[lo:].data_ptr()), mb, seq, C.c_void_p(s)))
+            for st in streams[1:]:
+                stream.wait_stream(st)                           # join
         step(); step()
         stream.synchronize()
         graph = torch.cuda.CUDAGraph()
@@ -690,5 +701,5 @@ def gpt_bench(world: int, rank: int, dev: torch.device, peaks: dict, steps: int 
     return {"what": w["what"], "model": f"gpt2-{w['model']}", "stages": world, "math": w["math"], "batch": batch, "seq_len": seq,
             "microbatch_sequences": mb, "layer_ranges": ranges or "even", "ms_per_batch": ms, "tokens_per_s": tokens / (ms * 1e-3),
             "model_tflops_total": tf, "frac_of_sustained_bf16_peak_per_gpu": tf / world / peaks["bf16_tflops_sustained"],
-            "launch": "one CUDA graph per rank per batch", "ids_equal_single_gpu": ids_equal, "steps": steps,
+            "launch": "one CUDA graph per rank per batch", "lanes_per_rank": (lanes if world == 1 else pipe.lanes), "ids_equal_single_gpu": ids_equal, "steps": steps,
             "data": "synthetic tokens, random-init weights (seed 1234)"}
