@@ -94,6 +94,20 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// the same two from warp-uniform code, predicated on elect.sync (see elect_one below): the tensor-map pointer, the
+// coordinates and the shared-memory addresses stay in uniform registers -- no ELECT / R2UR / BRA.U.ANY loop per load
+__device__ __forceinline__ void mbar_expect_tx_p(uint32_t bar_addr, uint32_t bytes, uint32_t lead) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t"
+               "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(bar_addr), "r"(bytes), "r"(lead) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_p(uint32_t smem_dst, const CUtensorMap* map, uint32_t bar_addr, int c0, int c1,
+                                              uint32_t lead) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_addr), "r"(c0), "r"(c1), "r"(lead)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {   // whole warp
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
                "r"(ncols)
@@ -427,7 +441,10 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
   pdl_wait();        // everything above overlapped the previous kernel's tail; its outputs are visible from here
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (uniform control flow, loads predicated on elect.sync) =====================
+    const uint32_t lead = elect_one();
+    const uint32_t tiles_u = __shfl_sync(0xffffffffu, smem_u32(tiles), 0);
+    const uint32_t full_u = __shfl_sync(0xffffffffu, smem_u32(full), 0);
     uint32_t stage = 0, phase = 0;
     for (int item = blockIdx.x; item < num_tiles; item += gridDim.x) {
       const int z = item % splits, tile = item / splits;
@@ -435,17 +452,14 @@ linear_tc(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
       const int kb0 = z * kb_per_split, kb1 = min(total_kb, kb0 + kb_per_split);
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1);
-        if (lane == 0) {
-          unsigned char* sa = tiles + stage * Cfg::STAGE_BYTES;
-          mbar_expect_tx(&full[stage], Cfg::STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, &full[stage], kb * Cfg::BK, m0);
-          tma_load_2d(sa + Cfg::A_BYTES, &tmap_w, &full[stage], kb * Cfg::BK, n0);
-          if (Cfg::SPLIT) {
-            tma_load_2d(sa + Cfg::A_PLANE, &tmap_a_lo, &full[stage], kb * Cfg::BK, m0);
-            tma_load_2d(sa + Cfg::A_BYTES + Cfg::B_PLANE, &tmap_w_lo, &full[stage], kb * Cfg::BK, n0);
-          }
+        const uint32_t sa = tiles_u + stage * Cfg::STAGE_BYTES, fb = full_u + stage * 8;
+        mbar_expect_tx_p(fb, Cfg::STAGE_BYTES, lead);
+        tma_load_2d_p(sa, &tmap_a, fb, kb * Cfg::BK, m0, lead);
+        tma_load_2d_p(sa + Cfg::A_BYTES, &tmap_w, fb, kb * Cfg::BK, n0, lead);
+        if (Cfg::SPLIT) {
+          tma_load_2d_p(sa + Cfg::A_PLANE, &tmap_a_lo, fb, kb * Cfg::BK, m0, lead);
+          tma_load_2d_p(sa + Cfg::A_BYTES + Cfg::B_PLANE, &tmap_w_lo, fb, kb * Cfg::BK, n0, lead);
         }
-        __syncwarp();
         if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
       }
     }

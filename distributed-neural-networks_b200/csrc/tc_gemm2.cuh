@@ -50,6 +50,14 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
       "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_pair_p(uint32_t smem_dst, const CUtensorMap* map, uint32_t leader_bar_addr, int c0,
+                                                   int c1, uint32_t lead) {      // from warp-uniform code (tc_gemm.cuh, elect_one)
+  asm volatile(
+      "{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+      "@q cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(leader_bar_addr & kPeerBitMask), "r"(c0), "r"(c1), "r"(lead)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
                : "memory");
@@ -150,19 +158,19 @@ linear_tc_pair(const __grid_constant__ CUtensorMap tmap_a,      // box [64 K, 12
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
+    const uint32_t lead = elect_one();                       // uniform control flow, loads predicated on elect.sync
+    const uint32_t tiles_u = __shfl_sync(0xffffffffu, smem_u32(tiles), 0);
+    const uint32_t full_u = __shfl_sync(0xffffffffu, smem_u32(full), 0);
     uint32_t stage = 0, phase = 0;
     for (int tile = pair; tile < num_tiles; tile += n_pairs) {
       const int m0 = (tile % tiles_m) * Cfg::BM_PAIR + rank * Cfg::BM_CTA;
       const int n0 = (tile / tiles_m) * BN + rank * (BN / 2);
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1);
-        if (lane == 0) {
-          unsigned char* sa = tiles + stage * Cfg::STAGE_BYTES;
-          if (rank == 0) mbar_expect_tx(&full[stage], 2 * Cfg::STAGE_BYTES);      // both CTAs' bytes land here
-          tma_load_2d_pair(sa, &tmap_a, &full[stage], kb * Cfg::BK, m0);
-          tma_load_2d_pair(sa + Cfg::A_BYTES, &tmap_w, &full[stage], kb * Cfg::BK, n0);
-        }
-        __syncwarp();
+        const uint32_t sa = tiles_u + stage * Cfg::STAGE_BYTES, fb = full_u + stage * 8;
+        if (rank == 0) mbar_expect_tx_p(fb, 2 * Cfg::STAGE_BYTES, lead);          // both CTAs' bytes land here
+        tma_load_2d_pair_p(sa, &tmap_a, fb, kb * Cfg::BK, m0, lead);
+        tma_load_2d_pair_p(sa + Cfg::A_BYTES, &tmap_w, fb, kb * Cfg::BK, n0, lead);
         if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
       }
     }
