@@ -186,14 +186,19 @@ B2P_API int b2p_stage_forward(b2p_stage* st, const void* in_dev, void* out_dev,
  *     math = B2P_MATH_FP32 has the reference's range.  (Un-normalised 0..255 images with
  *     ordinary weights are far inside the range; NaN inputs propagate to NaN outputs as in
  *     torch and are not flagged; +-inf inputs give NaN.)
+ *   - CIFAR part 1 in B2P_MATH_TF32X3: fc1 (cifar_model_parts.py:55) runs in the same split-fp16
+ *     scheme, so an activation or fc1 weight with |v| >= 65504 is flagged: B2P_ELIMIT (the
+ *     reference, fp32, stays finite there; math = B2P_MATH_FP32 has its range).
  * Returns 0 when clean. */
 B2P_API int b2p_stage_check(b2p_stage* st, void* stream);
 
 /* Developer aid (no reference counterpart): the first call arms a per-stage trace buffer,
  * later calls synchronise and copy out min(n, 1024) stamps of the CIFAR part-0 tensor-core
- * kernel: clock64 of CTA 0 as [role 0..3][sample 0..7][event 0..7] (entry 192 = end of set-up,
- * 250..254 = entry / exit), and from entry 256 on the %globaltimer entry and exit time of every
- * CTA (2 entries each).  n >= 256. */
+ * kernel: clock64 of CTA 0 as [role 0..3][sample 0..7][event 0..7] (entry 192 = end of set-up),
+ * from entry 256 on the %globaltimer entry / release / exit time of every CTA (3 entries each),
+ * 710..712 CTA 0's clock64 at entry / release / exit, 719.. a ring of the last 16 launches'
+ * release and exit times, 760.. who published which ring message and what it cost
+ * (scripts/trace_part0.py, scripts/probe_prod2.py decode it).  n >= 256. */
 B2P_API int b2p_stage_trace(b2p_stage* st, long long* host_out, int n);
 
 /* Developer aid (no reference counterpart): clock64 timeline of CTA (0,0,0) of the last tensor-core
