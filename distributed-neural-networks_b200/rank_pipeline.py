@@ -109,7 +109,9 @@ class CifarRankPipeline:
             # second half of every batch therefore enters through THAT GPU (pinned host -> its memory) and crosses to
             # this one over NVLink (6 MiB: 26 us) -- measured 110 GB/s for the two links together against 55 GB/s.
             self.via = None
-            if input_via_device is not None and input_via_device != device.index:
+            if (input_via_device is not None and input_via_device != device.index
+                    and 0 <= input_via_device < torch.cuda.device_count()
+                    and torch.cuda.can_device_access_peer(device.index, input_via_device)):
                 self.via = torch.device("cuda", input_via_device)
                 self.half = (self.n_mb // 2) * microbatch
                 self.hop_stream = torch.cuda.Stream(device=device)
@@ -256,6 +258,15 @@ class CifarRankPipeline:
             self.part.join(self.stream.cuda_stream)
 
 
+def input_over_both_links(world: int, override: str = "") -> bool:
+    """Host-facing path: does a 2-GPU pipeline take its input over both of its GPUs' host links?  Yes while the links are
+    the limit (up to two pipelines per node); from three pipelines up the host's memory system is (bench_main).
+    override: "1" / "0" force it (B2P_SPLIT_H2D)."""
+    if override in ("0", "1"):
+        return override == "1"
+    return world // 2 <= 2
+
+
 def bench_main(args) -> int:
     """bench.py --gpus N under torchrun (N >= 2)."""
     import torch.distributed as dist
@@ -281,8 +292,7 @@ def bench_main(args) -> int:
     # ask the host for more than its memory system delivers (~200 GB/s measured: 15.1 M split against 17.2 M over the
     # four stage-0 links alone), so from 3 pipelines up the input stays on the stage-0 links.  B2P_SPLIT_H2D=0/1 forces it.
     via = None
-    split_env = os.environ.get("B2P_SPLIT_H2D", "")
-    split_h2d = (split_env == "1") or (split_env != "0" and world // 2 <= 2)
+    split_h2d = input_over_both_links(world, os.environ.get("B2P_SPLIT_H2D", ""))
     if role.active and role.stage == 0 and split_h2d:
         via = dev.index + (role.next_rank - rank)            # one node: the stage-1 GPU of this pipeline
     pipe = CifarRankPipeline(role, dev, args.math, BATCH, MICROBATCH, slots=int(os.environ.get("B2P_RING_SLOTS", "32")),

@@ -27,6 +27,13 @@ def test_plan_two_stage_replicas():
     assert [x.stage for x in r] == list(range(8)) and r[7].next_rank is None and r[3].prev_rank == 2
 
 
+def test_input_link_policy():
+    rp = _rp()
+    assert rp.input_over_both_links(2) and rp.input_over_both_links(4)       # one or two pipelines: both host links each
+    assert not rp.input_over_both_links(8)                                   # four: the host's memory system is the limit
+    assert rp.input_over_both_links(8, "1") and not rp.input_over_both_links(2, "0")
+
+
 def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     import torch.distributed as dist
