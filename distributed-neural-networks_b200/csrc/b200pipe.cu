@@ -376,13 +376,13 @@ int gpt_blocks(b2p_stage* st, const float* x, float* final_out, int B, int T, cu
       else
         B2P_LAUNCH_PDL(kv::kv_append<float>, ceil_div(n, 256), 256, 0, s, st->ws_qkv, kc, vc, B, T, C, H, Tmax, pos0, pos_dev);
       if (decode) {
-        const size_t smem = ((size_t)Tmax + 64 + 128) * sizeof(float);
+        const size_t smem = ((size_t)Tmax + 64 + kv::DEC_THREADS) * sizeof(float);
         dim3 dgrid(H, B);
         if (bf)
-          B2P_LAUNCH_PDL(kv::attention_decode<__nv_bfloat16>, dgrid, 128, smem, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
+          B2P_LAUNCH_PDL(kv::attention_decode<__nv_bfloat16>, dgrid, kv::DEC_THREADS, smem, s, reinterpret_cast<const __nv_bfloat16*>(st->ws_qkv),
                          kc, vc, reinterpret_cast<__nv_bfloat16*>(st->ws_att), C, H, Tmax, pos0, pos_dev);
         else
-          B2P_LAUNCH_PDL(kv::attention_decode<float>, dgrid, 128, smem, s, st->ws_qkv, kc, vc, st->ws_att, C, H, Tmax, pos0, pos_dev);
+          B2P_LAUNCH_PDL(kv::attention_decode<float>, dgrid, kv::DEC_THREADS, smem, s, st->ws_qkv, kc, vc, st->ws_att, C, H, Tmax, pos0, pos_dev);
       }
     }
     if (decode) {

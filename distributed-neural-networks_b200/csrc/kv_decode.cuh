@@ -45,16 +45,19 @@ kv_append(const T* qkv, float* kc, float* vc,      // no __restrict__: qkv comes
   }
 }
 
-// One CTA of 128 threads per (sequence, head); the single query sits at position `pos` (keys 0..pos are in the cache).
-//   pass 1: thread t scores keys t, t+128, ... (64-term dot products, float4 loads of the 256-byte key rows)
+// One CTA of 512 threads per (sequence, head); the single query sits at position `pos` (keys 0..pos are in the cache).
+//   pass 1: thread t scores keys t, t+512, ... (64-term dot products, float4 loads of the 256-byte key rows)
 //   pass 2: soft-max over the scores in shared memory (max, exp, sum: fp32, like the causal kernels)
-//   pass 3: threads (half, d): half of the keys each, one output dim -- coalesced 256-byte reads of the value rows
+//   pass 3: threads (slice, d): an eighth of the keys each, one output dim -- coalesced 256-byte reads of the value rows
+// (With 128 threads -- two key slices in pass 3 -- a call took 31 us for 512 cached keys, 12 calls per decode step: each
+//  thread walked 256 value rows one dependent FMA after the other.)
+constexpr int DEC_THREADS = 512, DEC_SLICES = DEC_THREADS / 64;
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(DEC_THREADS)
 attention_decode(const T* qkv, const float* kc, const float* vc, T* y, int C, int H, int Tmax, int pos, const int* pos_dev) {
   extern __shared__ float sc[];                       // [Tmax] scores, then 64 q values, then scratch
   float* q = sc + Tmax;
-  float* red = q + 64;                                 // [128]
+  float* red = q + 64;                                 // [DEC_THREADS]
   const int h = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
   pdl_trigger();
   pdl_wait();
@@ -65,7 +68,7 @@ attention_decode(const T* qkv, const float* kc, const float* vc, T* y, int C, in
   const float* kb = kc + ((int64_t)b * H + h) * Tmax * 64;
   const float* vb = vc + ((int64_t)b * H + h) * Tmax * 64;
   float mx = -INFINITY;
-  for (int j = tid; j < n; j += 128) {
+  for (int j = tid; j < n; j += DEC_THREADS) {
     const float4* kr = reinterpret_cast<const float4*>(kb + (int64_t)j * 64);
     float s = 0.f;
 #pragma unroll
@@ -79,32 +82,37 @@ attention_decode(const T* qkv, const float* kc, const float* vc, T* y, int C, in
   }
   red[tid] = mx;
   __syncthreads();
-  for (int o = 64; o > 0; o >>= 1) {
+  for (int o = DEC_THREADS / 2; o > 0; o >>= 1) {
     if (tid < o) red[tid] = fmaxf(red[tid], red[tid + o]);
     __syncthreads();
   }
   mx = red[0];
   __syncthreads();
   float sum = 0.f;
-  for (int j = tid; j < n; j += 128) {
+  for (int j = tid; j < n; j += DEC_THREADS) {
     const float p = expf(sc[j] - mx);
     sc[j] = p;
     sum += p;
   }
   red[tid] = sum;
   __syncthreads();
-  for (int o = 64; o > 0; o >>= 1) {
+  for (int o = DEC_THREADS / 2; o > 0; o >>= 1) {
     if (tid < o) red[tid] += red[tid + o];
     __syncthreads();
   }
   const float inv = 1.0f / red[0];
   __syncthreads();
-  const int d = tid & 63, half = tid >> 6;
+  const int d = tid & 63, slice = tid >> 6;
   float acc = 0.f;
-  for (int j = half; j < n; j += 2) acc = fmaf(sc[j], vb[(int64_t)j * 64 + d], acc);
+  for (int j = slice; j < n; j += DEC_SLICES) acc = fmaf(sc[j], vb[(int64_t)j * 64 + d], acc);
   red[tid] = acc;
   __syncthreads();
-  if (tid < 64) from_f32(y + (int64_t)b * C + h * 64 + tid, (red[tid] + red[tid + 64]) * inv);
+  if (tid < 64) {
+    float o = red[tid];
+#pragma unroll
+    for (int sl = 1; sl < DEC_SLICES; ++sl) o += red[tid + 64 * sl];
+    from_f32(y + (int64_t)b * C + h * 64 + tid, o * inv);
+  }
 }
 
 }  // namespace kv
