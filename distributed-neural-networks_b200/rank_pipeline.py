@@ -514,10 +514,11 @@ class GptRankPipeline:
         # Two lanes (B2P_GPT_LANES=2): a second instance of the stage (own workspaces, own copy of the weights) on a second
         # stream takes every other microbatch, so the kernels of microbatch i+1 fill the SMs that the last wave of
         # microbatch i's kernels leaves idle (2048-token GEMMs are 1.3 to 2 waves of tiles on 148 SMs).
-        self.lanes = max(1, min(2, int(os.environ.get("B2P_GPT_LANES", "2"))))
+        self.lanes = int(os.environ.get("B2P_GPT_LANES", "2"))
+        self.lanes = self.lanes if self.lanes in (1, 2, 4) and slots % self.lanes == 0 else 1    # a ring slot always sees the same lane
         self.parts_l = [self.part]
         self.streams_l = [self.stream]
-        if self.lanes == 2:
+        for _ in range(self.lanes - 1):
             parts2 = engine.gpt_parts_for(model, role.stages, math=math, max_tokens=mb_seqs * seq, ranges=ranges)
             self.parts_l.append(parts2[role.stage].to(device).eval())
             self.streams_l.append(torch.cuda.Stream(device=device))
@@ -541,9 +542,10 @@ class GptRankPipeline:
         """One batch = n_microbatches microbatches of mb_seqs sequences through this rank's stage."""
         import ctypes as C
         from . import _lib
-        if self.lanes == 2:
+        if self.lanes > 1:
             assert head == "ids" or not self.is_last            # (the logits buffer of the final rank is not doubled)
-            self.streams_l[1].wait_stream(self.stream)           # fork (also inside a graph capture)
+            for st in self.streams_l[1:]:
+                st.wait_stream(self.stream)                      # fork (also inside a graph capture)
         for i in range(n_microbatches):
             lane = self.seq_no % self.lanes                      # a ring slot always sees the same lane (slots are even)
             part, s = self.parts_l[lane], self.streams_l[lane].cuda_stream
@@ -564,8 +566,8 @@ class GptRankPipeline:
             if self.ring_in:
                 self.ring_in.release(self.seq_no, s)
             self.seq_no += 1
-        if self.lanes == 2:
-            self.stream.wait_stream(self.streams_l[1])           # join
+        for st in self.streams_l[1:]:
+            self.stream.wait_stream(st)                          # join
 
     def step_graph(self, idx_batch: torch.Tensor | None, n_microbatches: int, head: str = "ids"):
         """``step`` as ONE CUDA-graph launch per rank.  The ring counters live in device memory, so no launch carries a
