@@ -18,18 +18,24 @@
 //          The B operand of tap (kh,kw) is a plain shifted window of the activation (three x-shifted copies with a
 //          zero halo, as in round 1): no im2col.  The accumulator comes out [channel][pixel], i.e. already in the
 //          reference's flatten order c*64+h*8+w, and the 2x2 pool is between a thread's own columns.
-//   conv1  as a "pool-window" GEMM: one column per POOLED pixel, one row per (channel, dy, dx) of its 2x2 window
-//          (32 x 4 = 128 rows: a full M), K = 3 channels x 4x4 input window = 48 (weights zero-padded 3x3 -> 4x4).
-//          Three split-fp16 products into ONE accumulator: lo terms first, then the first hi*hi MMA carries
-//          scale-input-d = 2^-11 (D = A*B + D*2^-11).  18 MMAs (N = 128) per sample instead of 6.9 k FP32-pipe cycles.
-//          The epilogue pools across the 4 lanes of a channel with lane-swapping shuffles, transposes 8x8 across
-//          lanes and writes the fp16 hi/lo activation rows for conv2.
+//   conv1  as a "pool-window" GEMM: one ROW per POOLED pixel (M = the 128 pooled pixels of half a sample), one column per
+//          (channel, dy, dx) of its 2x2 window (32 x 4 = 128 columns), K = 3 channels x 4x4 input window = 48 (weights
+//          zero-padded 3x3 -> 4x4).  Three split-fp16 products into ONE accumulator: lo terms first, then the first
+//          hi*hi MMA carries scale-input-d = 2^-11 (D = A*B + D*2^-11).  18 MMAs (N = 128) per sample instead of 6.9 k
+//          FP32-pipe cycles.  In the epilogue a thread owns a pixel and eight channels; the four window positions of a
+//          channel are its own neighbouring columns, so pool, bias, ReLU, the fp16 hi/lo split and the 16-byte rows of
+//          the activation copies need no shuffle (with the channels on M it took 48 per thread).
 //
 // Warp roles (20 warps, one persistent CTA per SM, samples blockIdx.x, +gridDim.x, ...):
-//   0..1     conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo)
-//   2        publisher: bulk copy of the finished sample to HBM or straight into the next GPU's ring slot (+ ring handshake)
-//   3        MMA issuer
+//   0..1     conv1 patch producers (input image -> 4x4 windows, fp16 hi/lo); they start on the first image while the
+//            other warps still set the kernel up
+//   2        publisher: four lanes send the finished samples in turn, one 16 KB bulk copy each, to HBM or straight into
+//            the next GPU's ring slot (+ the ring handshake: all slots of the step acquired before the first copy)
+//   3        MMA issuer: all 32 lanes in uniform control flow, tensor-core instructions predicated on elect.sync
 //   4..19    epilogue warps: drain conv2's accumulator (-> staging tile) and run conv1's epilogue, alternately
+// Set-up: conv2's tensor-memory image arrives by ONE bulk copy into the not-yet-used activation buffer and goes to
+// tensor memory from there.  Ring mode with bit 2 of the stage's PDL mask: no griddepcontrol.wait, consecutive steps
+// overlap (b200pipe.h).
 //
 // Arithmetic and range are those of round 1's kernel: x ~= hi + lo * 2^-11 with fp16 hi/lo, products exact in the
 // fp32 accumulator, the lo*lo term dropped.  |input| and |conv1 output| must stay below 65504 (fp16 range); beyond
