@@ -1,4 +1,6 @@
 // fc_stage_tc.cuh -- fc1 of CIFAR part 1 in the tensor-core parity mode (math = tf32x3), split-K 32.
+// Two kernels: fc1_f16x3_splitk (split fp16, second half of this file) is what runs; fc1_x3_splitk (3xTF32, round 1,
+// described first) stays behind B2P_FC1_TF32=1 for A/B measurements.
 //
 // Reference: ModelPart1_2Node.forward, cifar_model_parts.py:53-58
 //     x = relu(fc1(x)); x = fc2(x); return softmax(x, dim=1)          [B,4096] -> [B,10]
