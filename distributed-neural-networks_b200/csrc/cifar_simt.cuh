@@ -210,6 +210,9 @@ fc1_splitk_f32(const float* __restrict__ x,     // [M,4096]
 // GROUP: the partials are first added in groups of GROUP, left to right (((p0+p1)+p2)+p3, ...), the association the fc1
 // kernels of fc_stage_tc.cuh use when they sum the K slices of an item themselves -- so 32 single-slice partials with
 // GROUP = 4 and 8 four-slice partials with GROUP = 1 give the same bits (GROUP = 2: the 3xTF32 kernel's slice pairs).
+// (Tried: four consecutive rows per CTA, fc2's 20 KB of weights loaded once per four rows instead of once per row:
+//  part 1 went from 30.7 to 33.8 us per 1024 rows -- the 96 registers of that variant and a quarter of the CTAs hide the
+//  L2 latency of the partial-sum loads worse than 1024 small CTAs do.)
 template <int SPLITS, int GROUP = 1>
 __global__ void __launch_bounds__(128)
 fc_tail_f32(const float* __restrict__ ws, int M,
